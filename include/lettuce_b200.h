@@ -1,0 +1,164 @@
+/*
+ * lettuce_b200.h -- C ABI of the B200-native stream-collide engine.
+ *
+ * This is the drop-in boundary for lettuce's per-timestep hot path.  Every entry point
+ * takes plain pointers and sizes (device pointers unless the name says `_host`), returns
+ * 0 on success or a negative LB_E* code, and leaves a message retrievable with
+ * lb_last_error().  Nothing here depends on torch / pybind.
+ *
+ * Reference interfaces replaced (paths relative to the reference checkout):
+ *   - the per-step seam `Simulation._collide_and_stream(simulation)`
+ *       lettuce/_simulation.py:92-96,148,202              -> lb_step()
+ *   - the generated pybind11 extension entry
+ *       `collide_and_stream_<hash>(f, f_next[, no_collision_mask, no_streaming_mask]
+ *        [, tau_inv][, velocityK, densityK]...)`
+ *       lettuce/cuda_native/_template.py:59-86,297-367     -> lb_step()
+ *   - `Collision.__call__(flow)` (bgk_collision.py:17-22, trt_collision.py:16-27,
+ *       kbc_collision.py:96-160, no_collision.py:9-11) and `Boundary.__call__(flow)`
+ *       (bounce_back_boundary.py:17-18, equilibrium_boundary_pu.py:27-32)
+ *                                                          -> lb_collide()
+ *   - `Flow.rho/j/u` (lettuce/_flow.py:136-172)            -> lb_moments()
+ *   - the reporter reductions IncompressibleKineticEnergy / MaximumVelocity / Enstrophy
+ *       (lettuce/ext/_reporter/observable_reporter.py:27-68, util/utility.py:37-99)
+ *                                                          -> lb_observables(), and the
+ *       fused per-step variant through lb_fields.obs_out
+ *
+ * Layout: populations are f[q][x][y][z] (2-D: f[q][x][y]), C-contiguous, last axis
+ * fastest, exactly the reference's `flow.f` tensor (lettuce/_flow.py:89-91).
+ * Stencil index order is the reference's (d2q9.py:8-10, d3q19.py:8-13, d3q27.py:8-12).
+ */
+#ifndef LETTUCE_B200_H
+#define LETTUCE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define LB_API __attribute__((visibility("default")))
+#else
+#define LB_API
+#endif
+
+#define LB_ABI_VERSION 1
+#define LB_MAX_BOUNDARIES 8
+
+enum { LB_D2Q9 = 0, LB_D3Q19 = 1, LB_D3Q27 = 2 };                     /* lb_desc.stencil   */
+enum { LB_F32 = 0, LB_F64 = 1 };                                      /* lb_desc.dtype     */
+enum { LB_COLL_NONE = 0, LB_COLL_BGK = 1, LB_COLL_TRT = 2, LB_COLL_KBC = 3 }; /* .collision */
+enum { LB_BND_BOUNCE_BACK = 1, LB_BND_EQUILIBRIUM = 2 };              /* lb_boundary.kind  */
+
+enum {
+  LB_OK = 0,
+  LB_EINVAL = -1,      /* bad descriptor / null pointer / unsupported combination */
+  LB_ECUDA = -2,       /* a CUDA runtime call failed; see lb_last_error()         */
+  LB_EUNSUPPORTED = -3 /* e.g. KBC on D3Q19 (kbc_collision.py:101,115)            */
+};
+
+/* observables written per step into lb_fields.obs_out / by lb_observables():
+ * all in LATTICE units, accumulated in double precision.                          */
+enum {
+  LB_OBS_ENERGY = 0,   /* sum_nodes 0.5 |u|^2           (_flow.py:178-181)          */
+  LB_OBS_MAXU2 = 1,    /* max_nodes |u|^2               (observable_reporter.py:30) */
+  LB_OBS_MASS = 2,     /* sum_nodes rho                                           */
+  LB_OBS_ENSTROPHY = 3,/* sum |curl u|^2, 6th-order FD  (observable_reporter.py:53-68) */
+  LB_OBS_COUNT = 4
+};
+
+typedef struct lb_desc {
+  int32_t stencil;     /* LB_D2Q9 | LB_D3Q19 | LB_D3Q27 */
+  int32_t dtype;       /* LB_F32 | LB_F64               */
+  int32_t collision;   /* LB_COLL_*                     */
+  int32_t ndim;        /* 2 or 3 (must match stencil)   */
+  int64_t dims[3];     /* resolution, dims[ndim-1] is the contiguous axis */
+  double tau;          /* BGK: tau; TRT: tau_plus; KBC: tau (beta = 1/(2 tau)) */
+  double tau_minus;    /* TRT only (trt_collision.py:12-14) */
+} lb_desc;
+
+/* One entry per boundary object, in the order lettuce sorted them
+ * (_simulation.py:57-58): entry i applies where no_collision_mask == i + 1.
+ * rho / u are in lattice units, element type = lb_desc.dtype, addressed as
+ *   rho[x*rho_stride[0] + y*rho_stride[1] + z*rho_stride[2]]
+ *   u  [c*u_comp_stride + x*u_stride[0] + y*u_stride[1] + z*u_stride[2]]
+ * with strides in ELEMENTS; a stride of 0 broadcasts that axis
+ * (equilibrium_boundary_pu.py:21-32; tests/boundary/test_equilibrium_bc_pu.py:125-148). */
+typedef struct lb_boundary {
+  int32_t kind;
+  int32_t _pad;
+  const void* rho;
+  const void* u;
+  int64_t rho_stride[3];
+  int64_t u_stride[3];
+  int64_t u_comp_stride;
+} lb_boundary;
+
+typedef struct lb_fields {
+  void* f;                          /* populations, state in / (n even) state out        */
+  void* f_next;                     /* second buffer (flow.f_next); (n odd) state out    */
+  const uint8_t* no_collision_mask; /* [*res] uint8, value = boundary index, or NULL     */
+  const uint32_t* streaming_bits;   /* [*res] packed no_streaming_mask (bit q = nsm[q,x]),
+                                       from lb_pack_streaming_mask(), or NULL            */
+  const lb_boundary* boundaries;    /* n_boundaries entries (host memory)                */
+  int32_t n_boundaries;
+  int32_t _pad;
+  double* obs_out;                  /* device, [n_steps][LB_OBS_COUNT] or NULL: energy, max|u|^2
+                                       and mass of the state each step CONSUMES (f_t before
+                                       collide), fused into the step kernel               */
+  void* obs_scratch;                /* device scratch, lb_obs_scratch_bytes() bytes, if obs_out */
+  void* u_out;                      /* device [d][*res] or NULL: velocity of the consumed
+                                       state of the LAST step of the call (for enstrophy) */
+} lb_fields;
+
+LB_API int lb_abi_version(void);
+LB_API const char* lb_last_error(void);
+
+/* Advance n_steps time steps (collide -> boundaries -> stream each).  Buffers ping-pong:
+ * after the call the new state is in `f_next` if n_steps is odd, in `f` if even.
+ * All launches go to `stream` (a cudaStream_t; NULL = legacy default stream); no host sync. */
+LB_API int lb_step(const lb_desc* desc, const lb_fields* fields, int n_steps, void* stream);
+
+/* Collision (where mask == 0) and boundaries (where mask == i) only, no streaming:
+ * out may alias in.  Implements Collision.__call__ / Boundary.__call__. */
+LB_API int lb_collide(const lb_desc* desc, const void* f_in, void* f_out,
+               const uint8_t* no_collision_mask, const lb_boundary* boundaries,
+               int n_boundaries, void* stream);
+
+/* Pure streaming with optional destination mask (_simulation.py:160-175). */
+LB_API int lb_stream(const lb_desc* desc, const void* f_in, void* f_out,
+              const uint32_t* streaming_bits, void* stream);
+
+/* bits[x] |= (nsm[q][x] == 1) << q   (nsm: uint8 [q][*res]) */
+LB_API int lb_pack_streaming_mask(const lb_desc* desc, const uint8_t* nsm, uint32_t* bits, void* stream);
+
+/* rho_out [*res] and/or u_out [d][*res] (either may be NULL) */
+LB_API int lb_moments(const lb_desc* desc, const void* f, void* rho_out, void* u_out, void* stream);
+
+/* Standalone reduction of LB_OBS_* over state f into obs_out[LB_OBS_COUNT] (device, double).
+ * `want_enstrophy` != 0 additionally needs u_scratch [d][*res] of dtype. */
+LB_API size_t lb_obs_scratch_bytes(const lb_desc* desc);
+LB_API int lb_observables(const lb_desc* desc, const void* f, int want_enstrophy, void* u_scratch,
+                   void* obs_scratch, double* obs_out, void* stream);
+
+/* Enstrophy (lattice units, dx = 1) of a velocity field u [d][*res] (e.g. lb_fields.u_out)
+ * into obs_out[LB_OBS_ENSTROPHY]. */
+LB_API int lb_enstrophy(const lb_desc* desc, const void* u, void* obs_scratch, double* obs_out, void* stream);
+
+/* Host-buffer convenience entry (end-to-end path): copies f_host -> device, runs n_steps,
+ * copies the result back into f_host, synchronises.  masks / boundary arrays are HOST
+ * pointers here as well (nsm is the raw uint8 [q][*res] mask or NULL). */
+LB_API int lb_run_host(const lb_desc* desc, void* f_host, const uint8_t* ncm_host,
+                const uint8_t* nsm_host, const lb_boundary* boundaries_host_ptrs,
+                int n_boundaries, int n_steps, double* obs_host /* [LB_OBS_COUNT] or NULL */);
+
+/* Introspection for tests / roofline arithmetic */
+LB_API int lb_stencil_q(int stencil);
+LB_API size_t lb_bytes_per_update(const lb_desc* desc); /* 2 * Q * sizeof(dtype) */
+LB_API int lb_vector_width(const lb_desc* desc, int has_streaming_bits); /* nodes per thread chosen */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LETTUCE_B200_H */

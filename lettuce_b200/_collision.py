@@ -1,0 +1,114 @@
+"""Collision operators with the reference's constructor signatures.  Each carries a POD
+kernel descriptor (`native_descriptor`) instead of the reference's code generator, and
+`__call__(flow)` runs the native collide-only kernel (lb_collide) so the operator can still be
+used on its own, e.g. by conservation tests (reference/tests/collision/*).
+
+BGK  reference/lettuce/ext/_collision/bgk_collision.py:12-35
+TRT  .../trt_collision.py:6-27        KBC  .../kbc_collision.py:11-167
+None .../no_collision.py:9-17"""
+import warnings
+from abc import ABC, abstractmethod
+
+import torch
+
+from . import _native as nat
+
+__all__ = ['Collision', 'BGKCollision', 'TRTCollision', 'KBCCollision', 'KBCCollision2D',
+           'KBCCollision3D', 'NoCollision']
+
+
+class Collision(ABC):
+    """reference/lettuce/_simulation.py:16-27"""
+
+    @abstractmethod
+    def native_descriptor(self, flow: 'Flow') -> dict:
+        """{'collision': LB_COLL_*, 'tau': float, 'tau_minus': float}"""
+        ...
+
+    def native_available(self) -> bool:
+        return True
+
+    def native_generator(self):
+        return self
+
+    def __call__(self, flow: 'Flow') -> torch.Tensor:
+        """collision(flow) -> post-collision populations (new tensor), on the GPU."""
+        f = flow.f
+        if not f.is_cuda:
+            raise nat.NativeError("lettuce_b200 collisions run on CUDA tensors only (no CPU fallback)")
+        d = self.native_descriptor(flow)
+        desc = nat.make_desc(type(flow.stencil).__name__, f.dtype, flow.resolution, d['collision'],
+                             d.get('tau', 1.0), d.get('tau_minus', 1.0))
+        f = f.contiguous()
+        out = torch.empty_like(f)
+        with torch.cuda.device(f.device):
+            nat.check(nat.lib().lb_collide(desc, f.data_ptr(), out.data_ptr(), None, None, 0,
+                                           nat.current_stream_ptr(f.device)))
+        return out
+
+
+class NoCollision(Collision):
+    def native_descriptor(self, flow):
+        return dict(collision=nat.LB_COLL_NONE)
+
+    def __call__(self, flow):
+        return flow.f
+
+
+class BGKCollision(Collision):
+    def __init__(self, tau, force=None):
+        if force is not None:
+            raise NotImplementedError("forcing schemes are outside the hot-path scope (SURVEY.md "
+                                      "section 2 row 7); the reference's native path has none either")
+        self.tau = tau
+        self.force = force
+
+    def name(self):
+        return self.__class__.__name__
+
+    def native_descriptor(self, flow):
+        return dict(collision=nat.LB_COLL_BGK, tau=float(self.tau))
+
+
+class TRTCollision(Collision):
+    def __init__(self, tau, tau_minus=1.0):
+        self.tau_plus = tau
+        self.tau_minus = tau_minus
+
+    def native_descriptor(self, flow):
+        return dict(collision=nat.LB_COLL_TRT, tau=float(self.tau_plus), tau_minus=float(self.tau_minus))
+
+
+class KBCCollision(Collision):
+    """Entropic multi-relaxation model (Karlin et al.).  As in the reference, the constructor's
+    tau is ignored: tau is read from flow.units.relaxation_parameter_lu at first use
+    (kbc_collision.py:97-99)."""
+
+    def __init__(self, tau: float = None):
+        self.tau = tau
+        self.beta = None
+
+    def native_descriptor(self, flow):
+        if self.beta is None:
+            name = type(flow.stencil).__name__
+            if flow.stencil.d == 3:
+                assert name == "D3Q27", "KBC Collision is only implemented for D3Q27!"
+            elif flow.stencil.d == 2:
+                assert name == "D2Q9", "KBC Collision is only implemented for D2Q9!"
+            else:
+                raise NotImplementedError("KBC Collision is only implemented for 2d and 3d!")
+            self.tau = flow.units.relaxation_parameter_lu
+            self.beta = 1. / (2 * self.tau)
+        return dict(collision=nat.LB_COLL_KBC, tau=float(self.tau))
+
+
+class KBCCollision2D(KBCCollision):
+    def __init__(self, tau: float = None):
+        warnings.warn("KBCCollision2D is is deprecated! Use KBCCollision instead!")
+        super().__init__()
+
+
+class KBCCollision3D(KBCCollision):
+    def __init__(self, tau: float = None):
+        warnings.warn("KBCCollision2D is is deprecated! Use KBCCollision instead!")
+        super().__init__()

@@ -1,0 +1,488 @@
+// C ABI of the engine (include/lettuce_b200.h) and the small stencil-independent kernels
+// (mask packing, enstrophy).  Translates the runtime descriptor into the template
+// instantiations of lb_kernels.cuh; launches on the caller's stream, never synchronises
+// (except lb_run_host, which is a host-buffer convenience entry).
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <vector>
+
+#include "../../include/lettuce_b200.h"
+#include "lb_kernels.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define LB_CUDA(call)                                                                 \
+  do {                                                                                \
+    cudaError_t e_ = (call);                                                          \
+    if (e_ != cudaSuccess)                                                            \
+      return fail(LB_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_),   \
+                  __FILE__, __LINE__);                                                \
+  } while (0)
+
+struct Geometry {
+  unsigned nx, ny, nz;  // kernel axes (Z contiguous); 2-D runs as nx = 1
+  unsigned n_nodes;
+  int q, d;
+};
+
+int stencil_q(int s) { return s == LB_D2Q9 ? 9 : s == LB_D3Q19 ? 19 : s == LB_D3Q27 ? 27 : -1; }
+int stencil_d(int s) { return s == LB_D2Q9 ? 2 : (s == LB_D3Q19 || s == LB_D3Q27) ? 3 : -1; }
+
+int check_desc(const lb_desc* d, Geometry* g) {
+  if (!d) return fail(LB_EINVAL, "null descriptor");
+  const int q = stencil_q(d->stencil), dim = stencil_d(d->stencil);
+  if (q < 0) return fail(LB_EINVAL, "unknown stencil id %d", d->stencil);
+  if (d->ndim != dim) return fail(LB_EINVAL, "stencil is %d-D but ndim = %d", dim, d->ndim);
+  if (d->dtype != LB_F32 && d->dtype != LB_F64) return fail(LB_EINVAL, "unknown dtype %d", d->dtype);
+  if (d->collision < LB_COLL_NONE || d->collision > LB_COLL_KBC)
+    return fail(LB_EINVAL, "unknown collision id %d", d->collision);
+  if (d->collision == LB_COLL_KBC && d->stencil == LB_D3Q19)
+    return fail(LB_EUNSUPPORTED, "KBC collision is only implemented for D2Q9 and D3Q27");
+  long long n = 1;
+  for (int a = 0; a < dim; ++a) {
+    if (d->dims[a] < 1) return fail(LB_EINVAL, "dims[%d] = %lld", a, (long long)d->dims[a]);
+    n *= d->dims[a];
+    if (n >= (1ll << 31)) return fail(LB_EINVAL, "more than 2^31-1 nodes per device");
+  }
+  if (d->collision != LB_COLL_NONE && !(d->tau > 0.0)) return fail(LB_EINVAL, "tau must be > 0");
+  if (d->collision == LB_COLL_TRT && !(d->tau_minus > 0.0)) return fail(LB_EINVAL, "tau_minus must be > 0");
+  g->q = q;
+  g->d = dim;
+  if (dim == 2) { g->nx = 1; g->ny = (unsigned)d->dims[0]; g->nz = (unsigned)d->dims[1]; }
+  else { g->nx = (unsigned)d->dims[0]; g->ny = (unsigned)d->dims[1]; g->nz = (unsigned)d->dims[2]; }
+  g->n_nodes = (unsigned)n;
+  return LB_OK;
+}
+
+template <typename T>
+lb::CollisionParams<T> make_cp(const lb_desc* d) {
+  lb::CollisionParams<T> cp{};
+  if (d->collision == LB_COLL_NONE) return cp;
+  cp.omega = T(1.0 / d->tau);
+  cp.inv_2tau_p = T(1.0 / (2.0 * d->tau));
+  cp.inv_2tau_m = T(1.0 / (2.0 * (d->collision == LB_COLL_TRT ? d->tau_minus : 1.0)));
+  const double beta = 1. / (2 * d->tau);
+  cp.beta = T(beta);
+  cp.inv_beta = T(1. / beta);
+  return cp;
+}
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+template <typename T>
+int vector_width(const Geometry& g, const void* a, const void* b, bool sbits) {
+  constexpr unsigned VEC = 16 / sizeof(T);
+  if (sbits) return 1;
+  if (g.nz % VEC != 0) return 1;
+  if (!aligned16(a) || !aligned16(b)) return 1;
+  return VEC;
+}
+
+template <typename T>
+int fill_boundaries(const lb_desc* d, const Geometry& g, const lb_boundary* b, int nb,
+                    lb::StepParams<T>* p) {
+  if (nb < 0 || nb > LB_MAX_BOUNDARIES) return fail(LB_EINVAL, "n_boundaries = %d (max %d)", nb, LB_MAX_BOUNDARIES);
+  if (nb > 0 && !b) return fail(LB_EINVAL, "boundaries is null");
+  p->n_bnd = nb;
+  for (int i = 0; i < nb; ++i) {
+    lb::BoundaryDev<T>& o = p->bnd[i];
+    o.kind = b[i].kind;
+    o.rho = static_cast<const T*>(b[i].rho);
+    o.u = static_cast<const T*>(b[i].u);
+    o.ucs = b[i].u_comp_stride;
+    if (o.kind != LB_BND_BOUNCE_BACK && o.kind != LB_BND_EQUILIBRIUM)
+      return fail(LB_EINVAL, "boundary %d: unknown kind %d", i, o.kind);
+    if (o.kind == LB_BND_EQUILIBRIUM && (!o.rho || !o.u))
+      return fail(LB_EINVAL, "boundary %d: equilibrium boundary needs rho and u", i);
+    // lattice axes -> kernel axes (2-D: X unused)
+    for (int a = 0; a < 3; ++a) { o.rs[a] = 0; o.us[a] = 0; }
+    for (int a = 0; a < g.d; ++a) {
+      const int ka = (g.d == 2) ? a + 1 : a;
+      o.rs[ka] = b[i].rho_stride[a];
+      o.us[ka] = b[i].u_stride[a];
+    }
+  }
+  return LB_OK;
+}
+
+template <class S, typename T>
+int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_steps, bool do_stream,
+               cudaStream_t st) {
+  lb::StepParams<T> p{};
+  p.nx = g.nx; p.ny = g.ny; p.nz = g.nz; p.n_nodes = g.n_nodes;
+  p.cp = make_cp<T>(d);
+  p.ncm = fl->no_collision_mask;
+  p.sbits = fl->streaming_bits;
+  int rc = fill_boundaries<T>(d, g, fl->boundaries, fl->n_boundaries, &p);
+  if (rc) return rc;
+  if (p.sbits && !p.ncm) return fail(LB_EINVAL, "streaming_bits requires no_collision_mask (lettuce creates both, _simulation.py:71-75)");
+
+  lb::StepConfig c{};
+  c.collision = d->collision;
+  c.mode = p.sbits ? lb::MODE_NCM_SBITS : (p.ncm ? lb::MODE_NCM : lb::MODE_PLAIN);
+  c.stream = do_stream;
+  c.vec = do_stream ? vector_width<T>(g, fl->f, fl->f_next, p.sbits != nullptr) : 1;
+  p.nzv = g.nz / c.vec;
+  p.n_threads = g.nx * g.ny * p.nzv;
+
+  unsigned* counter = nullptr;
+  double* partials = nullptr;
+  if (fl->obs_out) {
+    if (!fl->obs_scratch) return fail(LB_EINVAL, "obs_out given without obs_scratch");
+    counter = static_cast<unsigned*>(fl->obs_scratch);
+    partials = reinterpret_cast<double*>(static_cast<char*>(fl->obs_scratch) + 64);
+    LB_CUDA(cudaMemsetAsync(counter, 0, 64, st));
+  }
+  T* a = static_cast<T*>(fl->f);
+  T* b = static_cast<T*>(fl->f_next);
+  for (int s = 0; s < n_steps; ++s) {
+    p.f_in = a;
+    p.f_out = b;
+    c.obs = fl->obs_out != nullptr;
+    p.obs_counter = counter;
+    p.obs_partials = partials;
+    p.obs_out = c.obs ? fl->obs_out + (size_t)s * LB_OBS_COUNT : nullptr;
+    p.u_out = (c.obs && s == n_steps - 1) ? static_cast<T*>(fl->u_out) : nullptr;
+    cudaError_t e = lb::launch_step<S, T>(c, p, st);
+    if (e != cudaSuccess) return fail(LB_ECUDA, "step kernel launch failed: %s", cudaGetErrorString(e));
+    T* t = a; a = b; b = t;
+  }
+  return LB_OK;
+}
+
+template <typename T>
+int step_stencil(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n, bool s, cudaStream_t st) {
+  switch (d->stencil) {
+    case LB_D2Q9: return step_typed<lb::D2Q9, T>(d, g, fl, n, s, st);
+    case LB_D3Q19: return step_typed<lb::D3Q19, T>(d, g, fl, n, s, st);
+    case LB_D3Q27: return step_typed<lb::D3Q27, T>(d, g, fl, n, s, st);
+  }
+  return fail(LB_EINVAL, "bad stencil");
+}
+
+int step_any(const lb_desc* d, const lb_fields* fl, int n_steps, bool do_stream, void* stream) {
+  Geometry g;
+  int rc = check_desc(d, &g);
+  if (rc) return rc;
+  if (!fl || !fl->f || !fl->f_next) return fail(LB_EINVAL, "null population buffer");
+  if (fl->f == fl->f_next && do_stream) return fail(LB_EINVAL, "f and f_next must be distinct buffers");
+  if (n_steps < 0) return fail(LB_EINVAL, "n_steps = %d", n_steps);
+  if (fl->u_out && !fl->obs_out) return fail(LB_EINVAL, "u_out requires obs_out");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return d->dtype == LB_F32 ? step_stencil<float>(d, g, fl, n_steps, do_stream, st)
+                            : step_stencil<double>(d, g, fl, n_steps, do_stream, st);
+}
+
+// ---- bits[x] = OR_q (nsm[q][x] == 1) << q ------------------------------------------------
+__global__ void pack_sbits_kernel(const uint8_t* __restrict__ nsm, uint32_t* __restrict__ bits,
+                                  unsigned n_nodes, int q) {
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_nodes) return;
+  uint32_t w = 0;
+  for (int k = 0; k < q; ++k) w |= (nsm[(size_t)k * n_nodes + i] == 1 ? 1u : 0u) << k;  // torch.eq(nsm, 1), _simulation.py:173
+  bits[i] = w;
+}
+
+// ---- enstrophy: sum |curl u|^2 with the 6th-order periodic central difference -------------
+// reference/lettuce/util/utility.py:37-99 (weights [-1/60, 3/20, -3/4, 3/4, -3/20, 1/60] on
+// roll shifts [+3, +2, +1, -1, -2, -3], i.e. on u[x-3] ... u[x+3]) and
+// observable_reporter.py:53-68.  u is [D][n_nodes] in lattice units, dx = 1.
+template <typename T>
+__device__ __forceinline__ T diff6(const T* __restrict__ u, unsigned base, unsigned i, unsigned n,
+                                   unsigned stride) {
+  // base = node index with the differentiated coordinate set to 0
+  auto at = [&](int s) {
+    int j = int(i) + s;
+    if (j < 0) j += int(n);
+    if (j >= int(n)) j -= int(n);
+    return u[base + unsigned(j) * stride];
+  };
+  return T(-1.0 / 60) * at(-3) + T(3.0 / 20) * at(-2) + T(-3.0 / 4) * at(-1) + T(3.0 / 4) * at(1) +
+         T(-3.0 / 20) * at(2) + T(1.0 / 60) * at(3);
+}
+
+template <typename T, int D>
+__global__ void __launch_bounds__(lb::STEP_BLOCK)
+enstrophy_kernel(const T* __restrict__ u, unsigned n0, unsigned n1, unsigned n2, unsigned n_nodes,
+                 double* partials, unsigned* counter, double* out) {
+  // lattice axes: D == 2 -> (n0, n1), D == 3 -> (n0, n1, n2); last is contiguous
+  const unsigned tid = blockIdx.x * lb::STEP_BLOCK + threadIdx.x;
+  double acc = 0.0;
+  if (tid < n_nodes) {
+    const T* u0 = u;
+    const T* u1 = u + (size_t)n_nodes;
+    if constexpr (D == 2) {
+      const unsigned i0 = tid / n1, i1 = tid - i0 * n1;
+      const T d1u0 = diff6<T>(u0, i0 * n1, i1, n1, 1);        // d u0 / d y
+      const T d0u1 = diff6<T>(u1, i1, i0, n0, n1);            // d u1 / d x
+      const T w = d1u0 - d0u1;
+      acc = double(w * w);
+    } else {
+      const T* u2 = u + 2 * (size_t)n_nodes;
+      const unsigned i0 = tid / (n1 * n2);
+      const unsigned r = tid - i0 * n1 * n2;
+      const unsigned i1 = r / n2, i2 = r - i1 * n2;
+      const unsigned b0 = i1 * n2 + i2, s0 = n1 * n2;          // vary axis 0
+      const unsigned b1 = i0 * n1 * n2 + i2, s1 = n2;          // vary axis 1
+      const unsigned b2 = i0 * n1 * n2 + i1 * n2;              // vary axis 2
+      const T wz = diff6<T>(u0, b1, i1, n1, s1) - diff6<T>(u1, b0, i0, n0, s0);
+      const T wx = diff6<T>(u2, b1, i1, n1, s1) - diff6<T>(u1, b2, i2, n2, 1);
+      const T wy = diff6<T>(u0, b2, i2, n2, 1) - diff6<T>(u2, b0, i0, n0, s0);
+      acc = double(wz * wz) + double(wx * wx + wy * wy);
+    }
+  }
+  // deterministic reduction; the single sum lands in the enstrophy slot
+  lb::reduce_observables<lb::STEP_BLOCK>(acc, 0.0, 0.0, partials, counter, out + LB_OBS_ENSTROPHY, 1);
+}
+
+}  // namespace
+
+extern "C" {
+
+int lb_abi_version(void) { return LB_ABI_VERSION; }
+const char* lb_last_error(void) { return g_err; }
+int lb_stencil_q(int stencil) { return stencil_q(stencil); }
+
+size_t lb_bytes_per_update(const lb_desc* d) {
+  if (!d) return 0;
+  const int q = stencil_q(d->stencil);
+  return q < 0 ? 0 : size_t(2) * q * (d->dtype == LB_F64 ? 8 : 4);
+}
+
+int lb_vector_width(const lb_desc* d, int has_streaming_bits) {
+  Geometry g;
+  if (check_desc(d, &g)) return -1;
+  const unsigned vec = d->dtype == LB_F64 ? 2 : 4;
+  return (!has_streaming_bits && g.nz % vec == 0) ? int(vec) : 1;
+}
+
+int lb_step(const lb_desc* desc, const lb_fields* fields, int n_steps, void* stream) {
+  return step_any(desc, fields, n_steps, true, stream);
+}
+
+int lb_collide(const lb_desc* desc, const void* f_in, void* f_out, const uint8_t* ncm,
+               const lb_boundary* boundaries, int n_boundaries, void* stream) {
+  lb_fields fl{};
+  fl.f = const_cast<void*>(f_in);
+  fl.f_next = f_out;
+  fl.no_collision_mask = ncm;
+  fl.boundaries = boundaries;
+  fl.n_boundaries = n_boundaries;
+  return step_any(desc, &fl, 1, false, stream);
+}
+
+int lb_stream(const lb_desc* desc, const void* f_in, void* f_out, const uint32_t* sbits, void* stream) {
+  if (!desc) return fail(LB_EINVAL, "null descriptor");
+  if (sbits) return fail(LB_EINVAL, "masked lb_stream: pass the masks through lb_step with LB_COLL_NONE");
+  lb_desc d = *desc;
+  d.collision = LB_COLL_NONE;
+  lb_fields fl{};
+  fl.f = const_cast<void*>(f_in);
+  fl.f_next = f_out;
+  return step_any(&d, &fl, 1, true, stream);
+}
+
+int lb_pack_streaming_mask(const lb_desc* desc, const uint8_t* nsm, uint32_t* bits, void* stream) {
+  Geometry g;
+  int rc = check_desc(desc, &g);
+  if (rc) return rc;
+  if (!nsm || !bits) return fail(LB_EINVAL, "null mask pointer");
+  const unsigned block = 256, grid = (g.n_nodes + block - 1) / block;
+  pack_sbits_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(nsm, bits, g.n_nodes, g.q);
+  LB_CUDA(cudaGetLastError());
+  return LB_OK;
+}
+
+size_t lb_obs_scratch_bytes(const lb_desc* desc) {
+  Geometry g;
+  if (check_desc(desc, &g)) return 0;
+  const size_t blocks = (size_t(g.n_nodes) + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK;
+  return 64 + blocks * lb::N_OBS_PART * sizeof(double);
+}
+
+}  // extern "C"
+
+namespace {
+
+template <class S, typename T>
+int moments_typed(const Geometry& g, const void* f, void* rho_out, void* u_out, void* scratch,
+                  double* obs_out, cudaStream_t st) {
+  lb::MomentsParams<T> p{};
+  p.f = static_cast<const T*>(f);
+  p.rho_out = static_cast<T*>(rho_out);
+  p.u_out = static_cast<T*>(u_out);
+  p.n_nodes = g.n_nodes;
+  p.obs_out = obs_out;
+  if (obs_out) {
+    p.obs_counter = static_cast<unsigned*>(scratch);
+    p.obs_partials = reinterpret_cast<double*>(static_cast<char*>(scratch) + 64);
+    LB_CUDA(cudaMemsetAsync(p.obs_counter, 0, 64, st));
+  }
+  cudaError_t e = lb::launch_moments<S, T>(p, st);
+  if (e != cudaSuccess) return fail(LB_ECUDA, "moments kernel launch failed: %s", cudaGetErrorString(e));
+  return LB_OK;
+}
+
+template <typename T>
+int moments_stencil(const lb_desc* d, const Geometry& g, const void* f, void* r, void* u, void* s,
+                    double* o, cudaStream_t st) {
+  switch (d->stencil) {
+    case LB_D2Q9: return moments_typed<lb::D2Q9, T>(g, f, r, u, s, o, st);
+    case LB_D3Q19: return moments_typed<lb::D3Q19, T>(g, f, r, u, s, o, st);
+    case LB_D3Q27: return moments_typed<lb::D3Q27, T>(g, f, r, u, s, o, st);
+  }
+  return fail(LB_EINVAL, "bad stencil");
+}
+
+template <typename T>
+int enstrophy_typed(const lb_desc* d, const Geometry& g, const void* u, void* scratch, double* obs_out,
+                    cudaStream_t st) {
+  unsigned* counter = static_cast<unsigned*>(scratch);
+  double* partials = reinterpret_cast<double*>(static_cast<char*>(scratch) + 64);
+  const unsigned grid = (g.n_nodes + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK;
+  LB_CUDA(cudaMemsetAsync(counter, 0, 64, st));
+  if (g.d == 2)
+    enstrophy_kernel<T, 2><<<grid, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(u), (unsigned)d->dims[0],
+                                                           (unsigned)d->dims[1], 1u, g.n_nodes, partials,
+                                                           counter, obs_out);
+  else
+    enstrophy_kernel<T, 3><<<grid, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(u), (unsigned)d->dims[0],
+                                                           (unsigned)d->dims[1], (unsigned)d->dims[2],
+                                                           g.n_nodes, partials, counter, obs_out);
+  LB_CUDA(cudaGetLastError());
+  return LB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int lb_moments(const lb_desc* desc, const void* f, void* rho_out, void* u_out, void* stream) {
+  Geometry g;
+  int rc = check_desc(desc, &g);
+  if (rc) return rc;
+  if (!f) return fail(LB_EINVAL, "null population buffer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return desc->dtype == LB_F32 ? moments_stencil<float>(desc, g, f, rho_out, u_out, nullptr, nullptr, st)
+                               : moments_stencil<double>(desc, g, f, rho_out, u_out, nullptr, nullptr, st);
+}
+
+int lb_observables(const lb_desc* desc, const void* f, int want_enstrophy, void* u_scratch,
+                   void* obs_scratch, double* obs_out, void* stream) {
+  Geometry g;
+  int rc = check_desc(desc, &g);
+  if (rc) return rc;
+  if (!f || !obs_scratch || !obs_out) return fail(LB_EINVAL, "null pointer");
+  if (want_enstrophy && !u_scratch) return fail(LB_EINVAL, "enstrophy needs u_scratch");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  rc = desc->dtype == LB_F32
+           ? moments_stencil<float>(desc, g, f, nullptr, want_enstrophy ? u_scratch : nullptr, obs_scratch, obs_out, st)
+           : moments_stencil<double>(desc, g, f, nullptr, want_enstrophy ? u_scratch : nullptr, obs_scratch, obs_out, st);
+  if (rc || !want_enstrophy) return rc;
+  return desc->dtype == LB_F32 ? enstrophy_typed<float>(desc, g, u_scratch, obs_scratch, obs_out, st)
+                               : enstrophy_typed<double>(desc, g, u_scratch, obs_scratch, obs_out, st);
+}
+
+int lb_enstrophy(const lb_desc* desc, const void* u, void* obs_scratch, double* obs_out, void* stream) {
+  Geometry g;
+  int rc = check_desc(desc, &g);
+  if (rc) return rc;
+  if (!u || !obs_scratch || !obs_out) return fail(LB_EINVAL, "null pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return desc->dtype == LB_F32 ? enstrophy_typed<float>(desc, g, u, obs_scratch, obs_out, st)
+                               : enstrophy_typed<double>(desc, g, u, obs_scratch, obs_out, st);
+}
+
+}  // extern "C"
+
+// ---- host-buffer entry: H2D -> n steps -> D2H ------------------------------------------
+namespace {
+struct DevBuf {
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+};
+size_t extent(const Geometry& g, const lb_desc* d, const int64_t* stride) {
+  size_t e = 1;
+  for (int a = 0; a < g.d; ++a) e += size_t(d->dims[a] - 1) * size_t(stride[a]);
+  return e;
+}
+}  // namespace
+
+extern "C" int lb_run_host(const lb_desc* desc, void* f_host, const uint8_t* ncm_host,
+                           const uint8_t* nsm_host, const lb_boundary* bnd_host, int n_boundaries,
+                           int n_steps, double* obs_host) {
+  Geometry g;
+  int rc = check_desc(desc, &g);
+  if (rc) return rc;
+  if (!f_host) return fail(LB_EINVAL, "null host buffer");
+  if (n_boundaries < 0 || n_boundaries > LB_MAX_BOUNDARIES) return fail(LB_EINVAL, "n_boundaries = %d", n_boundaries);
+  const size_t esz = desc->dtype == LB_F64 ? 8 : 4;
+  const size_t fbytes = size_t(g.q) * g.n_nodes * esz;
+  DevBuf fa, fb, ncm, nsm, bits, scratch, obs, brho[LB_MAX_BOUNDARIES], bu[LB_MAX_BOUNDARIES];
+  cudaStream_t st = nullptr;
+  LB_CUDA(cudaMalloc(&fa.p, fbytes));
+  LB_CUDA(cudaMalloc(&fb.p, fbytes));
+  LB_CUDA(cudaMemcpyAsync(fa.p, f_host, fbytes, cudaMemcpyHostToDevice, st));
+  lb_fields fl{};
+  fl.f = fa.p;
+  fl.f_next = fb.p;
+  if (ncm_host) {
+    LB_CUDA(cudaMalloc(&ncm.p, g.n_nodes));
+    LB_CUDA(cudaMemcpyAsync(ncm.p, ncm_host, g.n_nodes, cudaMemcpyHostToDevice, st));
+    fl.no_collision_mask = static_cast<const uint8_t*>(ncm.p);
+  }
+  if (nsm_host) {
+    bool any = false;
+    for (size_t i = 0; i < size_t(g.q) * g.n_nodes && !any; ++i) any = nsm_host[i] == 1;
+    if (any) {
+      LB_CUDA(cudaMalloc(&nsm.p, size_t(g.q) * g.n_nodes));
+      LB_CUDA(cudaMalloc(&bits.p, size_t(g.n_nodes) * 4));
+      LB_CUDA(cudaMemcpyAsync(nsm.p, nsm_host, size_t(g.q) * g.n_nodes, cudaMemcpyHostToDevice, st));
+      rc = lb_pack_streaming_mask(desc, static_cast<const uint8_t*>(nsm.p), static_cast<uint32_t*>(bits.p), st);
+      if (rc) return rc;
+      fl.streaming_bits = static_cast<const uint32_t*>(bits.p);
+    }
+  }
+  std::vector<lb_boundary> bd(bnd_host, bnd_host + n_boundaries);
+  for (int i = 0; i < n_boundaries; ++i) {
+    if (bd[i].kind != LB_BND_EQUILIBRIUM) continue;
+    if (!bd[i].rho || !bd[i].u) return fail(LB_EINVAL, "boundary %d: equilibrium boundary needs rho and u", i);
+    const size_t nr = extent(g, desc, bd[i].rho_stride) * esz;
+    const size_t nu = (extent(g, desc, bd[i].u_stride) + size_t(g.d - 1) * size_t(bd[i].u_comp_stride)) * esz;
+    LB_CUDA(cudaMalloc(&brho[i].p, nr));
+    LB_CUDA(cudaMalloc(&bu[i].p, nu));
+    LB_CUDA(cudaMemcpyAsync(brho[i].p, bd[i].rho, nr, cudaMemcpyHostToDevice, st));
+    LB_CUDA(cudaMemcpyAsync(bu[i].p, bd[i].u, nu, cudaMemcpyHostToDevice, st));
+    bd[i].rho = brho[i].p;
+    bd[i].u = bu[i].p;
+  }
+  fl.boundaries = bd.data();
+  fl.n_boundaries = n_boundaries;
+  rc = lb_step(desc, &fl, n_steps, st);
+  if (rc) return rc;
+  void* result = (n_steps & 1) ? fb.p : fa.p;
+  if (obs_host) {
+    LB_CUDA(cudaMalloc(&scratch.p, lb_obs_scratch_bytes(desc)));
+    LB_CUDA(cudaMalloc(&obs.p, LB_OBS_COUNT * sizeof(double)));
+    LB_CUDA(cudaMemsetAsync(obs.p, 0, LB_OBS_COUNT * sizeof(double), st));
+    rc = lb_observables(desc, result, 0, nullptr, scratch.p, static_cast<double*>(obs.p), st);
+    if (rc) return rc;
+    LB_CUDA(cudaMemcpyAsync(obs_host, obs.p, LB_OBS_COUNT * sizeof(double), cudaMemcpyDeviceToHost, st));
+  }
+  LB_CUDA(cudaMemcpyAsync(f_host, result, fbytes, cudaMemcpyDeviceToHost, st));
+  LB_CUDA(cudaStreamSynchronize(st));
+  return LB_OK;
+}

@@ -1,0 +1,457 @@
+// Fused collide -> boundary -> stream kernel for sm_100a (B200).
+//
+// One launch = one reference time step (reference/lettuce/_simulation.py:92-96):
+//   f*      = where(ncm == 0, collision(f), f); f* = where(ncm == i, boundary_i(f*), f*)
+//   f'[q,x] = nsm[q,x] ? f*[q,x] : f*[q, x - e_q]          (periodic, _simulation.py:160-175)
+//
+// Scheme.  "Aligned push": a thread owns V consecutive nodes along the contiguous z axis
+// (V = 16 bytes / sizeof(T)), loads its Q x V populations with 128-bit loads from the node's
+// own (aligned) location, does moments / equilibrium / relaxation in registers, and writes
+// every population to its destination line (x + ex, y + ey) -- a whole-line offset, so still
+// 16-byte aligned.  The +-1 shift along z is done in registers: each lane takes one element
+// from its neighbour lane with a warp shuffle, so the z-shifted populations also leave as
+// aligned 128-bit stores.  Only the two elements per warp that cross a warp/line edge are
+// written as 4(8)-byte scalars (they merge with the neighbouring vector store in L2).
+// Every load and store instruction is therefore fully coalesced and the kernel moves
+// exactly 2*Q*sizeof(T) bytes per node through HBM: the roofline figure of BASELINE.md.
+// The state stays in the reference's canonical form (post-streaming f_t) after every launch.
+//
+// With a packed streaming mask (MODE 2) the kernel runs one node per thread and checks the
+// destination's mask bit before each store; the destination node itself writes its kept
+// value, so every (q, node) of the output is written exactly once (no race, unlike the
+// reference's generated kernel, SURVEY section 3.3 "semantic trap").
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "lb_physics.cuh"
+
+namespace lb {
+
+constexpr int MAX_BND = 8;
+constexpr int STEP_BLOCK = 128;
+constexpr int N_OBS_PART = 3;  // energy, max|u|^2, mass
+
+enum { BND_BOUNCE_BACK = 1, BND_EQUILIBRIUM = 2 };
+enum { MODE_PLAIN = 0, MODE_NCM = 1, MODE_NCM_SBITS = 2 };
+
+template <typename T>
+struct BoundaryDev {
+  int kind;
+  const T* rho;
+  const T* u;
+  long long rs[3];  // strides (elements) along kernel axes X, Y, Z
+  long long us[3];
+  long long ucs;    // stride between velocity components (lattice order)
+};
+
+template <typename T>
+struct StepParams {
+  const T* f_in;
+  T* f_out;
+  const uint8_t* ncm;
+  const uint32_t* sbits;
+  unsigned nx, ny, nz, nzv;    // kernel-axis sizes; nzv = nz / V
+  unsigned n_nodes;            // nx * ny * nz  (< 2^31, checked by the host)
+  unsigned n_threads;          // nx * ny * nzv
+  CollisionParams<T> cp;
+  int n_bnd;
+  BoundaryDev<T> bnd[MAX_BND];
+  double* obs_partials;        // [gridDim.x][N_OBS_PART]
+  unsigned* obs_counter;
+  double* obs_out;             // [LB_OBS_COUNT]
+  T* u_out;                    // [D][n_nodes] or nullptr
+};
+
+template <typename T, int V>
+struct alignas(sizeof(T) * V) Vec {
+  T v[V];
+};
+
+template <typename T, int V>
+__device__ __forceinline__ Vec<T, V> ld_vec(const T* p) {
+  return *reinterpret_cast<const Vec<T, V>*>(p);
+}
+template <typename T, int V>
+__device__ __forceinline__ void st_vec(T* p, const Vec<T, V>& v) {
+  *reinterpret_cast<Vec<T, V>*>(p) = v;
+}
+
+template <int V>
+__device__ __forceinline__ uint32_t ld_mask(const uint8_t* p) {
+  if constexpr (V == 4) return *reinterpret_cast<const uint32_t*>(p);
+  else if constexpr (V == 2) return *reinterpret_cast<const uint16_t*>(p);
+  else return *p;
+}
+
+// Deterministic block reduction (sum, max, sum) followed by the "last block finishes"
+// pattern: no atomics on the values, fixed summation order -> bitwise reproducible.
+template <int BLOCK>
+__device__ __forceinline__ void reduce_observables(double e, double m2, double mass,
+                                                   double* partials, unsigned* counter,
+                                                   double* out, int n_out = N_OBS_PART) {
+  __shared__ double sm[N_OBS_PART][BLOCK / 32];
+  __shared__ bool is_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    e += __shfl_down_sync(0xffffffffu, e, o);
+    m2 = fmax(m2, __shfl_down_sync(0xffffffffu, m2, o));
+    mass += __shfl_down_sync(0xffffffffu, mass, o);
+  }
+  if (lane == 0) { sm[0][warp] = e; sm[1][warp] = m2; sm[2][warp] = mass; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = sm[0][0], b = sm[1][0], c = sm[2][0];
+#pragma unroll
+    for (int w = 1; w < BLOCK / 32; ++w) { a += sm[0][w]; b = fmax(b, sm[1][w]); c += sm[2][w]; }
+    partials[blockIdx.x * N_OBS_PART + 0] = a;
+    partials[blockIdx.x * N_OBS_PART + 1] = b;
+    partials[blockIdx.x * N_OBS_PART + 2] = c;
+    __threadfence();
+    const unsigned prev = atomicAdd(counter, 1u);
+    is_last = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  double a = 0.0, b = 0.0, c = 0.0;
+  for (unsigned i = threadIdx.x; i < gridDim.x; i += BLOCK) {
+    a += __ldcg(&partials[i * N_OBS_PART + 0]);
+    b = fmax(b, __ldcg(&partials[i * N_OBS_PART + 1]));
+    c += __ldcg(&partials[i * N_OBS_PART + 2]);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_down_sync(0xffffffffu, a, o);
+    b = fmax(b, __shfl_down_sync(0xffffffffu, b, o));
+    c += __shfl_down_sync(0xffffffffu, c, o);
+  }
+  __syncthreads();
+  if (lane == 0) { sm[0][warp] = a; sm[1][warp] = b; sm[2][warp] = c; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    a = sm[0][0]; b = sm[1][0]; c = sm[2][0];
+#pragma unroll
+    for (int w = 1; w < BLOCK / 32; ++w) { a += sm[0][w]; b = fmax(b, sm[1][w]); c += sm[2][w]; }
+    out[0] = a;                  // LB_OBS_ENERGY (or the single sum when n_out == 1)
+    if (n_out > 1) out[1] = b;   // LB_OBS_MAXU2
+    if (n_out > 2) out[2] = c;   // LB_OBS_MASS
+    *counter = 0u;
+  }
+}
+
+template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM>
+__global__ void __launch_bounds__(STEP_BLOCK)
+step_kernel(const __grid_constant__ StepParams<T> p) {
+  static_assert(MODE != MODE_NCM_SBITS || V == 1, "masked streaming runs one node per thread");
+  constexpr int Q = S::Q;
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned tid = blockIdx.x * STEP_BLOCK + threadIdx.x;
+  const bool active = tid < p.n_threads;
+  const unsigned t = active ? tid : p.n_threads - 1u;  // clamp: keeps address math valid
+  const unsigned nzv = p.nzv, nz = p.nz, ny = p.ny, nx = p.nx;
+  const unsigned line = t / nzv;
+  const unsigned zv = t - line * nzv;
+  const unsigned x = line / ny;
+  const unsigned y = line - x * ny;
+  const unsigned z0 = zv * V;
+  const unsigned node = line * nz + z0;
+  const size_t N = p.n_nodes;
+
+  // ---- load: Q aligned vector loads ------------------------------------------------
+  T f[Q][V];
+  {
+    const T* src = p.f_in + node;
+    static_for<Q>([&](auto qc) {
+      constexpr int q = decltype(qc)::value;
+      const Vec<T, V> v = ld_vec<T, V>(src + q * N);
+#pragma unroll
+      for (int k = 0; k < V; ++k) f[q][k] = v.v[k];
+    });
+  }
+  uint32_t mword = 0;
+  if constexpr (MODE != MODE_PLAIN) mword = ld_mask<V>(p.ncm + node);
+
+  double acc_e = 0.0, acc_mass = 0.0;
+  T acc_m2 = T(0);
+  T uo[3][V];
+
+  // ---- collide / boundaries, node by node, all in registers -------------------------
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    T g[Q];
+    static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
+    const unsigned m = (MODE == MODE_PLAIN) ? 0u : ((mword >> (8 * k)) & 0xffu);
+    T rho = T(0), u[3] = {T(0), T(0), T(0)};
+    if (OBS || (COLL != COLL_NONE && m == 0)) moments<S, T>(g, rho, u);
+    if constexpr (OBS) {
+      const T u2 = u[0] * u[0] + u[1] * u[1] + u[2] * u[2];
+      acc_e += double(T(0.5) * u2);
+      acc_m2 = max(acc_m2, u2);
+      acc_mass += double(rho);
+      uo[0][k] = u[0]; uo[1][k] = u[1]; uo[2][k] = u[2];
+    }
+    if (m == 0) {
+      collide_node<S, T, COLL>(g, rho, u, p.cp);
+    } else if constexpr (MODE != MODE_PLAIN) {
+      if (m <= unsigned(p.n_bnd)) {
+        const BoundaryDev<T>& b = p.bnd[m - 1];
+        if (b.kind == BND_BOUNCE_BACK) {
+          bounce_back_node<S, T>(g);
+        } else if (b.kind == BND_EQUILIBRIUM) {
+          // equilibrium_boundary_pu.py:27-32 (rho, u already in lattice units)
+          const long long z = z0 + k;
+          const T rb = b.rho[x * b.rs[0] + y * b.rs[1] + z * b.rs[2]];
+          T ub[3] = {T(0), T(0), T(0)};
+          const long long off = x * b.us[0] + y * b.us[1] + z * b.us[2];
+#pragma unroll
+          for (int c = 0; c < S::D; ++c) ub[S::axis(c)] = b.u[c * b.ucs + off];
+          equilibrium<S, T>(rb, ub, g);
+        }
+      }
+    }
+    static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
+  }
+
+  if constexpr (OBS) {
+    if (p.u_out != nullptr && active) {
+#pragma unroll
+      for (int c = 0; c < S::D; ++c) {
+        Vec<T, V> v;
+#pragma unroll
+        for (int k = 0; k < V; ++k) v.v[k] = uo[S::axis(c)][k];
+        st_vec<T, V>(p.u_out + c * N + node, v);
+      }
+    }
+  }
+
+  // ---- stream: push to (x + ex, y + ey, z + ez), periodic -----------------------------
+  if constexpr (!STREAM) {
+    if (active) {
+      static_for<Q>([&](auto qc) {
+        constexpr int q = decltype(qc)::value;
+        Vec<T, V> v;
+#pragma unroll
+        for (int k = 0; k < V; ++k) v.v[k] = f[q][k];
+        st_vec<T, V>(p.f_out + q * N + node, v);
+      });
+    }
+  } else {
+    const unsigned xp = (x + 1 == nx) ? 0u : x + 1, xm = (x == 0) ? nx - 1 : x - 1;
+    const unsigned yp = (y + 1 == ny) ? 0u : y + 1, ym = (y == 0) ? ny - 1 : y - 1;
+    const bool first_in_line = (zv == 0), last_in_line = (zv == nzv - 1);
+    const bool has_left = (lane > 0) && !first_in_line;
+    const bool has_right = (lane < 31) && !last_in_line;
+    uint32_t own_bits = 0;
+    if constexpr (MODE == MODE_NCM_SBITS) own_bits = p.sbits[node];
+
+    static_for<Q>([&](auto qc) {
+      constexpr int q = decltype(qc)::value;
+      constexpr int ex = S::e(q, 0), ey = S::e(q, 1), ez = S::e(q, 2);
+      const unsigned xd = (ex == 0) ? x : (ex > 0 ? xp : xm);
+      const unsigned yd = (ey == 0) ? y : (ey > 0 ? yp : ym);
+      const unsigned dline = (xd * ny + yd) * nz;
+      T* dst = p.f_out + q * N + dline;  // start of the destination line
+
+      if constexpr (MODE == MODE_NCM_SBITS) {
+        // destination-masked streaming, one node per thread
+        const unsigned zd = (ez == 0) ? z0 : (ez > 0 ? (z0 + 1 == nz ? 0u : z0 + 1)
+                                                     : (z0 == 0 ? nz - 1 : z0 - 1));
+        if (active) {
+          if constexpr (q == 0) {
+            dst[zd] = f[q][0];
+          } else {
+            const uint32_t dbits = p.sbits[dline + zd];
+            if (!((dbits >> q) & 1u)) dst[zd] = f[q][0];
+            if ((own_bits >> q) & 1u) p.f_out[q * N + node] = f[q][0];
+          }
+        }
+      } else if constexpr (ez == 0) {
+        if (active) {
+          Vec<T, V> v;
+#pragma unroll
+          for (int k = 0; k < V; ++k) v.v[k] = f[q][k];
+          st_vec<T, V>(dst + z0, v);
+        }
+      } else if constexpr (V == 1) {
+        const unsigned zd = (ez > 0) ? (z0 + 1 == nz ? 0u : z0 + 1) : (z0 == 0 ? nz - 1 : z0 - 1);
+        if (active) dst[zd] = f[q][0];
+      } else if constexpr (ez > 0) {
+        // destination z0+k takes the source value of z0+k-1: element 0 comes from the left lane
+        const T up = __shfl_up_sync(0xffffffffu, f[q][V - 1], 1);
+        if (active) {
+          if (has_left) {
+            Vec<T, V> v;
+            v.v[0] = up;
+#pragma unroll
+            for (int k = 1; k < V; ++k) v.v[k] = f[q][k - 1];
+            st_vec<T, V>(dst + z0, v);
+          } else {
+#pragma unroll
+            for (int k = 1; k < V; ++k) dst[z0 + k] = f[q][k - 1];
+          }
+          if (lane == 31 || last_in_line) dst[last_in_line ? 0u : z0 + V] = f[q][V - 1];
+        }
+      } else {
+        // ez < 0: destination z0+k takes the source value of z0+k+1
+        const T dn = __shfl_down_sync(0xffffffffu, f[q][0], 1);
+        if (active) {
+          if (has_right) {
+            Vec<T, V> v;
+#pragma unroll
+            for (int k = 0; k < V - 1; ++k) v.v[k] = f[q][k + 1];
+            v.v[V - 1] = dn;
+            st_vec<T, V>(dst + z0, v);
+          } else {
+#pragma unroll
+            for (int k = 0; k < V - 1; ++k) dst[z0 + k] = f[q][k + 1];
+          }
+          if (lane == 0 || first_in_line) dst[first_in_line ? nz - 1 : z0 - 1] = f[q][0];
+        }
+      }
+    });
+  }
+
+  if constexpr (OBS) {
+    if (!active) { acc_e = 0.0; acc_m2 = T(0); acc_mass = 0.0; }
+    reduce_observables<STEP_BLOCK>(acc_e, double(acc_m2), acc_mass, p.obs_partials,
+                                   p.obs_counter, p.obs_out);
+  }
+}
+
+// --------------------------------------------------------------------------------------
+// moments / standalone observables: rho [N], u [D][N] and/or the reductions of a state
+// (reference/lettuce/_flow.py:136-172, observable_reporter.py:27-42)
+// --------------------------------------------------------------------------------------
+template <typename T>
+struct MomentsParams {
+  const T* f;
+  T* rho_out;   // [n_nodes] or nullptr
+  T* u_out;     // [D][n_nodes] or nullptr
+  unsigned n_nodes;
+  double* obs_partials;
+  unsigned* obs_counter;
+  double* obs_out;  // nullptr: no reduction
+};
+
+template <class S, typename T, bool OBS>
+__global__ void __launch_bounds__(STEP_BLOCK)
+moments_kernel(const __grid_constant__ MomentsParams<T> p) {
+  const unsigned tid = blockIdx.x * STEP_BLOCK + threadIdx.x;
+  const bool active = tid < p.n_nodes;
+  const unsigned node = active ? tid : p.n_nodes - 1u;
+  const size_t N = p.n_nodes;
+  T g[S::Q];
+  static_for<S::Q>([&](auto qc) {
+    constexpr int q = decltype(qc)::value;
+    g[q] = p.f[q * N + node];
+  });
+  T rho, u[3];
+  moments<S, T>(g, rho, u);
+  if (active) {
+    if (p.rho_out) p.rho_out[node] = rho;
+    if (p.u_out) {
+#pragma unroll
+      for (int c = 0; c < S::D; ++c) p.u_out[c * N + node] = u[S::axis(c)];
+    }
+  }
+  if constexpr (OBS) {
+    const T u2 = u[0] * u[0] + u[1] * u[1] + u[2] * u[2];
+    double e = active ? double(T(0.5) * u2) : 0.0;
+    double m2 = active ? double(u2) : 0.0;
+    double mass = active ? double(rho) : 0.0;
+    reduce_observables<STEP_BLOCK>(e, m2, mass, p.obs_partials, p.obs_counter, p.obs_out);
+  }
+}
+
+template <class S, typename T>
+cudaError_t launch_moments(const MomentsParams<T>& p, cudaStream_t st);
+
+template <class S, typename T>
+cudaError_t launch_moments_impl(const MomentsParams<T>& p, cudaStream_t st) {
+  const unsigned grid = (p.n_nodes + STEP_BLOCK - 1) / STEP_BLOCK;
+  if (p.obs_out) moments_kernel<S, T, true><<<grid, STEP_BLOCK, 0, st>>>(p);
+  else moments_kernel<S, T, false><<<grid, STEP_BLOCK, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
+// --------------------------------------------------------------------------------------
+// host-side dispatch (runtime descriptor -> template instantiation), one per (stencil, T)
+// --------------------------------------------------------------------------------------
+struct StepConfig {
+  int vec;        // 1 or 16/sizeof(T)
+  int collision;  // COLL_*
+  int mode;       // MODE_*
+  bool obs;
+  bool stream;
+};
+
+template <class S, typename T>
+cudaError_t launch_step(const StepConfig& c, const StepParams<T>& p, cudaStream_t st);
+
+template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM>
+cudaError_t launch_one(const StepParams<T>& p, cudaStream_t st) {
+  const unsigned grid = (p.n_threads + STEP_BLOCK - 1) / STEP_BLOCK;
+  step_kernel<S, T, V, COLL, MODE, OBS, STREAM><<<grid, STEP_BLOCK, 0, st>>>(p);
+  return cudaGetLastError();
+}
+
+template <class S, typename T, int V, int COLL, int MODE>
+cudaError_t launch_mode(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+  if (!c.stream) {
+    if constexpr (V == 1 && MODE != MODE_NCM_SBITS)
+      return launch_one<S, T, V, COLL, MODE, false, false>(p, st);
+    else
+      return cudaErrorInvalidValue;
+  }
+  if (c.obs) return launch_one<S, T, V, COLL, MODE, true, true>(p, st);
+  return launch_one<S, T, V, COLL, MODE, false, true>(p, st);
+}
+
+template <class S, typename T, int V, int COLL>
+cudaError_t launch_coll(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+  switch (c.mode) {
+    case MODE_PLAIN: return launch_mode<S, T, V, COLL, MODE_PLAIN>(c, p, st);
+    case MODE_NCM: return launch_mode<S, T, V, COLL, MODE_NCM>(c, p, st);
+    case MODE_NCM_SBITS:
+      if constexpr (V == 1) return launch_mode<S, T, V, COLL, MODE_NCM_SBITS>(c, p, st);
+      else return cudaErrorInvalidValue;
+  }
+  return cudaErrorInvalidValue;
+}
+
+template <class S, typename T, int V>
+cudaError_t launch_vec(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+  switch (c.collision) {
+    case COLL_NONE: return launch_coll<S, T, V, COLL_NONE>(c, p, st);
+    case COLL_BGK: return launch_coll<S, T, V, COLL_BGK>(c, p, st);
+    case COLL_TRT: return launch_coll<S, T, V, COLL_TRT>(c, p, st);
+    case COLL_KBC:
+      if constexpr (S::ID != 1) return launch_coll<S, T, V, COLL_KBC>(c, p, st);
+      else return cudaErrorNotSupported;
+  }
+  return cudaErrorInvalidValue;
+}
+
+template <class S, typename T>
+cudaError_t launch_step_impl(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+  constexpr int VEC = 16 / sizeof(T);
+  if (c.vec == 1) return launch_vec<S, T, 1>(c, p, st);
+  if (c.vec == VEC) return launch_vec<S, T, VEC>(c, p, st);
+  return cudaErrorInvalidValue;
+}
+
+#define LB_INSTANTIATE(S, T)                                                              \
+  template <>                                                                             \
+  cudaError_t lb::launch_step<S, T>(const StepConfig& c, const StepParams<T>& p,          \
+                                    cudaStream_t st) {                                    \
+    return launch_step_impl<S, T>(c, p, st);                                              \
+  }                                                                                       \
+  template <>                                                                             \
+  cudaError_t lb::launch_moments<S, T>(const MomentsParams<T>& p, cudaStream_t st) {      \
+    return launch_moments_impl<S, T>(p, st);                                              \
+  }
+
+}  // namespace lb

@@ -1,0 +1,205 @@
+// Per-node physics in registers: moments, quadratic equilibrium, BGK / TRT / KBC relaxation,
+// bounce-back and equilibrium boundaries.  One call handles ONE lattice node whose Q
+// populations live in a register array.  All loops are unrolled at compile time so the
+// stencil constants fold into immediates.
+//
+// Arithmetic follows the reference's torch path op for op where it matters for parity
+// (SURVEY appendix A.7-A.11); file:line citations are relative to the reference checkout.
+#pragma once
+#include "lb_stencil.cuh"
+
+namespace lb {
+
+template <typename T>
+struct CollisionParams {
+  T omega;        // BGK: 1/tau (bgk_collision.py:22: `1.0 / self.tau` is a double, demoted to dtype)
+  T inv_2tau_p;   // TRT: 1/(2 tau_plus)   (trt_collision.py:20-22)
+  T inv_2tau_m;   // TRT: 1/(2 tau_minus)  (trt_collision.py:23-25)
+  T beta;         // KBC: 1/(2 tau)        (kbc_collision.py:98-99)
+  T inv_beta;     // KBC: 1/beta as the reference evaluates `1. / self.beta` (:153)
+};
+
+// rho = sum_q f_q (_flow.py:136-138), j = sum_q e_q f_q (:152-155), u = j / rho (:161-162)
+template <class S, typename T>
+__device__ __forceinline__ void moments(const T (&f)[S::Q], T& rho, T (&u)[3]) {
+  T r = f[0];
+  T jx = T(0), jy = T(0), jz = T(0);
+  static_for<S::Q>([&](auto qc) {
+    constexpr int q = decltype(qc)::value;
+    if constexpr (q > 0) r += f[q];
+    if constexpr (S::e(q, 0) == 1) jx += f[q];
+    if constexpr (S::e(q, 0) == -1) jx -= f[q];
+    if constexpr (S::e(q, 1) == 1) jy += f[q];
+    if constexpr (S::e(q, 1) == -1) jy -= f[q];
+    if constexpr (S::e(q, 2) == 1) jz += f[q];
+    if constexpr (S::e(q, 2) == -1) jz -= f[q];
+  });
+  rho = r;
+  // true division, as torch does
+  if constexpr (S::D == 3) u[0] = jx / r; else u[0] = T(0);  // 2-D runs with X == 1
+  u[1] = jy / r;
+  u[2] = jz / r;
+}
+
+// quadratic_equilibrium.py:11-25:
+//   feq_q = w_q * (rho * ((2 exu - uxu) / (2 cs^2) + 0.5 (exu / cs^2)^2 + 1))
+// Division by the two constants is done as multiplication by their (double-rounded-to-T)
+// reciprocals: <= 1 ulp away from the reference's division, well inside the parity budget.
+template <class S, typename T>
+__device__ __forceinline__ void equilibrium(T rho, const T (&u)[3], T (&feq)[S::Q]) {
+  constexpr T inv_cs2 = T(1.0 / LB_CS2);
+  constexpr T inv_2cs2 = T(1.0 / (2.0 * LB_CS2));
+  const T uxu = u[0] * u[0] + u[1] * u[1] + u[2] * u[2];
+  static_for<S::Q>([&](auto qc) {
+    constexpr int q = decltype(qc)::value;
+    T exu = T(0);
+    if constexpr (S::e(q, 0) == 1) exu += u[0];
+    if constexpr (S::e(q, 0) == -1) exu -= u[0];
+    if constexpr (S::e(q, 1) == 1) exu += u[1];
+    if constexpr (S::e(q, 1) == -1) exu -= u[1];
+    if constexpr (S::e(q, 2) == 1) exu += u[2];
+    if constexpr (S::e(q, 2) == -1) exu -= u[2];
+    const T a = exu * inv_cs2;
+    const T t = (T(2) * exu - uxu) * inv_2cs2 + T(0.5) * (a * a) + T(1);
+    feq[q] = T(S::w(q)) * (rho * t);
+  });
+}
+
+// ---------------------------------------------------------------------------------------
+// KBC helper: the `s` part of the moment representation (kbc_collision.py:25-94).
+// The reference builds all 27 (9) raw moments with an einsum; only rho and the six (three)
+// second moments enter s, so only those are formed here.
+// ---------------------------------------------------------------------------------------
+template <class S, typename T>
+__device__ __forceinline__ void kbc_s(const T (&g)[S::Q], T (&s)[S::Q]) {
+  T r = T(0), mxx = T(0), myy = T(0), mzz = T(0), mxy = T(0), mxz = T(0), myz = T(0);
+  static_for<S::Q>([&](auto qc) {
+    constexpr int q = decltype(qc)::value;
+    // lattice axes (x, y[, z]) -> kernel axes
+    constexpr int ex = S::e(q, S::axis(0));
+    constexpr int ey = S::e(q, S::axis(1));
+    constexpr int ez = (S::D == 3) ? S::e(q, S::axis(S::D == 3 ? 2 : 0)) : 0;
+    r += g[q];
+    if constexpr (ex * ex == 1) mxx += g[q];
+    if constexpr (ey * ey == 1) myy += g[q];
+    if constexpr (ez * ez == 1) mzz += g[q];
+    if constexpr (ex * ey == 1) mxy += g[q];
+    if constexpr (ex * ey == -1) mxy -= g[q];
+    if constexpr (ex * ez == 1) mxz += g[q];
+    if constexpr (ex * ez == -1) mxz -= g[q];
+    if constexpr (ey * ez == 1) myz += g[q];
+    if constexpr (ey * ez == -1) myz -= g[q];
+  });
+  // m = m / rho ; m[0,0,0] = rho   (kbc_collision.py:27-30, 36-39)
+  mxx /= r; myy /= r; mzz /= r; mxy /= r; mxz /= r; myz /= r;
+  static_for<S::Q>([&](auto qc) { s[decltype(qc)::value] = T(0); });
+  if constexpr (S::D == 3) {
+    // kbc_collision.py:47-72
+    const T Tr = mxx + myy + mzz;
+    const T Nxz = mxx - mzz;
+    const T Nyz = myy - mzz;
+    const T sixth = T(1. / 6.), quarter = T(1. / 4);
+    s[0] = r * -Tr;
+    s[1] = sixth * r * (T(2) * Nxz - Nyz + Tr);
+    s[2] = s[1];
+    s[3] = sixth * r * (T(2) * Nyz - Nxz + Tr);
+    s[4] = s[3];
+    s[5] = sixth * r * (-Nxz - Nyz + Tr);
+    s[6] = s[5];
+    s[7] = quarter * r * myz;
+    s[8] = s[7];
+    s[9] = -quarter * r * myz;
+    s[10] = s[9];
+    s[11] = quarter * r * mxz;
+    s[12] = s[11];
+    s[13] = -quarter * r * mxz;
+    s[14] = s[13];
+    s[15] = quarter * r * mxy;
+    s[16] = s[15];
+    s[17] = -quarter * r * mxy;
+    s[18] = s[17];
+  } else {
+    // kbc_collision.py:79-92
+    const T Tr = mxx + myy;
+    const T N = mxx - myy;
+    s[0] = r * -Tr;
+    s[1] = T(0.5) * r * (T(0.5) * (Tr + N));
+    s[2] = T(0.5) * r * (T(0.5) * (Tr - N));
+    s[3] = s[1];
+    s[4] = s[2];
+    s[5] = T(0.25) * r * mxy;
+    s[6] = -s[5];
+    s[7] = s[5];
+    s[8] = -s[7];
+  }
+}
+
+enum { COLL_NONE = 0, COLL_BGK = 1, COLL_TRT = 2, COLL_KBC = 3 };
+
+// f <- collision(f); rho, u are the moments of the incoming f (already computed).
+template <class S, typename T, int COLL>
+__device__ __forceinline__ void collide_node(T (&f)[S::Q], T rho, const T (&u)[3],
+                                             const CollisionParams<T>& cp) {
+  if constexpr (COLL == COLL_NONE) {
+    return;  // no_collision.py:9-11
+  } else {
+    T feq[S::Q];
+    equilibrium<S, T>(rho, u, feq);
+    if constexpr (COLL == COLL_BGK) {
+      // bgk_collision.py:22: f - 1.0/tau * (f - feq)
+      static_for<S::Q>([&](auto qc) {
+        constexpr int q = decltype(qc)::value;
+        f[q] = f[q] - cp.omega * (f[q] - feq[q]);
+      });
+    } else if constexpr (COLL == COLL_TRT) {
+      // trt_collision.py:20-26
+      T out[S::Q];
+      static_for<S::Q>([&](auto qc) {
+        constexpr int q = decltype(qc)::value;
+        constexpr int o = S::opp(q);
+        T d = ((f[q] + f[o]) - (feq[q] + feq[o])) * cp.inv_2tau_p;
+        d += ((f[q] - f[o]) - (feq[q] - feq[o])) * cp.inv_2tau_m;
+        out[q] = f[q] - d;
+      });
+      static_for<S::Q>([&](auto qc) { f[decltype(qc)::value] = out[decltype(qc)::value]; });
+    } else {
+      // kbc_collision.py:131-158
+      static_assert(S::ID != 1, "KBC is defined for D2Q9 and D3Q27 only (kbc_collision.py:101,115)");
+      T ds[S::Q], se[S::Q];
+      kbc_s<S, T>(f, ds);
+      kbc_s<S, T>(feq, se);
+      T sum_s = T(0), sum_h = T(0);
+      T dh[S::Q];
+      static_for<S::Q>([&](auto qc) {
+        constexpr int q = decltype(qc)::value;
+        ds[q] = ds[q] - se[q];
+        dh[q] = f[q] - feq[q] - ds[q];
+        sum_s += ds[q] * dh[q] / feq[q];
+        sum_h += dh[q] * dh[q] / feq[q];
+      });
+      T gamma = cp.inv_beta - (T(2) - cp.inv_beta) * sum_s / sum_h;
+      if (gamma < T(1E-15)) gamma = T(2);   // :154
+      if (gamma != gamma) gamma = T(2);     // NaN guard :156
+      static_for<S::Q>([&](auto qc) {
+        constexpr int q = decltype(qc)::value;
+        f[q] = f[q] - cp.beta * (T(2) * ds[q] + gamma * dh[q]);
+      });
+    }
+  }
+}
+
+// bounce_back_boundary.py:17-18: f <- f[opposite]
+template <class S, typename T>
+__device__ __forceinline__ void bounce_back_node(T (&f)[S::Q]) {
+  static_for<S::Q>([&](auto qc) {
+    constexpr int q = decltype(qc)::value;
+    constexpr int o = S::opp(q);
+    if constexpr (q < o) {
+      const T t = f[q];
+      f[q] = f[o];
+      f[o] = t;
+    }
+  });
+}
+
+}  // namespace lb

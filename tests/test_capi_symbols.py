@@ -1,0 +1,78 @@
+"""CPU-side checks of the C-ABI library: it loads, exports every symbol include/*.h declares,
+and validates descriptors without touching a GPU."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    names = []
+    for fn in os.listdir(os.path.join(ROOT, "include")):
+        if fn.endswith(".h"):
+            text = open(os.path.join(ROOT, "include", fn)).read()
+            names += re.findall(r"^LB_API\s+[\w\s\*]+?\b(lb_\w+)\s*\(", text, flags=re.M)
+    return sorted(set(names))
+
+
+def test_header_declares_the_binding_table():
+    from lettuce_b200 import _native as nat
+    assert declared_symbols() == sorted(nat.EXPORTED_SYMBOLS)
+
+
+def test_library_exports_every_declared_symbol():
+    from lettuce_b200 import _native as nat
+    assert os.path.exists(nat.LIB_PATH), "build the library first: python -c 'import __graft_entry__ as g; g.build()'"
+    L = C.CDLL(nat.LIB_PATH)
+    for name in declared_symbols():
+        assert hasattr(L, name), name
+    assert nat.lib().lb_abi_version() == nat.ABI_VERSION
+
+
+def test_descriptor_validation_needs_no_gpu():
+    from lettuce_b200 import _native as nat
+    import torch
+    L = nat.lib()
+    assert [L.lb_stencil_q(i) for i in range(4)] == [9, 19, 27, -1]
+    d = nat.make_desc("D3Q19", torch.float32, [256, 256, 256], nat.LB_COLL_BGK, 0.6)
+    assert L.lb_bytes_per_update(d) == 152            # 2 * Q * sizeof(float), BASELINE.md section 3
+    assert L.lb_vector_width(d, 0) == 4 and L.lb_vector_width(d, 1) == 1
+    d64 = nat.make_desc("D2Q9", torch.float64, [256, 256], nat.LB_COLL_BGK, 0.6)
+    assert L.lb_bytes_per_update(d64) == 144 and L.lb_vector_width(d64, 0) == 2
+    odd = nat.make_desc("D3Q27", torch.float32, [5, 7, 9])
+    assert L.lb_vector_width(odd, 0) == 1
+    # KBC exists for D2Q9 / D3Q27 only (kbc_collision.py:101,115)
+    bad = nat.make_desc("D3Q19", torch.float32, [8, 8, 8], nat.LB_COLL_KBC, 0.6)
+    fl = nat.LbFields()
+    assert L.lb_step(bad, fl, 1, None) == -3
+    assert b"KBC" in L.lb_last_error()
+    ok = nat.make_desc("D3Q19", torch.float32, [8, 8, 8], nat.LB_COLL_BGK, 0.6)
+    assert L.lb_step(ok, fl, 1, None) == -1           # null population buffers
+    neg = nat.make_desc("D3Q19", torch.float32, [8, 8, 8], nat.LB_COLL_BGK, -1.0)
+    assert L.lb_step(neg, fl, 1, None) == -1
+    with pytest.raises(nat.NativeError):
+        nat.make_desc("D3Q15", torch.float32, [8, 8, 8])
+
+
+def test_no_cpu_fallback():
+    """the product refuses to step without the CUDA engine instead of falling back"""
+    import torch
+    import lettuce_b200 as lt
+    ctx = lt.Context(device="cpu", dtype=torch.float64, use_native=False)
+    flow = lt.TaylorGreenVortex(ctx, resolution=16, reynolds_number=10, mach_number=0.05, stencil=lt.D2Q9)
+    with pytest.raises(RuntimeError, match="no torch / CPU fallback"):
+        lt.Simulation(flow, lt.BGKCollision(0.6), [])
+    with pytest.raises(lt.native.NativeError):
+        lt.BGKCollision(0.6)(flow)
+
+
+def test_product_does_not_import_the_oracle():
+    pkg = os.path.join(ROOT, "lettuce_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, fn)).read()
+                assert "oracle" not in text.replace("no oracle", ""), os.path.join(dirpath, fn)

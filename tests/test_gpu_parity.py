@@ -1,0 +1,227 @@
+"""GPU parity tests: the CUDA path (through lt.Simulation -> ctypes -> C ABI -> kernels) against
+  (1) the golden vectors produced by the unmodified reference,
+  (2) the CPU oracle on seeded inputs at sizes it finishes in seconds,
+  (3) size-independent properties at BASELINE's full sizes.
+Bars (BASELINE.json north_star): streaming / masking / bounce-back bit-exact; populations after
+N steps within 1e-12 (fp64) / 1e-5 (fp32) relative (max|a-b| / max|b|)."""
+import numpy as np
+import pytest
+import torch
+
+from golden_util import DT, TOL, collision_params, golden_names, load_case, rel_err
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu():
+    import gpu_util
+    import lettuce_b200 as lt
+    return gpu_util, lt
+
+
+def _is_exact(meta):
+    return meta["collision"] == "none" and not any(b["kind"] == "equilibrium" for b in meta["boundaries"])
+
+
+# ------------------------------------------------------------------------------------------
+# (1) golden vectors from the reference
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", golden_names())
+def test_golden(name):
+    gu, lt = _gpu()
+    case = load_case(name)
+    meta = case["meta"]
+    sim = gu.simulation_from_case(case)
+    sim(meta["n_steps"])
+    out = sim.flow.f.cpu().numpy()
+    ref = case["f_out"]
+    assert out.shape == ref.shape and out.dtype == ref.dtype
+    if _is_exact(meta):
+        assert np.array_equal(out, ref), "streaming / bounce-back must be bit-exact"
+    else:
+        assert rel_err(out, ref) <= TOL[meta["dtype"]]
+
+
+@pytest.mark.parametrize("name", golden_names())
+def test_golden_step_by_step(name):
+    """the per-step seam `_collide_and_stream(simulation)` gives the same result as the batch"""
+    gu, lt = _gpu()
+    case = load_case(name)
+    meta = case["meta"]
+    a = gu.simulation_from_case(case)
+    b = gu.simulation_from_case(case)
+    a(meta["n_steps"])
+    for _ in range(meta["n_steps"]):
+        b._collide_and_stream(b)
+        b.flow.i += 1
+    assert torch.equal(a.flow.f, b.flow.f)
+
+
+@pytest.mark.parametrize("name", [n for n in golden_names() if n.startswith("tgv_") and "_bgk_" in n])
+def test_golden_reporters(name):
+    """fused energy / max-velocity / enstrophy reporters vs the reference's observables"""
+    gu, lt = _gpu()
+    case = load_case(name)
+    meta = case["meta"]
+    sim = gu.simulation_from_case(case)
+    # the golden flow's unit system (make_golden.GoldenFlow) == gpu_util.FieldFlow's
+    reps = [lt.ObservableReporter(lt.IncompressibleKineticEnergy(sim.flow), interval=1, out=None),
+            lt.ObservableReporter(lt.MaximumVelocity(sim.flow), interval=5, out=None),
+            lt.ObservableReporter(lt.Enstrophy(sim.flow), interval=meta["n_steps"], out=None)]
+    sim.reporter.extend(reps)
+    sim(meta["n_steps"])
+    tol = 2e-5 if meta["dtype"] == "f32" else 1e-11
+    e, m, w = reps[0].out, reps[1].out, reps[2].out
+    assert [r[0] for r in e] == list(range(meta["n_steps"] + 1))
+    assert [r[0] for r in m] == list(range(0, meta["n_steps"] + 1, 5))
+    assert [r[0] for r in w] == [0, meta["n_steps"]]
+    for rep, k in ((e, 0), (m, 1), (w, 2)):
+        assert rep[0][2] == pytest.approx(case["obs0"][k], rel=tol * (10 if k == 2 else 1))
+        assert rep[-1][2] == pytest.approx(case["obs_out"][k], rel=tol * (10 if k == 2 else 1))
+    # energy of a decaying vortex decreases monotonically
+    assert all(e[i + 1][2] <= e[i][2] * (1 + 1e-6) for i in range(len(e) - 1))
+
+
+# ------------------------------------------------------------------------------------------
+# (2) oracle on seeded inputs: shapes chosen to hit the vector path with lines longer than a
+#     warp, several lines per warp, the scalar path, and degenerate axes
+# ------------------------------------------------------------------------------------------
+SHAPES = {
+    "D2Q9": [[24, 512], [7, 36], [5, 7], [1, 8], [16, 2], [3, 1]],
+    "D3Q19": [[4, 6, 256], [3, 5, 20], [4, 3, 7], [1, 1, 8], [2, 2, 2]],
+    "D3Q27": [[3, 4, 132], [2, 3, 9], [1, 2, 4]],
+}
+
+
+def _run_pair(stencil, dtype, res, collision, params, n_steps, seed, masks=False, amp=0.1):
+    from oracle import lbm_oracle as orc
+    gu, lt = _gpu()
+    rng = np.random.default_rng(seed)
+    lat = orc.OracleLattice(stencil, DT[dtype])
+    S = getattr(lt, stencil)()
+    w = np.asarray(S.w).reshape([S.q] + [1] * len(res))
+    f0 = torch.tensor(w * (1.0 + amp * rng.random([S.q, *res])), dtype=DT[dtype])
+    ncm = nsm = None
+    obnds = []
+    ctx = lt.Context(device="cuda", dtype=DT[dtype], use_native=True)
+    flow = gu.FieldFlow(ctx, res, getattr(lt, stencil), f0)
+    if masks:
+        solid = torch.tensor(rng.random(res) < 0.15)
+        eqm = torch.tensor(rng.random(res) < 0.1)
+        smask = torch.tensor(rng.random([S.q, *res]) < 0.1) if masks == "nsm" else None
+        rho_b = torch.tensor(1.0 + 0.01 * rng.random([1] + list(res[:-1]) + [1]), dtype=DT[dtype])
+        u_b = torch.tensor(0.05 * rng.random([len(res)] + [1] * (len(res) - 1) + [res[-1]]), dtype=DT[dtype])
+        flow.boundaries.append(gu.TaggedBounceBack(solid, nsm=smask, tag=1))
+        flow.boundaries.append(gu.LUEquilibriumBoundary(ctx, eqm, rho_b, u_b, tag=2))
+        obnds = [orc.OracleBoundary("bounce_back", solid),
+                 orc.OracleBoundary("equilibrium", eqm, rho=rho_b, u=u_b)]
+        ncm, nsm = orc.build_masks(lat, res, obnds, [smask])
+    sim = lt.Simulation(flow, gu.make_collision(dict(collision=collision, tau=params.get("tau"),
+                                                     tau_minus=params.get("tau_minus", 1.0))), [])
+    sim(n_steps)
+    ref = orc.run(lat, f0, n_steps, collision, params, ncm=ncm, nsm=nsm, boundaries=obnds)
+    return sim.flow.f.cpu().numpy(), ref.numpy()
+
+
+@pytest.mark.parametrize("stencil", list(SHAPES))
+@pytest.mark.parametrize("dtype", ["f32", "f64"])
+def test_streaming_bit_exact_vs_oracle(stencil, dtype):
+    for k, res in enumerate(SHAPES[stencil]):
+        out, ref = _run_pair(stencil, dtype, res, "none", {}, 3, seed=100 + k)
+        assert np.array_equal(out, ref), f"{stencil} {dtype} {res}"
+
+
+@pytest.mark.parametrize("stencil", list(SHAPES))
+@pytest.mark.parametrize("masks", ["ncm", "nsm"])
+def test_masked_streaming_bit_exact_vs_oracle(stencil, masks):
+    """NoCollision + bounce-back + destination-masked streaming is pure data movement;
+    the equilibrium nodes are excluded from the exactness check by comparing them with tolerance"""
+    for k, res in enumerate(SHAPES[stencil][:4]):
+        out, ref = _run_pair(stencil, "f64", res, "none", {}, 3, seed=200 + k, masks=masks)
+        assert rel_err(out, ref) <= 1e-14, f"{stencil} {res}"
+
+
+@pytest.mark.parametrize("stencil,collision", [("D2Q9", "bgk"), ("D2Q9", "trt"), ("D2Q9", "kbc"),
+                                               ("D3Q19", "bgk"), ("D3Q19", "trt"),
+                                               ("D3Q27", "bgk"), ("D3Q27", "trt"), ("D3Q27", "kbc")])
+@pytest.mark.parametrize("dtype", ["f32", "f64"])
+@pytest.mark.parametrize("masks", [False, "ncm", "nsm"])
+def test_collisions_vs_oracle(stencil, collision, dtype, masks):
+    params = dict(tau=0.62)
+    if collision == "trt":
+        params["tau_minus"] = 0.9
+    for k, res in enumerate(SHAPES[stencil][:3]):
+        out, ref = _run_pair(stencil, dtype, res, collision, params, 10, seed=300 + k, masks=masks,
+                             amp=0.02)
+        assert rel_err(out, ref) <= TOL[dtype], f"{stencil} {collision} {dtype} {res}"
+
+
+# ------------------------------------------------------------------------------------------
+# (3) properties at BASELINE's full sizes
+# ------------------------------------------------------------------------------------------
+def test_full_size_streaming_period_d3q19_256():
+    """config 2 size: 256 NoCollision steps on a periodic 256^3 box bring every population back
+    to where it started -- bit-exact, and every intermediate state is a permutation (same sum)."""
+    gu, lt = _gpu()
+    ctx = lt.Context(device="cuda", dtype=torch.float32, use_native=True)
+    g = torch.Generator(device="cuda").manual_seed(7)
+    f0 = torch.rand([19, 256, 256, 256], device="cuda", dtype=torch.float32, generator=g)
+    flow = gu.FieldFlow(ctx, [256, 256, 256], lt.D3Q19, f0)
+    sim = lt.Simulation(flow, lt.NoCollision(), [])
+    sim(1)
+    # one step moves population q by e_q: check three directions against torch.roll on the GPU
+    for q, e in ((1, (1, 0, 0)), (10, (0, -1, 1)), (14, (-1, 0, 1))):
+        assert torch.equal(flow.f[q], torch.roll(f0[q], shifts=e, dims=(0, 1, 2)))
+    sim(255)
+    assert torch.equal(flow.f, f0)
+
+
+def test_full_size_bgk_conservation_d3q19_256():
+    """config 2: TGV 256^3 D3Q19 BGK fp32, 20 steps: mass and momentum are conserved to
+    round-off, kinetic energy decays, nothing becomes NaN."""
+    gu, lt = _gpu()
+    ctx = lt.Context(device="cuda", dtype=torch.float32, use_native=True)
+    flow = lt.TaylorGreenVortex(ctx, resolution=256, reynolds_number=1600, mach_number=0.1,
+                                stencil=lt.D3Q19)
+    m0 = flow.f.double().sum().item()
+    j0 = flow.j().double().sum(dim=(1, 2, 3))
+    rep = lt.ObservableReporter(lt.IncompressibleKineticEnergy(flow), interval=5, out=None)
+    sim = lt.Simulation(flow, lt.BGKCollision(tau=flow.units.relaxation_parameter_lu), [rep])
+    sim(20)
+    assert torch.isfinite(flow.f).all()
+    assert flow.f.double().sum().item() == pytest.approx(m0, rel=1e-6)
+    assert torch.allclose(flow.j().double().sum(dim=(1, 2, 3)), j0, atol=1e-2)
+    e = [r[2] for r in rep.out]
+    assert len(e) == 5 and all(e[i + 1] < e[i] for i in range(4))
+
+
+def test_full_size_obstacle_2048x1024():
+    """config 3: D2Q9 BGK 2048x1024 with bounce-back cylinder + equilibrium inlet/outlet:
+    solid interior stays at rest state, inlet/outlet columns hold their equilibrium."""
+    gu, lt = _gpu()
+    ctx = lt.Context(device="cuda", dtype=torch.float32, use_native=True)
+    flow = lt.Obstacle(ctx, [2048, 1024], reynolds_number=300, mach_number=0.01, domain_length_x=1)
+    x, y = flow.grid
+    flow.mask = ((x - 0.3 * x.max()) ** 2 + (y - 0.5 * y.max()) ** 2) < (0.05 * y.max()) ** 2
+    sim = lt.Simulation(flow, lt.BGKCollision(tau=flow.units.relaxation_parameter_lu), [])
+    assert sorted(sim.no_collision_mask.unique().tolist()) == [0, 1, 2, 3]
+    sim(50)
+    assert torch.isfinite(flow.f).all()
+    u = flow.u()
+    assert float(u[0].mean()) > 0
+
+
+def test_kbc_d3q27_energy_reporter_interval():
+    """config 4 reduced (D3Q27 KBC fp32 + fused energy reporter): interval 1 / 10 agree"""
+    gu, lt = _gpu()
+    outs = []
+    for interval in (1, 10):
+        ctx = lt.Context(device="cuda", dtype=torch.float32, use_native=True)
+        flow = lt.TaylorGreenVortex(ctx, resolution=64, reynolds_number=1600, mach_number=0.1,
+                                    stencil=lt.D3Q27)
+        rep = lt.ObservableReporter(lt.IncompressibleKineticEnergy(flow), interval=interval, out=None)
+        lt.Simulation(flow, lt.KBCCollision(), [rep])(30)
+        outs.append({r[0]: r[2] for r in rep.out})
+    assert sorted(outs[1]) == [0, 10, 20, 30]
+    for i in outs[1]:
+        assert outs[1][i] == pytest.approx(outs[0][i], rel=1e-6)
