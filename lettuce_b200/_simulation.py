@@ -152,7 +152,8 @@ class Simulation:
         flow = self.flow
         if not flow.f.is_contiguous():
             flow.f = flow.f.contiguous()
-        if flow.f.device != self.context.device:
+        cdev = self.context.device
+        if flow.f.device.type != cdev.type or (cdev.index is not None and flow.f.device != cdev):
             raise ValueError("flow.f is not on the context device")
         fl = nat.LbFields()
         fl.f, fl.f_next = flow.f.data_ptr(), flow.f_next.data_ptr()

@@ -62,7 +62,31 @@ struct StepParams {
   unsigned* obs_counter;
   double* obs_out;             // [LB_OBS_COUNT]
   T* u_out;                    // [D][n_nodes] or nullptr
+  // z-slab decomposition (multi-GPU): when set, populations leaving the slab through its
+  // z = nz-1 face (ez = +1) / z = 0 face (ez = -1) are stored to
+  //   halo_hi / halo_lo [qidx * halo_qs + dest_line * halo_ls + halo_{hi,lo}_off]
+  // instead of wrapping around locally.  qidx = q (direct: the base is the neighbour's
+  // population buffer, peer-mapped) or the compact z-face index (packed send buffer).
+  T* halo_hi;
+  T* halo_lo;
+  long long halo_qs, halo_ls;
+  unsigned halo_hi_off, halo_lo_off;
+  int halo_compact;
 };
+
+// number of directions q' < q that leave through the same z face as q
+template <class S>
+__host__ __device__ constexpr int zface_index(int q) {
+  int n = 0;
+  for (int k = 0; k < q; ++k) n += (S::e(k, 2) == S::e(q, 2)) ? 1 : 0;
+  return n;
+}
+template <class S>
+__host__ __device__ constexpr int zface_count() {
+  int n = 0;
+  for (int k = 0; k < S::Q; ++k) n += (S::e(k, 2) == 1) ? 1 : 0;
+  return n;
+}
 
 template <typename T, int V>
 struct alignas(sizeof(T) * V) Vec {
@@ -276,8 +300,16 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
           st_vec<T, V>(dst + z0, v);
         }
       } else if constexpr (V == 1) {
-        const unsigned zd = (ez > 0) ? (z0 + 1 == nz ? 0u : z0 + 1) : (z0 == 0 ? nz - 1 : z0 - 1);
-        if (active) dst[zd] = f[q][0];
+        const bool crosses = (ez > 0) ? (z0 + 1 == nz) : (z0 == 0);
+        const unsigned zd = (ez > 0) ? (crosses ? 0u : z0 + 1) : (crosses ? nz - 1 : z0 - 1);
+        if (active) {
+          T* hp = (ez > 0) ? p.halo_hi : p.halo_lo;
+          if (crosses && hp != nullptr)
+            hp[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs + (long long)(xd * ny + yd) * p.halo_ls +
+               ((ez > 0) ? p.halo_hi_off : p.halo_lo_off)] = f[q][0];
+          else
+            dst[zd] = f[q][0];
+        }
       } else if constexpr (ez > 0) {
         // destination z0+k takes the source value of z0+k-1: element 0 comes from the left lane
         const T up = __shfl_up_sync(0xffffffffu, f[q][V - 1], 1);
@@ -292,7 +324,13 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
 #pragma unroll
             for (int k = 1; k < V; ++k) dst[z0 + k] = f[q][k - 1];
           }
-          if (lane == 31 || last_in_line) dst[last_in_line ? 0u : z0 + V] = f[q][V - 1];
+          if (lane == 31 || last_in_line) {
+            if (last_in_line && p.halo_hi != nullptr)
+              p.halo_hi[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs +
+                        (long long)(xd * ny + yd) * p.halo_ls + p.halo_hi_off] = f[q][V - 1];
+            else
+              dst[last_in_line ? 0u : z0 + V] = f[q][V - 1];
+          }
         }
       } else {
         // ez < 0: destination z0+k takes the source value of z0+k+1
@@ -308,7 +346,13 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
 #pragma unroll
             for (int k = 0; k < V - 1; ++k) dst[z0 + k] = f[q][k + 1];
           }
-          if (lane == 0 || first_in_line) dst[first_in_line ? nz - 1 : z0 - 1] = f[q][0];
+          if (lane == 0 || first_in_line) {
+            if (first_in_line && p.halo_lo != nullptr)
+              p.halo_lo[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs +
+                        (long long)(xd * ny + yd) * p.halo_ls + p.halo_lo_off] = f[q][0];
+            else
+              dst[first_in_line ? nz - 1 : z0 - 1] = f[q][0];
+          }
         }
       }
     });
