@@ -43,7 +43,7 @@ extern "C" {
 #define LB_API
 #endif
 
-#define LB_ABI_VERSION 1
+#define LB_ABI_VERSION 2
 #define LB_MAX_BOUNDARIES 8
 
 enum { LB_D2Q9 = 0, LB_D3Q19 = 1, LB_D3Q27 = 2 };                     /* lb_desc.stencil   */
@@ -95,6 +95,40 @@ typedef struct lb_boundary {
   int64_t u_comp_stride;
 } lb_boundary;
 
+/* z-slab decomposition across GPUs (BASELINE.json: slabs along the contiguous z axis; the
+ * reference itself is single-device).  When lb_fields.halo is set, the
+ * populations that leave the local slab through z = nz-1 (ez = +1, "hi") or z = 0 (ez = -1,
+ * "lo") are not wrapped around but stored by the step kernel itself to
+ *     base[qidx * q_stride + dest_line * line_stride + offset],   dest_line = x' * ny + y'
+ * (x', y' = periodic destination line).  Two layouts:
+ *   compact = 0, "direct": base = the +z / -z neighbour's population buffer, peer-mapped
+ *       (CUDA IPC over NVLink), qidx = q, q_stride = nodes, line_stride = nz,
+ *       hi_offset = 0, lo_offset = nz-1: the kernel writes the neighbour's boundary planes in
+ *       place, no pack / unpack / copy kernels.  hi[k] / lo[k] are the neighbour's buffers that
+ *       correspond to this rank's f_next (k = 0) and f (k = 1).
+ *   compact = 1, "packed": base = a send buffer [zface][lines] (zface = 5 / 9 / 3 directions for
+ *       D3Q19 / D3Q27 / D2Q9), to be exchanged with NCCL send/recv and scattered by
+ *       lb_unpack_halo().
+ * If wait_slots is set, every step is followed by a neighbour handshake: the rank stores the
+ * step counter into both neighbours' wait slots (signal_up / signal_down, peer-mapped) and spins
+ * until both of its own slots reached it, so that step t+1 never reads a plane its neighbour has
+ * not written, nor overwrites one its neighbour still reads. */
+typedef struct lb_halo {
+  void* hi[2];
+  void* lo[2];
+  int64_t q_stride, line_stride;
+  int64_t hi_offset, lo_offset;
+  int32_t compact;
+  int32_t _pad;
+  uint32_t* signal_up;    /* peer: up neighbour's wait_slots[0] */
+  uint32_t* signal_down;  /* peer: down neighbour's wait_slots[1] */
+  uint32_t* wait_slots;   /* local [4]: [0] written by the down neighbour, [1] by the up neighbour,
+                             [2] set to 1 by the kernel if a wait timed out */
+  uint32_t epoch;         /* counter value before this call; the call performs n_steps + 1
+                             handshakes with values epoch+1 .. epoch+n_steps+1 */
+  uint32_t _pad2;
+} lb_halo;
+
 typedef struct lb_fields {
   void* f;                          /* populations, state in / (n even) state out        */
   void* f_next;                     /* second buffer (flow.f_next); (n odd) state out    */
@@ -110,6 +144,7 @@ typedef struct lb_fields {
   void* obs_scratch;                /* device scratch, lb_obs_scratch_bytes() bytes, if obs_out */
   void* u_out;                      /* device [d][*res] or NULL: velocity of the consumed
                                        state of the LAST step of the call (for enstrophy) */
+  const lb_halo* halo;              /* NULL: the slab is periodic in z by itself             */
 } lb_fields;
 
 LB_API int lb_abi_version(void);
@@ -152,6 +187,18 @@ LB_API int lb_enstrophy(const lb_desc* desc, const void* u, void* obs_scratch, d
 LB_API int lb_run_host(const lb_desc* desc, void* f_host, const uint8_t* ncm_host,
                 const uint8_t* nsm_host, const lb_boundary* boundaries_host_ptrs,
                 int n_boundaries, int n_steps, double* obs_host /* [LB_OBS_COUNT] or NULL */);
+
+/* ---- multi-GPU plumbing (one process per GPU) --------------------------------------------- */
+/* scatter packed halos received from the -z neighbour (its hi face -> our z = 0 plane) and the
+ * +z neighbour (its lo face -> our z = nz-1 plane) into f; either may be NULL */
+LB_API int lb_unpack_halo(const lb_desc* desc, void* f, const void* from_down, const void* from_up, void* stream);
+LB_API int lb_zface_count(int stencil);  /* directions per z face: 3 / 5 / 9 */
+/* device memory that other processes of the node can map (cudaMalloc + CUDA IPC) */
+LB_API int lb_ipc_alloc(size_t bytes, void** dptr);
+LB_API int lb_ipc_free(void* dptr);
+LB_API int lb_ipc_export(void* dptr, unsigned char handle[64]);
+LB_API int lb_ipc_open(const unsigned char handle[64], void** dptr);
+LB_API int lb_ipc_close(void* dptr);
 
 /* Introspection for tests / roofline arithmetic */
 LB_API int lb_stencil_q(int stencil);

@@ -20,7 +20,7 @@ LB_COLL_NONE, LB_COLL_BGK, LB_COLL_TRT, LB_COLL_KBC = 0, 1, 2, 3
 LB_BND_BOUNCE_BACK, LB_BND_EQUILIBRIUM = 1, 2
 LB_OBS_ENERGY, LB_OBS_MAXU2, LB_OBS_MASS, LB_OBS_ENSTROPHY, LB_OBS_COUNT = 0, 1, 2, 3, 4
 LB_MAX_BOUNDARIES = 8
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 STENCIL_IDS = {"D2Q9": LB_D2Q9, "D3Q19": LB_D3Q19, "D3Q27": LB_D3Q27}
 DTYPE_IDS = {torch.float32: LB_F32, torch.float64: LB_F64}
@@ -30,6 +30,8 @@ EXPORTED_SYMBOLS = (
     "lb_abi_version", "lb_last_error", "lb_step", "lb_collide", "lb_stream",
     "lb_pack_streaming_mask", "lb_moments", "lb_obs_scratch_bytes", "lb_observables",
     "lb_enstrophy", "lb_run_host", "lb_stencil_q", "lb_bytes_per_update", "lb_vector_width",
+    "lb_unpack_halo", "lb_zface_count", "lb_ipc_alloc", "lb_ipc_free", "lb_ipc_export",
+    "lb_ipc_open", "lb_ipc_close",
 )
 
 
@@ -53,11 +55,19 @@ class LbBoundary(C.Structure):
                 ("u_comp_stride", C.c_int64)]
 
 
+class LbHalo(C.Structure):
+    _fields_ = [("hi", C.c_void_p * 2), ("lo", C.c_void_p * 2), ("q_stride", C.c_int64),
+                ("line_stride", C.c_int64), ("hi_offset", C.c_int64), ("lo_offset", C.c_int64),
+                ("compact", C.c_int32), ("_pad", C.c_int32), ("signal_up", C.c_void_p),
+                ("signal_down", C.c_void_p), ("wait_slots", C.c_void_p), ("epoch", C.c_uint32),
+                ("_pad2", C.c_uint32)]
+
+
 class LbFields(C.Structure):
     _fields_ = [("f", C.c_void_p), ("f_next", C.c_void_p), ("no_collision_mask", C.c_void_p),
                 ("streaming_bits", C.c_void_p), ("boundaries", C.POINTER(LbBoundary)),
                 ("n_boundaries", C.c_int32), ("_pad", C.c_int32), ("obs_out", C.c_void_p),
-                ("obs_scratch", C.c_void_p), ("u_out", C.c_void_p)]
+                ("obs_scratch", C.c_void_p), ("u_out", C.c_void_p), ("halo", C.POINTER(LbHalo))]
 
 
 _lib = None
@@ -88,12 +98,21 @@ def lib() -> C.CDLL:
     L.lb_enstrophy.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.lb_run_host.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p,
                               C.POINTER(LbBoundary), C.c_int, C.c_int, C.c_void_p]
+    L.lb_unpack_halo.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.lb_zface_count.argtypes = [C.c_int]
+    L.lb_ipc_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
+    L.lb_ipc_free.argtypes = [C.c_void_p]
+    L.lb_ipc_export.argtypes = [C.c_void_p, C.c_char_p]
+    L.lb_ipc_open.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    L.lb_ipc_close.argtypes = [C.c_void_p]
     L.lb_stencil_q.argtypes = [C.c_int]
     L.lb_bytes_per_update.argtypes = [C.POINTER(LbDesc)]
     L.lb_bytes_per_update.restype = C.c_size_t
     L.lb_vector_width.argtypes = [C.POINTER(LbDesc), C.c_int]
     for name in ("lb_step", "lb_collide", "lb_stream", "lb_pack_streaming_mask", "lb_moments",
-                 "lb_observables", "lb_enstrophy", "lb_run_host", "lb_stencil_q", "lb_vector_width"):
+                 "lb_observables", "lb_enstrophy", "lb_run_host", "lb_stencil_q", "lb_vector_width",
+                 "lb_unpack_halo", "lb_zface_count", "lb_ipc_alloc", "lb_ipc_free", "lb_ipc_export",
+                 "lb_ipc_open", "lb_ipc_close"):
         getattr(L, name).restype = C.c_int
     if L.lb_abi_version() != ABI_VERSION:
         raise NativeError(f"ABI mismatch: library {L.lb_abi_version()} vs binding {ABI_VERSION}")

@@ -62,6 +62,9 @@ class Observable(ABC):
             nat.check(L.lb_observables(desc, f.data_ptr(), int(want_enstrophy), nat.ptr(u),
                                        scratch.data_ptr(), out.data_ptr(),
                                        nat.current_stream_ptr(f.device)))
+        reduce_ = getattr(flow, '_obs_allreduce', None)   # set by the slab driver: global reduction
+        if reduce_ is not None:
+            out = reduce_(out[None, :])[0]
         return float(out[self.native_slot].item())
 
     def _as_tensor(self, value: float) -> torch.Tensor:

@@ -243,6 +243,10 @@ class Simulation:
         end = timer()
         return num_steps * flow.rho().numel() / 1e6 / (end - beg)
 
+    def _finalize_obs(self, obs: torch.Tensor) -> torch.Tensor:
+        """device [n, LB_OBS_COUNT] -> host; the slab driver all-reduces across ranks here"""
+        return obs.cpu()
+
     def _run_segment(self, n, fused):
         """Advance n steps from flow.i, recording every fused reporter at each index
         i in (flow.i, flow.i + n] with i % interval == 0."""
@@ -297,7 +301,7 @@ class Simulation:
                                            self._obs_scratch.data_ptr(), obs[len(idx)].data_ptr(),
                                            nat.current_stream_ptr(dev)))
             row[i1] = len(idx)
-        host = obs.cpu()                 # the one device->host sync of the segment
+        host = self._finalize_obs(obs)   # the one device->host sync of the segment
         flow.i = i1
         for i in sorted(wanted):
             for r in wanted[i]:

@@ -11,6 +11,7 @@
 
 #include "../../include/lettuce_b200.h"
 #include "lb_kernels.cuh"
+#include "lb_halo.cuh"
 
 namespace {
 
@@ -146,9 +147,24 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
     partials = reinterpret_cast<double*>(static_cast<char*>(fl->obs_scratch) + 64);
     LB_CUDA(cudaMemsetAsync(counter, 0, 64, st));
   }
+  const lb_halo* h = fl->halo;
+  if (h) {
+    if (!do_stream) return fail(LB_EINVAL, "halo given to a collide-only call");
+    if (p.sbits) return fail(LB_EUNSUPPORTED, "masked streaming (no_streaming_mask) is not supported across slabs");
+    if (!h->hi[0] || !h->lo[0] || (n_steps > 1 && (!h->hi[1] || !h->lo[1])))
+      return fail(LB_EINVAL, "halo destination is null");
+    p.halo_qs = h->q_stride; p.halo_ls = h->line_stride;
+    p.halo_hi_off = (unsigned)h->hi_offset; p.halo_lo_off = (unsigned)h->lo_offset;
+    p.halo_compact = h->compact;
+    if (h->wait_slots) {
+      rc = lb::launch_halo_sync(h->signal_up, h->signal_down, h->wait_slots, h->epoch + 1u, st);
+      if (rc) return fail(LB_ECUDA, "halo sync launch failed");
+    }
+  }
   T* a = static_cast<T*>(fl->f);
   T* b = static_cast<T*>(fl->f_next);
   for (int s = 0; s < n_steps; ++s) {
+    if (h) { p.halo_hi = static_cast<T*>(h->hi[s & 1]); p.halo_lo = static_cast<T*>(h->lo[s & 1]); }
     p.f_in = a;
     p.f_out = b;
     c.obs = fl->obs_out != nullptr;
@@ -158,6 +174,10 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
     p.u_out = (c.obs && s == n_steps - 1) ? static_cast<T*>(fl->u_out) : nullptr;
     cudaError_t e = lb::launch_step<S, T>(c, p, st);
     if (e != cudaSuccess) return fail(LB_ECUDA, "step kernel launch failed: %s", cudaGetErrorString(e));
+    if (h && h->wait_slots) {
+      rc = lb::launch_halo_sync(h->signal_up, h->signal_down, h->wait_slots, h->epoch + 2u + (unsigned)s, st);
+      if (rc) return fail(LB_ECUDA, "halo sync launch failed");
+    }
     T* t = a; a = b; b = t;
   }
   return LB_OK;

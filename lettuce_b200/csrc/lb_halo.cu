@@ -1,0 +1,133 @@
+// Neighbour handshake over NVLink peer memory, packed-halo scatter, CUDA IPC helpers.
+//
+// Direct mode (see lb_halo in include/lettuce_b200.h): the step kernel of rank r writes the
+// populations that cross its z faces straight into the boundary planes of its neighbours'
+// output buffers through peer-mapped pointers.  What remains per step is a handshake:
+//   "I finished step t"  ->  st.release.sys into both neighbours' wait slots,
+//   spin (ld.acquire.sys) until both neighbours said the same.
+// After it, (a) the neighbours' stores into our planes are visible, so step t+1 may read them,
+// and (b) the neighbours have finished reading the buffer step t+1 will overwrite remotely.
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/lettuce_b200.h"
+#include "lb_halo.cuh"
+#include "lb_kernels.cuh"
+
+namespace lb {
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// counters only grow; compare with wrap-around safe signed difference
+__device__ __forceinline__ bool reached(uint32_t have, uint32_t want) { return int32_t(have - want) >= 0; }
+
+__global__ void halo_sync_kernel(uint32_t* signal_up, uint32_t* signal_down, uint32_t* wait_slots,
+                                 uint32_t value, long long timeout_cycles) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  __threadfence_system();  // order the previous kernel's peer stores before the signal
+  if (signal_up) st_release_sys(signal_up, value);
+  if (signal_down) st_release_sys(signal_down, value);
+  const long long t0 = clock64();
+  while (!(reached(ld_acquire_sys(&wait_slots[0]), value) && reached(ld_acquire_sys(&wait_slots[1]), value))) {
+    if (clock64() - t0 > timeout_cycles) {  // never hang the GPU: flag the error and carry on
+      wait_slots[2] = 1u;
+      break;
+    }
+    __nanosleep(100);
+  }
+}
+
+int launch_halo_sync(uint32_t* signal_up, uint32_t* signal_down, uint32_t* wait_slots, uint32_t value,
+                     cudaStream_t st) {
+  // ~10 s at 2 GHz: far beyond any legitimate skew between neighbours inside one node
+  halo_sync_kernel<<<1, 32, 0, st>>>(signal_up, signal_down, wait_slots, value, 20000000000ll);
+  return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+// packed [zface][lines] -> f[q][line * nz + z_edge]
+template <class S, typename T>
+__global__ void unpack_halo_kernel(T* __restrict__ f, const T* __restrict__ from_down,
+                                   const T* __restrict__ from_up, unsigned lines, unsigned nz,
+                                   size_t n_nodes) {
+  const unsigned line = blockIdx.x * blockDim.x + threadIdx.x;
+  if (line >= lines) return;
+  static_for<S::Q>([&](auto qc) {
+    constexpr int q = decltype(qc)::value;
+    constexpr int ez = S::e(q, 2);
+    if constexpr (ez == 1) {
+      if (from_down) f[q * n_nodes + size_t(line) * nz] = from_down[size_t(zface_index<S>(q)) * lines + line];
+    } else if constexpr (ez == -1) {
+      if (from_up) f[q * n_nodes + size_t(line) * nz + (nz - 1)] = from_up[size_t(zface_index<S>(q)) * lines + line];
+    }
+  });
+}
+
+template <class S, typename T>
+int unpack_typed(void* f, const void* d, const void* u, unsigned lines, unsigned nz, size_t n, cudaStream_t st) {
+  unpack_halo_kernel<S, T><<<(lines + 255) / 256, 256, 0, st>>>(static_cast<T*>(f), static_cast<const T*>(d),
+                                                               static_cast<const T*>(u), lines, nz, n);
+  return cudaGetLastError() == cudaSuccess ? 0 : -1;
+}
+
+}  // namespace lb
+
+extern "C" {
+
+int lb_zface_count(int stencil) {
+  switch (stencil) {
+    case LB_D2Q9: return lb::zface_count<lb::D2Q9>();
+    case LB_D3Q19: return lb::zface_count<lb::D3Q19>();
+    case LB_D3Q27: return lb::zface_count<lb::D3Q27>();
+  }
+  return -1;
+}
+
+int lb_unpack_halo(const lb_desc* d, void* f, const void* from_down, const void* from_up, void* stream) {
+  if (!d || !f) return LB_EINVAL;
+  const bool two_d = d->stencil == LB_D2Q9;
+  const unsigned nz = unsigned(two_d ? d->dims[1] : d->dims[2]);
+  const unsigned lines = unsigned(two_d ? d->dims[0] : d->dims[0] * d->dims[1]);
+  const size_t n = size_t(lines) * nz;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int rc = -1;
+  if (d->dtype == LB_F32) {
+    if (d->stencil == LB_D2Q9) rc = lb::unpack_typed<lb::D2Q9, float>(f, from_down, from_up, lines, nz, n, st);
+    if (d->stencil == LB_D3Q19) rc = lb::unpack_typed<lb::D3Q19, float>(f, from_down, from_up, lines, nz, n, st);
+    if (d->stencil == LB_D3Q27) rc = lb::unpack_typed<lb::D3Q27, float>(f, from_down, from_up, lines, nz, n, st);
+  } else if (d->dtype == LB_F64) {
+    if (d->stencil == LB_D2Q9) rc = lb::unpack_typed<lb::D2Q9, double>(f, from_down, from_up, lines, nz, n, st);
+    if (d->stencil == LB_D3Q19) rc = lb::unpack_typed<lb::D3Q19, double>(f, from_down, from_up, lines, nz, n, st);
+    if (d->stencil == LB_D3Q27) rc = lb::unpack_typed<lb::D3Q27, double>(f, from_down, from_up, lines, nz, n, st);
+  }
+  return rc == 0 ? LB_OK : LB_ECUDA;
+}
+
+int lb_ipc_alloc(size_t bytes, void** dptr) {
+  if (!dptr) return LB_EINVAL;
+  if (cudaMalloc(dptr, bytes) != cudaSuccess) return LB_ECUDA;
+  if (cudaMemset(*dptr, 0, bytes) != cudaSuccess) return LB_ECUDA;
+  return LB_OK;
+}
+int lb_ipc_free(void* dptr) { return cudaFree(dptr) == cudaSuccess ? LB_OK : LB_ECUDA; }
+int lb_ipc_export(void* dptr, unsigned char handle[64]) {
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+  cudaIpcMemHandle_t h;
+  if (cudaIpcGetMemHandle(&h, dptr) != cudaSuccess) return LB_ECUDA;
+  memcpy(handle, &h, 64);
+  return LB_OK;
+}
+int lb_ipc_open(const unsigned char handle[64], void** dptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle, 64);
+  return cudaIpcOpenMemHandle(dptr, h, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess ? LB_OK : LB_ECUDA;
+}
+int lb_ipc_close(void* dptr) { return cudaIpcCloseMemHandle(dptr) == cudaSuccess ? LB_OK : LB_ECUDA; }
+
+}  // extern "C"

@@ -1,0 +1,312 @@
+"""z-slab decomposition across the GPUs of one node: one process per GPU (torchrun), each rank
+owns a contiguous range of the last (contiguous) axis, periodic ring of neighbours.  New work
+defined by BASELINE.json -- the reference is single-device.
+
+Three transports behind one class:
+  'p2p'   the step kernel writes the populations that cross a z face straight into the
+          neighbour's boundary plane through CUDA-IPC peer pointers over NVLink, followed by a
+          one-thread neighbour handshake kernel: compute and exchange in ONE kernel, no
+          pack / copy / unpack, no host involvement between steps.  (default on CUDA)
+  'nccl'  the step kernel packs the crossing populations into send buffers, torch.distributed
+          send/recv moves them, lb_unpack_halo scatters them (the baseline design north_star names).
+  'host'  same exchange logic over any torch.distributed backend with an injected local stepper;
+          this is what the world_size-2 gloo tests on CPU drive (tests inject the oracle).
+"""
+import ctypes as C
+from timeit import default_timer as timer
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from . import _native as nat
+from ._flows import TaylorGreenVortex
+from ._reporter import ObservableReporter
+from ._simulation import Simulation
+
+__all__ = ['slab_range', 'zface_populations', 'SlabTaylorGreenVortex', 'SlabSimulation']
+
+
+def slab_range(n: int, rank: int, world: int):
+    """[z0, z1) of rank's slab; equal slabs are required by the direct transport"""
+    if n % world != 0:
+        raise ValueError(f"the slab axis ({n}) must be divisible by the number of ranks ({world})")
+    nl = n // world
+    return rank * nl, (rank + 1) * nl
+
+
+def zface_populations(stencil):
+    """(hi, lo): directions leaving through the +z / -z face of a slab, in ascending q --
+    the order of the packed halo buffers (lb::zface_index)"""
+    hi = [q for q, e in enumerate(stencil.e) if e[-1] == 1]
+    lo = [q for q, e in enumerate(stencil.e) if e[-1] == -1]
+    return hi, lo
+
+
+class SlabTaylorGreenVortex(TaylorGreenVortex):
+    """The local slab of a global Taylor-Green vortex.  Initialisation evaluates the analytic
+    (p, u) on the slab extended by the radius of the 6th-order gradient stencil (3 planes each
+    side, periodic indices into the GLOBAL grid), runs the usual feq - fneq initialisation there
+    and keeps the interior, so the populations equal the corresponding slice of the global
+    initial state."""
+    GHOST = 3
+
+    def __init__(self, context, global_resolution, reynolds_number, mach_number, stencil,
+                 rank: int, world: int, initialize_fneq: bool = True):
+        stencil = stencil() if callable(stencil) else stencil
+        self.global_resolution = list(global_resolution)
+        self.rank, self.world = rank, world
+        self.z0, self.z1 = slab_range(self.global_resolution[-1], rank, world)
+        self._ghost = self.GHOST if world > 1 else 0
+        ext = self.global_resolution[:-1] + [self.z1 - self.z0 + 2 * self._ghost]
+        TaylorGreenVortex.__init__(self, context, ext, reynolds_number, mach_number, stencil,
+                                   initialize_fneq=initialize_fneq)
+        g = self._ghost
+        if g:
+            self.f = self.f[..., g:-g].contiguous()
+        self.resolution = self.global_resolution[:-1] + [self.z1 - self.z0]
+
+    def make_units(self, reynolds_number, mach_number, resolution):
+        return TaylorGreenVortex.make_units(self, reynolds_number, mach_number, self.global_resolution)
+
+    @property
+    def grid(self):
+        axes = [torch.linspace(0, 2 * torch.pi * (1 - 1 / n), steps=n, device=self.context.device,
+                               dtype=self.context.dtype) for n in self.global_resolution]
+        g = self._ghost
+        idx = torch.arange(self.z0 - g, self.z1 + g, device=self.context.device) % self.global_resolution[-1]
+        axes[-1] = axes[-1][idx]
+        return torch.meshgrid(*axes, indexing='ij')
+
+
+class _DeviceMemory:
+    """cudaMalloc'ed, IPC-exportable memory exposed to torch through __cuda_array_interface__"""
+
+    def __init__(self, shape, dtype: torch.dtype):
+        self.shape, self.dtype = tuple(shape), dtype
+        n = 1
+        for s in shape:
+            n *= s
+        self.nbytes = n * torch.empty((), dtype=dtype).element_size()
+        p = C.c_void_p()
+        nat.check(nat.lib().lb_ipc_alloc(self.nbytes, C.byref(p)))
+        self.ptr = p.value
+        typestr = {torch.float32: "<f4", torch.float64: "<f8", torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
+        self.__cuda_array_interface__ = {"shape": self.shape, "typestr": typestr,
+                                         "data": (self.ptr, False), "version": 2}
+
+    def tensor(self, device):
+        return torch.as_tensor(self, device=device)
+
+    def handle(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        nat.check(nat.lib().lb_ipc_export(self.ptr, buf))
+        return buf.raw
+
+    def free(self):
+        if self.ptr:
+            nat.lib().lb_ipc_free(self.ptr)
+            self.ptr = None
+
+
+def _open_handle(handle: bytes) -> int:
+    p = C.c_void_p()
+    nat.check(nat.lib().lb_ipc_open(handle, C.byref(p)))
+    return p.value
+
+
+class SlabSimulation(Simulation):
+    """`Simulation` over one z-slab per rank.  Same call protocol: simulation(num_steps) -> global
+    MLUPS; fused reporters receive globally reduced observables."""
+
+    def __init__(self, flow, collision, reporter, transport: Optional[str] = None, group=None,
+                 local_stepper=None):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.up = (self.rank + 1) % self.world
+        self.down = (self.rank - 1) % self.world
+        self.local_stepper = local_stepper
+        if transport is None:
+            transport = 'host' if local_stepper is not None else 'p2p'
+        if transport not in ('p2p', 'nccl', 'host'):
+            raise ValueError(transport)
+        self.transport = transport
+        self._epoch = 0
+        self._mem = []
+        if transport == 'host':
+            # host-logic path (tests): no native engine, the injected stepper does the local update
+            self.flow, self.collision, self.reporter = flow, collision, reporter
+            self.flow.collision = collision
+            self.context = flow.context
+            self.boundaries = [None]
+            self.no_collision_mask = self.no_streaming_mask = None
+        else:
+            Simulation.__init__(self, flow, collision, reporter)
+            if self.no_streaming_mask is not None and bool(self.no_streaming_mask.any()):
+                raise NotImplementedError("no_streaming_mask is not supported across slabs")
+        flow._obs_allreduce = self._reduce_obs
+        self.hi_q, self.lo_q = zface_populations(flow.stencil)
+        self.lines = 1
+        for n in flow.resolution[:-1]:
+            self.lines *= n
+        if self.world > 1:
+            if transport == 'p2p':
+                self._setup_p2p()
+            else:
+                self._setup_packed()
+
+    # ---- packed transport (nccl / host) --------------------------------------------------------
+    def _setup_packed(self):
+        f = self.flow.f
+        shape = [len(self.hi_q), self.lines]
+        self.send_hi, self.send_lo = f.new_zeros(shape), f.new_zeros(shape)
+        self.recv_down, self.recv_up = f.new_zeros(shape), f.new_zeros(shape)
+
+    def _exchange_packed(self):
+        """send_hi -> up neighbour's recv_down, send_lo -> down neighbour's recv_up (ring)"""
+        ops = [dist.P2POp(dist.isend, self.send_hi, self.up, self.group),
+               dist.P2POp(dist.isend, self.send_lo, self.down, self.group),
+               dist.P2POp(dist.irecv, self.recv_down, self.down, self.group),
+               dist.P2POp(dist.irecv, self.recv_up, self.up, self.group)]
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+
+    # ---- direct transport ------------------------------------------------------------------------
+    def _setup_p2p(self):
+        flow, dev = self.flow, self.flow.f.device
+        with torch.cuda.device(dev):
+            bufs = [_DeviceMemory(flow.f.shape, flow.f.dtype) for _ in range(2)]
+            flags = _DeviceMemory([4], torch.int32)
+            self._mem = bufs + [flags]
+            self._buf = [b.tensor(dev) for b in bufs]
+            self._buf[0].copy_(flow.f)
+            flow.f, flow.f_next = self._buf[0], self._buf[1]
+            self._flags = flags.tensor(dev)
+            torch.cuda.synchronize(dev)
+            handles = [None] * self.world
+            dist.all_gather_object(handles, [m.handle() for m in self._mem], group=self.group)
+            self._peer = {}
+            for r in {self.up, self.down}:
+                self._peer[r] = [_open_handle(h) for h in handles[r]]
+        dist.barrier(group=self.group)
+
+    def _halo_struct(self, epoch):
+        flow = self.flow
+        h = nat.LbHalo()
+        nz = flow.resolution[-1]
+        if self.transport == 'p2p':
+            cur = 0 if flow.f.data_ptr() == self._buf[0].data_ptr() else 1
+            up, down = self._peer[self.up], self._peer[self.down]
+            # step s writes into f_next (s even) / f (s odd): the neighbour's matching buffers
+            h.hi[0], h.hi[1] = up[1 - cur], up[cur]
+            h.lo[0], h.lo[1] = down[1 - cur], down[cur]
+            h.q_stride, h.line_stride = flow.f[0].numel(), nz
+            h.hi_offset, h.lo_offset = 0, nz - 1
+            h.compact = 0
+            h.signal_up = up[2] + 0          # up neighbour's wait_slots[0] (we are its down neighbour)
+            h.signal_down = down[2] + 4      # down neighbour's wait_slots[1]
+            h.wait_slots = self._flags.data_ptr()
+            h.epoch = epoch
+        else:
+            h.hi[0] = h.hi[1] = self.send_hi.data_ptr()
+            h.lo[0] = h.lo[1] = self.send_lo.data_ptr()
+            h.q_stride, h.line_stride = self.lines, 1
+            h.hi_offset = h.lo_offset = 0
+            h.compact = 1
+        return h
+
+    def _fields(self, desc, obs_out=None, u_out=None):
+        fl = Simulation._fields(self, desc, obs_out, u_out)
+        if self.world > 1:
+            self._halo = self._halo_struct(self._epoch)
+            fl.halo = C.pointer(self._halo)
+        return fl
+
+    def _advance(self, n, obs_out=None, u_out=None):
+        if n <= 0:
+            return
+        if self.transport == 'host':
+            for _ in range(n):
+                self._host_step()
+            return
+        if self.world == 1:
+            return Simulation._advance(self, n, obs_out, u_out)
+        if self.transport == 'p2p':
+            Simulation._advance(self, n, obs_out, u_out)
+            self._epoch += n + 1
+            return
+        # nccl: one step per call, exchange + unpack in between
+        dev = self.context.device
+        for s in range(n):
+            Simulation._advance(self, 1, None if obs_out is None else obs_out[s:s + 1],
+                                u_out if s == n - 1 else None)
+            self._exchange_packed()
+            desc = self._desc()
+            with torch.cuda.device(dev):
+                nat.check(nat.lib().lb_unpack_halo(desc, self.flow.f.data_ptr(), self.recv_down.data_ptr(),
+                                                   self.recv_up.data_ptr(), nat.current_stream_ptr(dev)))
+
+    def _host_step(self):
+        """local update by the injected stepper, which follows the kernel's contract: it returns
+        the locally streamed slab (periodic in z by itself) -- the planes that wrapped around are
+        exactly the populations owed to the neighbours."""
+        flow = self.flow
+        f = self.local_stepper(flow.f)
+        if self.world > 1:
+            for k, q in enumerate(self.hi_q):
+                self.send_hi[k] = f[q][..., 0].reshape(-1)       # wrapped to z=0: belongs to `up`
+            for k, q in enumerate(self.lo_q):
+                self.send_lo[k] = f[q][..., -1].reshape(-1)      # wrapped to z=nz-1: belongs to `down`
+            self._exchange_packed()
+            plane = f[0][..., 0].shape
+            for k, q in enumerate(self.hi_q):
+                f[q][..., 0] = self.recv_down[k].reshape(plane)
+            for k, q in enumerate(self.lo_q):
+                f[q][..., -1] = self.recv_up[k].reshape(plane)
+        flow.f = f
+
+    # ---- reporters: global reductions ------------------------------------------------------------
+    def _reduce_obs(self, obs: torch.Tensor):
+        """[n, LB_OBS_COUNT] local partials (device) -> global: sums except the max|u|^2 column"""
+        if self.world == 1:
+            return obs
+        t = obs.clone()
+        mx = t[:, nat.LB_OBS_MAXU2].clone()
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX, group=self.group)
+        t[:, nat.LB_OBS_MAXU2] = mx
+        return t
+
+    def _finalize_obs(self, obs):
+        return self._reduce_obs(obs).cpu()
+
+    def _run_segment(self, n, fused):
+        if any(r.native_slot == nat.LB_OBS_ENSTROPHY for r in fused) and self.world > 1:
+            raise NotImplementedError("Enstrophy across slabs needs a 3-plane velocity halo (not built yet)")
+        if self.transport == 'host':
+            self._advance(n)
+            self.flow.i += n
+            return
+        return Simulation._run_segment(self, n, fused)
+
+    def __call__(self, num_steps):
+        if self.transport == 'host':
+            beg = timer()
+            self._advance(num_steps)
+            self.flow.i += num_steps
+            return num_steps * self.flow.f[0].numel() * self.world / 1e6 / (timer() - beg)
+        mlups_local = Simulation.__call__(self, num_steps)
+        if self.world > 1 and self.transport == 'p2p':
+            if int(self._flags[2].item()) != 0:
+                raise RuntimeError("halo handshake timed out: a neighbour rank did not reach the same step")
+        return mlups_local * self.world
+
+    def close(self):
+        if self.world > 1 and self.transport == 'p2p':
+            torch.cuda.synchronize(self.context.device)
+            dist.barrier(group=self.group)
+            for r, ptrs in self._peer.items():
+                for p in ptrs:
+                    nat.lib().lb_ipc_close(p)
+            self._peer = {}

@@ -1,0 +1,103 @@
+"""Slab halo paths of the step kernel on ONE GPU: R slabs of a lattice live in one process, the
+"peer" pointers are simply the other slabs' buffers, launches are serial in one stream (no
+handshake needed, none used: kernels that wait on one another must not share a GPU).  Both halo
+layouts -- direct stores into the neighbour's planes, and packed send buffers + lb_unpack_halo --
+must reproduce the undivided single-GPU run bit for bit."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from golden_util import DT
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_slabs(stencil, dtype, res, R, n_steps, collision, mode, with_mask):
+    import gpu_util as gu
+    import lettuce_b200 as lt
+    nat = lt.native
+    L = nat.lib()
+    tdt = DT[dtype]
+    S = getattr(lt, stencil)()
+    rng = np.random.default_rng(42)
+    w = np.asarray(S.w).reshape([S.q] + [1] * len(res))
+    f0 = torch.tensor(w * (1.0 + 0.05 * rng.random([S.q, *res])), dtype=tdt, device="cuda")
+    solid = torch.tensor(rng.random(res) < 0.1, device="cuda") if with_mask else None
+
+    # undivided reference run on the GPU
+    ctx = lt.Context(device="cuda", dtype=tdt, use_native=True)
+    flow = gu.FieldFlow(ctx, res, getattr(lt, stencil), f0)
+    if with_mask:
+        flow.boundaries.append(gu.TaggedBounceBack(solid, tag=1))
+    coll = {"none": lt.NoCollision(), "bgk": lt.BGKCollision(0.7), "trt": lt.TRTCollision(0.7, 0.9)}[collision]
+    sim = lt.Simulation(flow, coll, [])
+    sim(n_steps)
+    want = flow.f
+
+    # R slabs
+    nzl = res[-1] // R
+    lres = list(res[:-1]) + [nzl]
+    cd = coll.native_descriptor(flow)
+    desc = nat.make_desc(stencil, tdt, lres, cd["collision"], cd.get("tau", 1.0), cd.get("tau_minus", 1.0))
+    A = [f0[..., r * nzl:(r + 1) * nzl].contiguous() for r in range(R)]
+    B = [torch.empty_like(a) for a in A]
+    ncm = [solid[..., r * nzl:(r + 1) * nzl].to(torch.uint8).contiguous() for r in range(R)] if with_mask else None
+    bnd = (nat.LbBoundary * 1)()
+    bnd[0].kind = nat.LB_BND_BOUNCE_BACK
+    lines = int(np.prod(res[:-1]))
+    nf = L.lb_zface_count(desc.stencil)
+    send_hi = [torch.zeros([nf, lines], dtype=tdt, device="cuda") for _ in range(R)]
+    send_lo = [torch.zeros([nf, lines], dtype=tdt, device="cuda") for _ in range(R)]
+    st = torch.cuda.current_stream().cuda_stream
+    for _ in range(n_steps):
+        for r in range(R):
+            up, down = (r + 1) % R, (r - 1) % R
+            h = nat.LbHalo()
+            if mode == "direct":
+                h.hi[0], h.lo[0] = B[up].data_ptr(), B[down].data_ptr()
+                h.q_stride, h.line_stride = A[r][0].numel(), nzl
+                h.hi_offset, h.lo_offset, h.compact = 0, nzl - 1, 0
+            else:
+                h.hi[0], h.lo[0] = send_hi[r].data_ptr(), send_lo[r].data_ptr()
+                h.q_stride, h.line_stride = lines, 1
+                h.hi_offset, h.lo_offset, h.compact = 0, 0, 1
+            fl = nat.LbFields()
+            fl.f, fl.f_next = A[r].data_ptr(), B[r].data_ptr()
+            if with_mask:
+                fl.no_collision_mask = ncm[r].data_ptr()
+                fl.boundaries = C.cast(bnd, C.POINTER(nat.LbBoundary))
+                fl.n_boundaries = 1
+            fl.halo = C.pointer(h)
+            nat.check(L.lb_step(desc, fl, 1, st))
+        if mode == "packed":
+            for r in range(R):
+                up, down = (r + 1) % R, (r - 1) % R
+                nat.check(L.lb_unpack_halo(desc, B[r].data_ptr(), send_hi[down].data_ptr(),
+                                           send_lo[up].data_ptr(), st))
+        A, B = B, A
+    got = torch.cat(A, dim=-1)
+    return got, want
+
+
+CASES = [
+    ("D3Q19", "f32", [6, 5, 32], 2), ("D3Q19", "f32", [4, 4, 512], 4), ("D3Q19", "f64", [3, 5, 12], 4),
+    ("D3Q19", "f32", [3, 4, 15], 3), ("D3Q27", "f32", [4, 3, 24], 2), ("D3Q27", "f64", [3, 3, 9], 3),
+    ("D2Q9", "f64", [7, 16], 4), ("D2Q9", "f32", [5, 6], 2), ("D3Q19", "f32", [4, 4, 2], 2),
+]
+
+
+@pytest.mark.parametrize("stencil,dtype,res,R", CASES)
+@pytest.mark.parametrize("mode", ["direct", "packed"])
+def test_slab_streaming_equals_undivided(stencil, dtype, res, R, mode):
+    got, want = _run_slabs(stencil, dtype, res, R, 4, "none", mode, with_mask=False)
+    assert torch.equal(got, want)
+
+
+@pytest.mark.parametrize("stencil,dtype,res,R", CASES[:6])
+@pytest.mark.parametrize("mode", ["direct", "packed"])
+@pytest.mark.parametrize("collision", ["bgk", "trt"])
+def test_slab_collision_with_mask_equals_undivided(stencil, dtype, res, R, mode, collision):
+    got, want = _run_slabs(stencil, dtype, res, R, 6, collision, mode, with_mask=True)
+    assert torch.equal(got, want)
