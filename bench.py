@@ -197,7 +197,8 @@ def run_native(args):
         from lettuce_b200.slab import SlabTaylorGreenVortex, SlabSimulation
         flow = SlabTaylorGreenVortex(ctx, [res, res, res * world], reynolds_number=1600, mach_number=0.1,
                                      stencil=lt.D3Q19, rank=rank, world=world)
-        sim = SlabSimulation(flow, lt.BGKCollision(tau=flow.units.relaxation_parameter_lu), [])
+        sim = SlabSimulation(flow, lt.BGKCollision(tau=flow.units.relaxation_parameter_lu), [],
+                             transport=os.environ.get("LB_SLAB_TRANSPORT", "p2p"))
     nodes_local = res ** 3
     f_bytes = flow.f.numel() * flow.f.element_size()
 

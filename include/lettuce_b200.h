@@ -43,7 +43,7 @@ extern "C" {
 #define LB_API
 #endif
 
-#define LB_ABI_VERSION 2
+#define LB_ABI_VERSION 3
 #define LB_MAX_BOUNDARIES 8
 
 enum { LB_D2Q9 = 0, LB_D3Q19 = 1, LB_D3Q27 = 2 };                     /* lb_desc.stencil   */
@@ -96,37 +96,50 @@ typedef struct lb_boundary {
 } lb_boundary;
 
 /* z-slab decomposition across GPUs (BASELINE.json: slabs along the contiguous z axis; the
- * reference itself is single-device).  When lb_fields.halo is set, the
- * populations that leave the local slab through z = nz-1 (ez = +1, "hi") or z = 0 (ez = -1,
- * "lo") are not wrapped around but stored by the step kernel itself to
- *     base[qidx * q_stride + dest_line * line_stride + offset],   dest_line = x' * ny + y'
- * (x', y' = periodic destination line).  Two layouts:
- *   compact = 0, "direct": base = the +z / -z neighbour's population buffer, peer-mapped
- *       (CUDA IPC over NVLink), qidx = q, q_stride = nodes, line_stride = nz,
- *       hi_offset = 0, lo_offset = nz-1: the kernel writes the neighbour's boundary planes in
- *       place, no pack / unpack / copy kernels.  hi[k] / lo[k] are the neighbour's buffers that
- *       correspond to this rank's f_next (k = 0) and f (k = 1).
- *   compact = 1, "packed": base = a send buffer [zface][lines] (zface = 5 / 9 / 3 directions for
- *       D3Q19 / D3Q27 / D2Q9), to be exchanged with NCCL send/recv and scattered by
- *       lb_unpack_halo().
- * If wait_slots is set, every step is followed by a neighbour handshake: the rank stores the
- * step counter into both neighbours' wait slots (signal_up / signal_down, peer-mapped) and spins
- * until both of its own slots reached it, so that step t+1 never reads a plane its neighbour has
- * not written, nor overwrites one its neighbour still reads. */
+ * reference itself is single-device).  With lb_fields.halo set, the
+ * populations that leave the local slab through z = nz-1 (ez = +1, "hi" face) or z = 0
+ * (ez = -1, "lo" face) are not wrapped around locally.  Three modes:
+ *
+ * LB_HALO_PACKED  the step kernel stores them into send_hi[0] / send_lo[0], packed as
+ *     [zface][lines] (zface = 3 / 5 / 9 directions for D2Q9 / D3Q19 / D3Q27, ascending q;
+ *     lines = product of the non-contiguous axes, indexed by the DESTINATION line).  The caller
+ *     moves them (NCCL send/recv) and scatters what it received with lb_unpack_halo() -- or
+ *     hands it to the next call as recv_lo[0] / recv_hi[0], which the step kernel then consumes
+ *     at load time instead of the boundary planes of f.  n_steps must be 1.
+ * LB_HALO_PUSH    (default multi-GPU path) as PACKED, but the library itself moves the halos:
+ *     after every step one small kernel copies send_hi -> the +z neighbour's recv_lo and
+ *     send_lo -> the -z neighbour's recv_hi through peer-mapped pointers (CUDA IPC, NVLink) with
+ *     128-bit stores, then performs the neighbour handshake.  The next step kernel consumes the
+ *     received halo straight from recv_* at load time; only at the end of the call is it
+ *     scattered into the population buffer so that f is canonical again.  All buffers are
+ *     double-buffered by step parity ([s & 1]).
+ * LB_HALO_DIRECT  the step kernel stores the crossing populations straight into the neighbours'
+ *     population buffers (peer_up_f / peer_down_f, the buffers matching this rank's f_next [0]
+ *     and f [1]) followed by the handshake.  No staging at all, but 4-byte remote stores.
+ *
+ * Handshake (PUSH, DIRECT): the rank stores the step counter into both neighbours' wait slots
+ * (signal_up / signal_down, peer-mapped) and spins until both of its own slots reached it, so
+ * that step t+1 never reads a halo its neighbour has not delivered, nor overwrites one its
+ * neighbour still reads.  A call performs n_steps + 1 handshakes with the values
+ * epoch+1 .. epoch+n_steps+1; the caller advances epoch by n_steps + 1.  A wait that exceeds
+ * ~10 s sets wait_slots[2] = 1 and gives up instead of hanging the GPU. */
+enum { LB_HALO_PACKED = 1, LB_HALO_PUSH = 2, LB_HALO_DIRECT = 3 };
+
 typedef struct lb_halo {
-  void* hi[2];
-  void* lo[2];
-  int64_t q_stride, line_stride;
-  int64_t hi_offset, lo_offset;
-  int32_t compact;
-  int32_t _pad;
-  uint32_t* signal_up;    /* peer: up neighbour's wait_slots[0] */
-  uint32_t* signal_down;  /* peer: down neighbour's wait_slots[1] */
-  uint32_t* wait_slots;   /* local [4]: [0] written by the down neighbour, [1] by the up neighbour,
-                             [2] set to 1 by the kernel if a wait timed out */
-  uint32_t epoch;         /* counter value before this call; the call performs n_steps + 1
-                             handshakes with values epoch+1 .. epoch+n_steps+1 */
-  uint32_t _pad2;
+  int32_t mode;
+  uint32_t epoch;
+  void* send_hi[2];            /* local packed send buffers                                 */
+  void* send_lo[2];
+  void* recv_lo[2];            /* local: written by the -z neighbour (its hi face)          */
+  void* recv_hi[2];            /* local: written by the +z neighbour (its lo face)          */
+  void* peer_up_recv_lo[2];    /* peer-mapped: the +z neighbour's recv_lo                   */
+  void* peer_down_recv_hi[2];  /* peer-mapped: the -z neighbour's recv_hi                   */
+  void* peer_up_f[2];          /* DIRECT: +z neighbour's buffers matching f_next [0], f [1] */
+  void* peer_down_f[2];
+  uint32_t* signal_up;         /* peer-mapped: +z neighbour's wait_slots[0]                 */
+  uint32_t* signal_down;       /* peer-mapped: -z neighbour's wait_slots[1]                 */
+  uint32_t* wait_slots;        /* local [8]: [0] written by the -z neighbour, [1] by the +z
+                                  neighbour, [2] timeout flag, [3] block counter (scratch)  */
 } lb_halo;
 
 typedef struct lb_fields {

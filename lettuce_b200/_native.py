@@ -20,7 +20,7 @@ LB_COLL_NONE, LB_COLL_BGK, LB_COLL_TRT, LB_COLL_KBC = 0, 1, 2, 3
 LB_BND_BOUNCE_BACK, LB_BND_EQUILIBRIUM = 1, 2
 LB_OBS_ENERGY, LB_OBS_MAXU2, LB_OBS_MASS, LB_OBS_ENSTROPHY, LB_OBS_COUNT = 0, 1, 2, 3, 4
 LB_MAX_BOUNDARIES = 8
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 STENCIL_IDS = {"D2Q9": LB_D2Q9, "D3Q19": LB_D3Q19, "D3Q27": LB_D3Q27}
 DTYPE_IDS = {torch.float32: LB_F32, torch.float64: LB_F64}
@@ -55,12 +55,16 @@ class LbBoundary(C.Structure):
                 ("u_comp_stride", C.c_int64)]
 
 
+LB_HALO_PACKED, LB_HALO_PUSH, LB_HALO_DIRECT = 1, 2, 3
+
+
 class LbHalo(C.Structure):
-    _fields_ = [("hi", C.c_void_p * 2), ("lo", C.c_void_p * 2), ("q_stride", C.c_int64),
-                ("line_stride", C.c_int64), ("hi_offset", C.c_int64), ("lo_offset", C.c_int64),
-                ("compact", C.c_int32), ("_pad", C.c_int32), ("signal_up", C.c_void_p),
-                ("signal_down", C.c_void_p), ("wait_slots", C.c_void_p), ("epoch", C.c_uint32),
-                ("_pad2", C.c_uint32)]
+    _fields_ = [("mode", C.c_int32), ("epoch", C.c_uint32),
+                ("send_hi", C.c_void_p * 2), ("send_lo", C.c_void_p * 2),
+                ("recv_lo", C.c_void_p * 2), ("recv_hi", C.c_void_p * 2),
+                ("peer_up_recv_lo", C.c_void_p * 2), ("peer_down_recv_hi", C.c_void_p * 2),
+                ("peer_up_f", C.c_void_p * 2), ("peer_down_f", C.c_void_p * 2),
+                ("signal_up", C.c_void_p), ("signal_down", C.c_void_p), ("wait_slots", C.c_void_p)]
 
 
 class LbFields(C.Structure):

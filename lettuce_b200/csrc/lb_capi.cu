@@ -6,6 +6,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -148,23 +149,64 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
     LB_CUDA(cudaMemsetAsync(counter, 0, 64, st));
   }
   const lb_halo* h = fl->halo;
+  bool halo_sync = false;
+  const size_t face_elems = size_t(lb::zface_count<S>()) * g.nx * g.ny;
   if (h) {
     if (!do_stream) return fail(LB_EINVAL, "halo given to a collide-only call");
     if (p.sbits) return fail(LB_EUNSUPPORTED, "masked streaming (no_streaming_mask) is not supported across slabs");
-    if (!h->hi[0] || !h->lo[0] || (n_steps > 1 && (!h->hi[1] || !h->lo[1])))
-      return fail(LB_EINVAL, "halo destination is null");
-    p.halo_qs = h->q_stride; p.halo_ls = h->line_stride;
-    p.halo_hi_off = (unsigned)h->hi_offset; p.halo_lo_off = (unsigned)h->lo_offset;
-    p.halo_compact = h->compact;
-    if (h->wait_slots) {
-      rc = lb::launch_halo_sync(h->signal_up, h->signal_down, h->wait_slots, h->epoch + 1u, st);
+    static const bool debug_nosync = getenv("LB_DEBUG_HALO_NOSYNC") != nullptr;  // timing experiments only
+    switch (h->mode) {
+      case LB_HALO_PACKED:
+        if (n_steps > 1) return fail(LB_EINVAL, "LB_HALO_PACKED advances one step per call");
+        if (!h->send_hi[0] || !h->send_lo[0]) return fail(LB_EINVAL, "halo send buffer is null");
+        break;
+      case LB_HALO_PUSH:
+        for (int k = 0; k < 2; ++k)
+          if (!h->send_hi[k] || !h->send_lo[k] || !h->recv_lo[k] || !h->recv_hi[k] ||
+              !h->peer_up_recv_lo[k] || !h->peer_down_recv_hi[k])
+            return fail(LB_EINVAL, "LB_HALO_PUSH needs both parities of every halo buffer");
+        if (!h->wait_slots || !h->signal_up || !h->signal_down) return fail(LB_EINVAL, "LB_HALO_PUSH needs the handshake slots");
+        halo_sync = !debug_nosync;
+        break;
+      case LB_HALO_DIRECT:
+        if (!h->peer_up_f[0] || !h->peer_down_f[0] || (n_steps > 1 && (!h->peer_up_f[1] || !h->peer_down_f[1])))
+          return fail(LB_EINVAL, "LB_HALO_DIRECT needs the neighbours' population buffers");
+        if (!h->wait_slots || !h->signal_up || !h->signal_down) return fail(LB_EINVAL, "LB_HALO_DIRECT needs the handshake slots");
+        halo_sync = !debug_nosync;
+        break;
+      default:
+        return fail(LB_EINVAL, "unknown halo mode %d", h->mode);
+    }
+    if (h->mode == LB_HALO_DIRECT) {
+      p.halo_qs = g.n_nodes; p.halo_ls = g.nz; p.halo_hi_off = 0; p.halo_lo_off = g.nz - 1; p.halo_compact = 0;
+    } else {
+      p.halo_qs = (long long)g.nx * g.ny; p.halo_ls = 1; p.halo_hi_off = 0; p.halo_lo_off = 0; p.halo_compact = 1;
+    }
+    if (halo_sync) {  // everybody has entered the call: the neighbours' buffers are ours to write
+      rc = lb::launch_halo_push(nullptr, nullptr, nullptr, nullptr, 0, h->signal_up, h->signal_down,
+                                h->wait_slots, h->epoch + 1u, st);
       if (rc) return fail(LB_ECUDA, "halo sync launch failed");
     }
   }
   T* a = static_cast<T*>(fl->f);
   T* b = static_cast<T*>(fl->f_next);
   for (int s = 0; s < n_steps; ++s) {
-    if (h) { p.halo_hi = static_cast<T*>(h->hi[s & 1]); p.halo_lo = static_cast<T*>(h->lo[s & 1]); }
+    if (h) {
+      const int k = s & 1;
+      if (h->mode == LB_HALO_DIRECT) {
+        p.halo_hi = static_cast<T*>(h->peer_up_f[k]); p.halo_lo = static_cast<T*>(h->peer_down_f[k]);
+      } else {
+        const int ks = h->mode == LB_HALO_PACKED ? 0 : k;
+        p.halo_hi = static_cast<T*>(h->send_hi[ks]); p.halo_lo = static_cast<T*>(h->send_lo[ks]);
+        if (h->mode == LB_HALO_PUSH && s > 0) {   // consume what the previous step's push delivered
+          p.halo_in_lo = static_cast<const T*>(h->recv_lo[k ^ 1]);
+          p.halo_in_hi = static_cast<const T*>(h->recv_hi[k ^ 1]);
+        } else if (h->mode == LB_HALO_PACKED) {   // optional: a halo received but not yet unpacked
+          p.halo_in_lo = static_cast<const T*>(h->recv_lo[0]);
+          p.halo_in_hi = static_cast<const T*>(h->recv_hi[0]);
+        }
+      }
+    }
     p.f_in = a;
     p.f_out = b;
     c.obs = fl->obs_out != nullptr;
@@ -174,11 +216,25 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
     p.u_out = (c.obs && s == n_steps - 1) ? static_cast<T*>(fl->u_out) : nullptr;
     cudaError_t e = lb::launch_step<S, T>(c, p, st);
     if (e != cudaSuccess) return fail(LB_ECUDA, "step kernel launch failed: %s", cudaGetErrorString(e));
-    if (h && h->wait_slots) {
-      rc = lb::launch_halo_sync(h->signal_up, h->signal_down, h->wait_slots, h->epoch + 2u + (unsigned)s, st);
-      if (rc) return fail(LB_ECUDA, "halo sync launch failed");
+    if (h && h->mode != LB_HALO_PACKED) {
+      const int k = s & 1;
+      const bool push = h->mode == LB_HALO_PUSH;
+      if (push || halo_sync) {
+        rc = lb::launch_halo_push(push ? h->send_hi[k] : nullptr, push ? h->peer_up_recv_lo[k] : nullptr,
+                                  push ? h->send_lo[k] : nullptr, push ? h->peer_down_recv_hi[k] : nullptr,
+                                  push ? face_elems * sizeof(T) : 0, halo_sync ? h->signal_up : nullptr,
+                                  halo_sync ? h->signal_down : nullptr, h->wait_slots,
+                                  h->epoch + 2u + (unsigned)s, st);
+        if (rc) return fail(LB_ECUDA, "halo push launch failed");
+      }
     }
     T* t = a; a = b; b = t;
+  }
+  if (h && h->mode == LB_HALO_PUSH && n_steps > 0) {
+    // make the population buffer canonical again: scatter the last received halo into it
+    const int k = (n_steps - 1) & 1;
+    rc = lb_unpack_halo(d, a, h->recv_lo[k], h->recv_hi[k], st);
+    if (rc) return fail(LB_ECUDA, "halo unpack launch failed");
   }
   return LB_OK;
 }

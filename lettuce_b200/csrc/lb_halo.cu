@@ -1,8 +1,8 @@
 // Neighbour handshake over NVLink peer memory, packed-halo scatter, CUDA IPC helpers.
 //
-// Direct mode (see lb_halo in include/lettuce_b200.h): the step kernel of rank r writes the
-// populations that cross its z faces straight into the boundary planes of its neighbours'
-// output buffers through peer-mapped pointers.  What remains per step is a handshake:
+// Push mode (see lb_halo in include/lettuce_b200.h): the step kernel packs the populations that
+// cross its z faces; halo_push_kernel copies them into the neighbours' receive buffers through
+// peer-mapped pointers and then performs the handshake:
 //   "I finished step t"  ->  st.release.sys into both neighbours' wait slots,
 //   spin (ld.acquire.sys) until both neighbours said the same.
 // After it, (a) the neighbours' stores into our planes are visible, so step t+1 may read them,
@@ -28,10 +28,38 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 // counters only grow; compare with wrap-around safe signed difference
 __device__ __forceinline__ bool reached(uint32_t have, uint32_t want) { return int32_t(have - want) >= 0; }
 
-__global__ void halo_sync_kernel(uint32_t* signal_up, uint32_t* signal_down, uint32_t* wait_slots,
-                                 uint32_t value, long long timeout_cycles) {
-  if (threadIdx.x != 0 || blockIdx.x != 0) return;
-  __threadfence_system();  // order the previous kernel's peer stores before the signal
+constexpr int PUSH_BLOCK = 256;
+constexpr int PUSH_GRID = 32;
+
+// One launch per time step: (1) all blocks copy the packed halos into the neighbours' receive
+// buffers with 16-byte stores (coalesced NVLink writes), (2) the last block to finish signals
+// both neighbours and waits for theirs.  wait_slots[3] is the block counter.
+__global__ void __launch_bounds__(PUSH_BLOCK)
+halo_push_kernel(const uint4* __restrict__ src_hi, uint4* __restrict__ dst_hi,
+                 const uint4* __restrict__ src_lo, uint4* __restrict__ dst_lo, size_t n_vec, size_t tail_bytes,
+                 uint32_t* signal_up, uint32_t* signal_down, uint32_t* wait_slots, uint32_t value,
+                 long long timeout_cycles) {
+  const size_t stride = size_t(gridDim.x) * PUSH_BLOCK;
+  if (src_hi != nullptr)
+    for (size_t i = size_t(blockIdx.x) * PUSH_BLOCK + threadIdx.x; i < n_vec; i += stride) dst_hi[i] = src_hi[i];
+  if (src_lo != nullptr)
+    for (size_t i = size_t(blockIdx.x) * PUSH_BLOCK + threadIdx.x; i < n_vec; i += stride) dst_lo[i] = src_lo[i];
+  if (tail_bytes != 0 && blockIdx.x == 0 && threadIdx.x < tail_bytes / 4) {  // < 16 trailing bytes
+    if (src_hi) reinterpret_cast<uint32_t*>(dst_hi + n_vec)[threadIdx.x] = reinterpret_cast<const uint32_t*>(src_hi + n_vec)[threadIdx.x];
+    if (src_lo) reinterpret_cast<uint32_t*>(dst_lo + n_vec)[threadIdx.x] = reinterpret_cast<const uint32_t*>(src_lo + n_vec)[threadIdx.x];
+  }
+  if (signal_up == nullptr && signal_down == nullptr) return;
+  __shared__ bool is_last;
+  __threadfence_system();   // this thread's peer stores before the block's arrival
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(&wait_slots[3], 1u);
+    is_last = (prev == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last || threadIdx.x != 0) return;
+  wait_slots[3] = 0u;
+  __threadfence_system();   // every block's stores (observed through the counter) before the signal
   if (signal_up) st_release_sys(signal_up, value);
   if (signal_down) st_release_sys(signal_down, value);
   const long long t0 = clock64();
@@ -40,14 +68,21 @@ __global__ void halo_sync_kernel(uint32_t* signal_up, uint32_t* signal_down, uin
       wait_slots[2] = 1u;
       break;
     }
-    __nanosleep(100);
+    __nanosleep(64);
   }
 }
 
-int launch_halo_sync(uint32_t* signal_up, uint32_t* signal_down, uint32_t* wait_slots, uint32_t value,
+int launch_halo_push(const void* src_hi, void* dst_hi, const void* src_lo, void* dst_lo, size_t bytes,
+                     uint32_t* signal_up, uint32_t* signal_down, uint32_t* wait_slots, uint32_t value,
                      cudaStream_t st) {
+  const size_t n_vec = bytes / 16, tail = bytes % 16;
+  const bool copy = bytes != 0 && (src_hi != nullptr || src_lo != nullptr);
+  const int grid = copy ? PUSH_GRID : 1;
   // ~10 s at 2 GHz: far beyond any legitimate skew between neighbours inside one node
-  halo_sync_kernel<<<1, 32, 0, st>>>(signal_up, signal_down, wait_slots, value, 20000000000ll);
+  halo_push_kernel<<<grid, PUSH_BLOCK, 0, st>>>(
+      copy ? static_cast<const uint4*>(src_hi) : nullptr, static_cast<uint4*>(dst_hi),
+      copy ? static_cast<const uint4*>(src_lo) : nullptr, static_cast<uint4*>(dst_lo), n_vec, tail,
+      signal_up, signal_down, wait_slots, value, 20000000000ll);
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 

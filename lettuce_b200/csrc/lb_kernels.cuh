@@ -67,6 +67,12 @@ struct StepParams {
   //   halo_hi / halo_lo [qidx * halo_qs + dest_line * halo_ls + halo_{hi,lo}_off]
   // instead of wrapping around locally.  qidx = q (direct: the base is the neighbour's
   // population buffer, peer-mapped) or the compact z-face index (packed send buffer).
+  // halo_in_*: packed [zface][lines] populations that ARRIVED through the z = 0 face (ez = +1,
+  // from the -z neighbour) / the z = nz-1 face (ez = -1, from the +z neighbour) in the previous
+  // step; when set they replace the corresponding boundary-plane values at load time, so the
+  // received halo never has to be scattered into f between steps.
+  const T* halo_in_lo;
+  const T* halo_in_hi;
   T* halo_hi;
   T* halo_lo;
   long long halo_qs, halo_ls;
@@ -197,6 +203,20 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
   }
   uint32_t mword = 0;
   if constexpr (MODE != MODE_PLAIN) mword = ld_mask<V>(p.ncm + node);
+  if (p.halo_in_lo != nullptr && zv == 0) {
+    const size_t lines = size_t(nx) * ny;
+    static_for<Q>([&](auto qc) {
+      constexpr int q = decltype(qc)::value;
+      if constexpr (S::e(q, 2) == 1) f[q][0] = p.halo_in_lo[zface_index<S>(q) * lines + line];
+    });
+  }
+  if (p.halo_in_hi != nullptr && zv == nzv - 1) {
+    const size_t lines = size_t(nx) * ny;
+    static_for<Q>([&](auto qc) {
+      constexpr int q = decltype(qc)::value;
+      if constexpr (S::e(q, 2) == -1) f[q][V - 1] = p.halo_in_hi[zface_index<S>(q) * lines + line];
+    });
+  }
 
   double acc_e = 0.0, acc_mass = 0.0;
   T acc_m2 = T(0);

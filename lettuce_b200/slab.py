@@ -2,13 +2,17 @@
 owns a contiguous range of the last (contiguous) axis, periodic ring of neighbours.  New work
 defined by BASELINE.json -- the reference is single-device.
 
-Three transports behind one class:
-  'p2p'   the step kernel writes the populations that cross a z face straight into the
-          neighbour's boundary plane through CUDA-IPC peer pointers over NVLink, followed by a
-          one-thread neighbour handshake kernel: compute and exchange in ONE kernel, no
-          pack / copy / unpack, no host involvement between steps.  (default on CUDA)
-  'nccl'  the step kernel packs the crossing populations into send buffers, torch.distributed
-          send/recv moves them, lb_unpack_halo scatters them (the baseline design north_star names).
+Transports behind one class:
+  'p2p'   (default on CUDA, LB_HALO_PUSH) the step kernel packs the populations that cross a z
+          face; one small kernel per step pushes them into the neighbours' receive buffers through
+          CUDA-IPC peer pointers over NVLink (128-bit stores) and does the neighbour handshake;
+          the next step kernel consumes the received halo at load time.  No host involvement
+          between steps: simulation(n) is one C call.
+  'p2p-direct' (LB_HALO_DIRECT) the step kernel stores the crossing populations straight into the
+          neighbours' boundary planes (peer pointers), handshake kernel only.  No staging, but the
+          4-byte remote stores cost more than the push (measured).
+  'nccl'  (LB_HALO_PACKED) packed send buffers, torch.distributed send/recv, lb_unpack_halo:
+          the baseline design north_star names.
   'host'  same exchange logic over any torch.distributed backend with an injected local stepper;
           this is what the world_size-2 gloo tests on CPU drive (tests inject the oracle).
 """
@@ -129,7 +133,7 @@ class SlabSimulation(Simulation):
         self.local_stepper = local_stepper
         if transport is None:
             transport = 'host' if local_stepper is not None else 'p2p'
-        if transport not in ('p2p', 'nccl', 'host'):
+        if transport not in ('p2p', 'p2p-direct', 'nccl', 'host'):
             raise ValueError(transport)
         self.transport = transport
         self._epoch = 0
@@ -152,7 +156,9 @@ class SlabSimulation(Simulation):
             self.lines *= n
         if self.world > 1:
             if transport == 'p2p':
-                self._setup_p2p()
+                self._setup_push()
+            elif transport == 'p2p-direct':
+                self._setup_direct()
             else:
                 self._setup_packed()
 
@@ -172,48 +178,72 @@ class SlabSimulation(Simulation):
         for req in dist.batch_isend_irecv(ops):
             req.wait()
 
-    # ---- direct transport ------------------------------------------------------------------------
-    def _setup_p2p(self):
+    # ---- peer-memory transports ------------------------------------------------------------------
+    def _share(self, mems):
+        """export our IPC allocations, open the neighbours': {rank: [device pointers]}"""
+        handles = [None] * self.world
+        dist.all_gather_object(handles, [m.handle() for m in mems], group=self.group)
+        peer = {}
+        for r in {self.up, self.down}:
+            peer[r] = [_open_handle(h) for h in handles[r]]
+        dist.barrier(group=self.group)
+        return peer
+
+    def _setup_push(self):
+        flow, dev = self.flow, self.flow.f.device
+        shape = [len(self.hi_q), self.lines]
+        with torch.cuda.device(dev):
+            # local send buffers; IPC-visible receive buffers [lo0, lo1, hi0, hi1] + flags
+            self._send = [flow.f.new_zeros(shape) for _ in range(4)]        # hi0 hi1 lo0 lo1
+            recv = [_DeviceMemory(shape, flow.f.dtype) for _ in range(4)]   # lo0 lo1 hi0 hi1
+            flags = _DeviceMemory([8], torch.int32)
+            self._mem = recv + [flags]
+            self._recv = [m.tensor(dev) for m in recv]
+            self._flags = flags.tensor(dev)
+            torch.cuda.synchronize(dev)
+            self._peer = self._share(self._mem)
+
+    def _setup_direct(self):
         flow, dev = self.flow, self.flow.f.device
         with torch.cuda.device(dev):
             bufs = [_DeviceMemory(flow.f.shape, flow.f.dtype) for _ in range(2)]
-            flags = _DeviceMemory([4], torch.int32)
+            flags = _DeviceMemory([8], torch.int32)
             self._mem = bufs + [flags]
             self._buf = [b.tensor(dev) for b in bufs]
             self._buf[0].copy_(flow.f)
             flow.f, flow.f_next = self._buf[0], self._buf[1]
             self._flags = flags.tensor(dev)
             torch.cuda.synchronize(dev)
-            handles = [None] * self.world
-            dist.all_gather_object(handles, [m.handle() for m in self._mem], group=self.group)
-            self._peer = {}
-            for r in {self.up, self.down}:
-                self._peer[r] = [_open_handle(h) for h in handles[r]]
-        dist.barrier(group=self.group)
+            self._peer = self._share(self._mem)
 
     def _halo_struct(self, epoch):
         flow = self.flow
         h = nat.LbHalo()
-        nz = flow.resolution[-1]
+        h.epoch = epoch
         if self.transport == 'p2p':
-            cur = 0 if flow.f.data_ptr() == self._buf[0].data_ptr() else 1
             up, down = self._peer[self.up], self._peer[self.down]
-            # step s writes into f_next (s even) / f (s odd): the neighbour's matching buffers
-            h.hi[0], h.hi[1] = up[1 - cur], up[cur]
-            h.lo[0], h.lo[1] = down[1 - cur], down[cur]
-            h.q_stride, h.line_stride = flow.f[0].numel(), nz
-            h.hi_offset, h.lo_offset = 0, nz - 1
-            h.compact = 0
-            h.signal_up = up[2] + 0          # up neighbour's wait_slots[0] (we are its down neighbour)
-            h.signal_down = down[2] + 4      # down neighbour's wait_slots[1]
-            h.wait_slots = self._flags.data_ptr()
-            h.epoch = epoch
+            h.mode = nat.LB_HALO_PUSH
+            for k in range(2):
+                h.send_hi[k], h.send_lo[k] = self._send[k].data_ptr(), self._send[2 + k].data_ptr()
+                h.recv_lo[k], h.recv_hi[k] = self._recv[k].data_ptr(), self._recv[2 + k].data_ptr()
+                h.peer_up_recv_lo[k] = up[k]            # our hi face lands in the +z neighbour's recv_lo
+                h.peer_down_recv_hi[k] = down[2 + k]    # our lo face lands in the -z neighbour's recv_hi
+            flag_idx = 4
+        elif self.transport == 'p2p-direct':
+            up, down = self._peer[self.up], self._peer[self.down]
+            h.mode = nat.LB_HALO_DIRECT
+            cur = 0 if flow.f.data_ptr() == self._buf[0].data_ptr() else 1
+            # step s writes into f_next (s even) / f (s odd): the neighbours' matching buffers
+            h.peer_up_f[0], h.peer_up_f[1] = up[1 - cur], up[cur]
+            h.peer_down_f[0], h.peer_down_f[1] = down[1 - cur], down[cur]
+            flag_idx = 2
         else:
-            h.hi[0] = h.hi[1] = self.send_hi.data_ptr()
-            h.lo[0] = h.lo[1] = self.send_lo.data_ptr()
-            h.q_stride, h.line_stride = self.lines, 1
-            h.hi_offset = h.lo_offset = 0
-            h.compact = 1
+            h.mode = nat.LB_HALO_PACKED
+            h.send_hi[0], h.send_lo[0] = self.send_hi.data_ptr(), self.send_lo.data_ptr()
+            return h
+        h.signal_up = up[flag_idx] + 0        # +z neighbour's wait_slots[0] (we are its -z neighbour)
+        h.signal_down = down[flag_idx] + 4    # -z neighbour's wait_slots[1]
+        h.wait_slots = self._flags.data_ptr()
         return h
 
     def _fields(self, desc, obs_out=None, u_out=None):
@@ -232,7 +262,7 @@ class SlabSimulation(Simulation):
             return
         if self.world == 1:
             return Simulation._advance(self, n, obs_out, u_out)
-        if self.transport == 'p2p':
+        if self.transport in ('p2p', 'p2p-direct'):
             Simulation._advance(self, n, obs_out, u_out)
             self._epoch += n + 1
             return
@@ -297,13 +327,13 @@ class SlabSimulation(Simulation):
             self.flow.i += num_steps
             return num_steps * self.flow.f[0].numel() * self.world / 1e6 / (timer() - beg)
         mlups_local = Simulation.__call__(self, num_steps)
-        if self.world > 1 and self.transport == 'p2p':
+        if self.world > 1 and self.transport in ('p2p', 'p2p-direct'):
             if int(self._flags[2].item()) != 0:
                 raise RuntimeError("halo handshake timed out: a neighbour rank did not reach the same step")
         return mlups_local * self.world
 
     def close(self):
-        if self.world > 1 and self.transport == 'p2p':
+        if self.world > 1 and self.transport in ('p2p', 'p2p-direct'):
             torch.cuda.synchronize(self.context.device)
             dist.barrier(group=self.group)
             for r, ptrs in self._peer.items():
