@@ -190,6 +190,19 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
   const unsigned node = line * nz + z0;
   const size_t N = p.n_nodes;
 
+  // ---- incoming halo (multi-GPU): issued BEFORE the population loads so that both are in
+  // flight together; a thread is on at most one z face unless the line is a single vector
+  constexpr int NF = zface_count<S>();
+  T hin[NF];
+  const bool in_lo = (p.halo_in_lo != nullptr) && (zv == 0);
+  const bool edge_in = in_lo || ((p.halo_in_hi != nullptr) && (zv == nzv - 1));
+  if (edge_in) {
+    const T* hsrc = (in_lo ? p.halo_in_lo : p.halo_in_hi) + line;
+    const size_t lines = size_t(nx) * ny;
+#pragma unroll
+    for (int k = 0; k < NF; ++k) hin[k] = hsrc[k * lines];
+  }
+
   // ---- load: Q aligned vector loads ------------------------------------------------
   T f[Q][V];
   {
@@ -203,19 +216,18 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
   }
   uint32_t mword = 0;
   if constexpr (MODE != MODE_PLAIN) mword = ld_mask<V>(p.ncm + node);
-  if (p.halo_in_lo != nullptr && zv == 0) {
-    const size_t lines = size_t(nx) * ny;
+  if (edge_in) {
     static_for<Q>([&](auto qc) {
       constexpr int q = decltype(qc)::value;
-      if constexpr (S::e(q, 2) == 1) f[q][0] = p.halo_in_lo[zface_index<S>(q) * lines + line];
+      if constexpr (S::e(q, 2) == 1) { if (in_lo) f[q][0] = hin[zface_index<S>(q)]; }
+      if constexpr (S::e(q, 2) == -1) { if (!in_lo) f[q][V - 1] = hin[zface_index<S>(q)]; }
     });
-  }
-  if (p.halo_in_hi != nullptr && zv == nzv - 1) {
-    const size_t lines = size_t(nx) * ny;
-    static_for<Q>([&](auto qc) {
-      constexpr int q = decltype(qc)::value;
-      if constexpr (S::e(q, 2) == -1) f[q][V - 1] = p.halo_in_hi[zface_index<S>(q) * lines + line];
-    });
+    if (p.halo_in_hi != nullptr && in_lo && nzv == 1) {   // one-vector lines: both faces in one thread
+      static_for<Q>([&](auto qc) {
+        constexpr int q = decltype(qc)::value;
+        if constexpr (S::e(q, 2) == -1) f[q][V - 1] = p.halo_in_hi[zface_index<S>(q) * size_t(nx) * ny + line];
+      });
+    }
   }
 
   double acc_e = 0.0, acc_mass = 0.0;
