@@ -3,14 +3,15 @@ owns a contiguous range of the last (contiguous) axis, periodic ring of neighbou
 defined by BASELINE.json -- the reference is single-device.
 
 Transports behind one class:
-  'p2p'   (default on CUDA, LB_HALO_PUSH) the step kernel packs the populations that cross a z
+  'p2p-push'  (LB_HALO_PUSH) the step kernel packs the populations that cross a z
           face; one small kernel per step pushes them into the neighbours' receive buffers through
           CUDA-IPC peer pointers over NVLink (128-bit stores) and does the neighbour handshake;
           the next step kernel consumes the received halo at load time.  No host involvement
           between steps: simulation(n) is one C call.
-  'p2p-direct' (LB_HALO_DIRECT) the step kernel stores the crossing populations straight into the
-          neighbours' boundary planes (peer pointers), handshake kernel only.  No staging, but the
-          4-byte remote stores cost more than the push (measured).
+  'p2p'   (default on CUDA, LB_HALO_DIRECT) the step kernel itself stores the crossing populations
+          straight into the neighbours' boundary planes through CUDA-IPC peer pointers over NVLink:
+          compute and exchange in ONE kernel, no pack / copy / unpack; a one-block handshake kernel
+          follows each step.  Fastest of the three (measured).
   'nccl'  (LB_HALO_PACKED) packed send buffers, torch.distributed send/recv, lb_unpack_halo:
           the baseline design north_star names.
   'host'  same exchange logic over any torch.distributed backend with an injected local stepper;
@@ -133,7 +134,7 @@ class SlabSimulation(Simulation):
         self.local_stepper = local_stepper
         if transport is None:
             transport = 'host' if local_stepper is not None else 'p2p'
-        if transport not in ('p2p', 'p2p-direct', 'nccl', 'host'):
+        if transport not in ('p2p-push', 'p2p', 'nccl', 'host'):
             raise ValueError(transport)
         self.transport = transport
         self._epoch = 0
@@ -155,9 +156,9 @@ class SlabSimulation(Simulation):
         for n in flow.resolution[:-1]:
             self.lines *= n
         if self.world > 1:
-            if transport == 'p2p':
+            if transport == 'p2p-push':
                 self._setup_push()
-            elif transport == 'p2p-direct':
+            elif transport == 'p2p':
                 self._setup_direct()
             else:
                 self._setup_packed()
@@ -220,7 +221,7 @@ class SlabSimulation(Simulation):
         flow = self.flow
         h = nat.LbHalo()
         h.epoch = epoch
-        if self.transport == 'p2p':
+        if self.transport == 'p2p-push':
             up, down = self._peer[self.up], self._peer[self.down]
             h.mode = nat.LB_HALO_PUSH
             for k in range(2):
@@ -229,7 +230,7 @@ class SlabSimulation(Simulation):
                 h.peer_up_recv_lo[k] = up[k]            # our hi face lands in the +z neighbour's recv_lo
                 h.peer_down_recv_hi[k] = down[2 + k]    # our lo face lands in the -z neighbour's recv_hi
             flag_idx = 4
-        elif self.transport == 'p2p-direct':
+        elif self.transport == 'p2p':
             up, down = self._peer[self.up], self._peer[self.down]
             h.mode = nat.LB_HALO_DIRECT
             cur = 0 if flow.f.data_ptr() == self._buf[0].data_ptr() else 1
@@ -262,7 +263,7 @@ class SlabSimulation(Simulation):
             return
         if self.world == 1:
             return Simulation._advance(self, n, obs_out, u_out)
-        if self.transport in ('p2p', 'p2p-direct'):
+        if self.transport in ('p2p-push', 'p2p'):
             Simulation._advance(self, n, obs_out, u_out)
             self._epoch += n + 1
             return
@@ -327,13 +328,13 @@ class SlabSimulation(Simulation):
             self.flow.i += num_steps
             return num_steps * self.flow.f[0].numel() * self.world / 1e6 / (timer() - beg)
         mlups_local = Simulation.__call__(self, num_steps)
-        if self.world > 1 and self.transport in ('p2p', 'p2p-direct'):
+        if self.world > 1 and self.transport in ('p2p-push', 'p2p'):
             if int(self._flags[2].item()) != 0:
                 raise RuntimeError("halo handshake timed out: a neighbour rank did not reach the same step")
         return mlups_local * self.world
 
     def close(self):
-        if self.world > 1 and self.transport in ('p2p', 'p2p-direct'):
+        if self.world > 1 and self.transport in ('p2p-push', 'p2p'):
             torch.cuda.synchronize(self.context.device)
             dist.barrier(group=self.group)
             for r, ptrs in self._peer.items():
