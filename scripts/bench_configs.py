@@ -1,0 +1,104 @@
+"""MLUPS and HBM-roofline fraction of every BASELINE.json config that fits one GPU, plus a few
+kernel variants.  Device-resident timing with CUDA events (10 warm-up steps, then `steps`).
+
+    python scripts/bench_configs.py [--quick]
+Prints one JSON line per case."""
+import json
+import os
+import sys
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import lettuce_b200 as lt  # noqa: E402
+
+PEAK = 6553.0
+try:
+    PEAK = float(json.load(open(os.path.join(os.path.dirname(__file__), "..", "MEASURED_PEAKS.json")))["hbm_gbs"])
+except Exception:
+    pass
+quick = "--quick" in sys.argv
+
+
+def timed(sim, steps, warm=10):
+    sim(warm)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    sim(steps)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / 1e3
+
+
+def report(name, flow, seconds, steps, extra=None):
+    n = flow.f[0].numel()
+    q = flow.stencil.q
+    esz = flow.f.element_size()
+    mlups = n * steps / 1e6 / seconds
+    gbs = mlups * 1e6 * 2 * q * esz / 1e9
+    line = {"case": name, "mlups": round(mlups, 1), "us_per_step": round(seconds / steps * 1e6, 2),
+            "bytes_per_update": 2 * q * esz, "achieved_gbs": round(gbs, 1), "frac_of_measured_peak": round(gbs / PEAK, 4)}
+    if extra:
+        line.update(extra)
+    print(json.dumps(line), flush=True)
+
+
+def tgv(res, stencil, dtype, collision, re=1600, ma=0.1, reporters=None, steps=100):
+    ctx = lt.Context(device="cuda", dtype=dtype, use_native=True)
+    flow = lt.TaylorGreenVortex(ctx, resolution=res, reynolds_number=re, mach_number=ma, stencil=stencil)
+    tau = flow.units.relaxation_parameter_lu
+    coll = {"bgk": lambda: lt.BGKCollision(tau), "trt": lambda: lt.TRTCollision(tau), "kbc": lambda: lt.KBCCollision(),
+            "none": lambda: lt.NoCollision()}[collision]()
+    reps = reporters(flow) if reporters else []
+    sim = lt.Simulation(flow, coll, reps)
+    return flow, sim, timed(sim, steps)
+
+
+def main():
+    S = 20 if quick else 100
+    # config 1: TGV2D D2Q9 BGK fp64 256^2, 1000 steps (launch-latency bound)
+    flow, sim, t = tgv(256, lt.D2Q9, torch.float64, "bgk", re=100, ma=0.05, steps=1000)
+    report("cfg1 TGV2D D2Q9 BGK f64 256^2 x1000", flow, t, 1000)
+    # config 2 and its neighbours
+    for coll in ("bgk", "trt", "none"):
+        flow, sim, t = tgv(256, lt.D3Q19, torch.float32, coll, steps=S)
+        report(f"cfg2 TGV3D D3Q19 {coll} f32 256^3", flow, t, S)
+        del flow, sim
+    flow, sim, t = tgv(256, lt.D3Q19, torch.float64, "bgk", steps=S)
+    report("TGV3D D3Q19 bgk f64 256^3", flow, t, S)
+    del flow, sim
+    for coll in ("bgk", "kbc"):
+        flow, sim, t = tgv(256, lt.D3Q27, torch.float32, coll, steps=S)
+        report(f"TGV3D D3Q27 {coll} f32 256^3", flow, t, S)
+        del flow, sim
+    # config 3: obstacle 2048x1024 D2Q9 BGK, bounce-back cylinder + equilibrium inlet/outlet
+    for dtype, nm in ((torch.float32, "f32"), (torch.float64, "f64")):
+        ctx = lt.Context(device="cuda", dtype=dtype, use_native=True)
+        flow = lt.Obstacle(ctx, [2048, 1024], reynolds_number=300, mach_number=0.01, domain_length_x=1)
+        x, y = flow.grid
+        flow.mask = ((x - 0.3 * x.max()) ** 2 + (y - 0.5 * y.max()) ** 2) < (0.05 * y.max()) ** 2
+        sim = lt.Simulation(flow, lt.BGKCollision(flow.units.relaxation_parameter_lu), [])
+        t = timed(sim, 5 * S)
+        report(f"cfg3 Obstacle D2Q9 BGK {nm} 2048x1024 (bounce-back + 2 equilibrium)", flow, t, 5 * S)
+        del flow, sim
+    # 2-D large, no masks, for comparison
+    flow, sim, t = tgv([2048, 1024], lt.D2Q9, torch.float32, "bgk", steps=5 * S)
+    report("TGV2D D2Q9 BGK f32 2048x1024 (no masks)", flow, t, 5 * S)
+    del flow, sim
+    # config 4: TGV3D D3Q27 KBC f32 512^3 with the fused energy reporter, interval 1 / 10 / 100 / none
+    if not quick:
+        for interval in (1, 10, 100, None):
+            reps = (lambda fl, k=interval: [lt.ObservableReporter(lt.IncompressibleKineticEnergy(fl), interval=k, out=None)]) \
+                if interval else None
+            flow, sim, t = tgv(512, lt.D3Q27, torch.float32, "kbc", reporters=reps, steps=100)
+            report(f"cfg4 TGV3D D3Q27 KBC f32 512^3 energy reporter interval={interval}", flow, t, 100)
+            del flow, sim
+            torch.cuda.empty_cache()
+        flow, sim, t = tgv(512, lt.D3Q19, torch.float32, "bgk", steps=50)
+        report("TGV3D D3Q19 bgk f32 512^3", flow, t, 50)
+
+
+if __name__ == "__main__":
+    main()
