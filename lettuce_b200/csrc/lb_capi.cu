@@ -82,15 +82,19 @@ lb::CollisionParams<T> make_cp(const lb_desc* d) {
   return cp;
 }
 
-bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+bool aligned_to(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
 
+// nodes per thread along the contiguous axis: the widest of 16 / 8 / 4(8) bytes that divides the
+// line and matches the buffers' alignment.  LB_VEC=<n> overrides the choice (tuning experiments).
 template <typename T>
-int vector_width(const Geometry& g, const void* a, const void* b, bool sbits) {
-  constexpr unsigned VEC = 16 / sizeof(T);
+int vector_width(const lb_desc* d, const Geometry& g, const void* a, const void* b, bool sbits) {
   if (sbits) return 1;
-  if (g.nz % VEC != 0) return 1;
-  if (!aligned16(a) || !aligned16(b)) return 1;
-  return VEC;
+  int cap = 16 / int(sizeof(T));
+  static const char* env = getenv("LB_VEC");
+  if (env && atoi(env) >= 1) cap = atoi(env) < cap ? atoi(env) : cap;
+  for (int v = cap; v > 1; v >>= 1)
+    if (g.nz % unsigned(v) == 0 && aligned_to(a, v * sizeof(T)) && aligned_to(b, v * sizeof(T))) return v;
+  return 1;
 }
 
 template <typename T>
@@ -136,7 +140,7 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   c.collision = d->collision;
   c.mode = p.sbits ? lb::MODE_NCM_SBITS : (p.ncm ? lb::MODE_NCM : lb::MODE_PLAIN);
   c.stream = do_stream;
-  c.vec = do_stream ? vector_width<T>(g, fl->f, fl->f_next, p.sbits != nullptr) : 1;
+  c.vec = do_stream ? vector_width<T>(d, g, fl->f, fl->f_next, p.sbits != nullptr) : 1;
   p.nzv = g.nz / c.vec;
   p.n_threads = g.nx * g.ny * p.nzv;
 
@@ -341,8 +345,9 @@ size_t lb_bytes_per_update(const lb_desc* d) {
 int lb_vector_width(const lb_desc* d, int has_streaming_bits) {
   Geometry g;
   if (check_desc(d, &g)) return -1;
-  const unsigned vec = d->dtype == LB_F64 ? 2 : 4;
-  return (!has_streaming_bits && g.nz % vec == 0) ? int(vec) : 1;
+  static char dummy[16] __attribute__((aligned(16)));
+  return d->dtype == LB_F64 ? vector_width<double>(d, g, dummy, dummy, has_streaming_bits != 0)
+                            : vector_width<float>(d, g, dummy, dummy, has_streaming_bits != 0);
 }
 
 int lb_step(const lb_desc* desc, const lb_fields* fields, int n_steps, void* stream) {

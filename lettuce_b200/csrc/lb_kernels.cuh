@@ -516,6 +516,9 @@ cudaError_t launch_step_impl(const StepConfig& c, const StepParams<T>& p, cudaSt
   constexpr int VEC = 16 / sizeof(T);
   if (c.vec == 1) return launch_vec<S, T, 1>(c, p, st);
   if (c.vec == VEC) return launch_vec<S, T, VEC>(c, p, st);
+  if constexpr (VEC == 4) {
+    if (c.vec == 2) return launch_vec<S, T, 2>(c, p, st);   // 64-bit accesses: nz % 4 == 2, or fewer registers
+  }
   return cudaErrorInvalidValue;
 }
 

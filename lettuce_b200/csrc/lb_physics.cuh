@@ -68,10 +68,23 @@ __device__ __forceinline__ void equilibrium(T rho, const T (&u)[3], T (&feq)[S::
 // ---------------------------------------------------------------------------------------
 // KBC helper: the `s` part of the moment representation (kbc_collision.py:25-94).
 // The reference builds all 27 (9) raw moments with an einsum; only rho and the six (three)
-// second moments enter s, so only those are formed here.
+// second moments enter s, so only those are formed here.  s has 10 (2-D: 5) distinct values:
+//   3-D  s0 | sA (q 1,2) | sB (3,4) | sC (5,6) | +-pyz (7,8 | 9,10) | +-pxz (11,12 | 13,14)
+//        | +-pxy (15,16 | 17,18) | 0 for the corner populations 19..26     (:54-72)
+//   2-D  s0 | sA (q 1,3) | sB (2,4) | +-pxy (5,7 | 6,8)                     (:84-92)
 // ---------------------------------------------------------------------------------------
+template <typename T>
+struct KbcS {
+  T s0, sA, sB, sC, pyz, pxz, pxy;
+};
+
+template <typename T> __device__ __forceinline__ T fast_rcp(T x) { return T(1) / x; }
+// 1 ulp reciprocal (MUFU.RCP): used only for the two sums that set gamma, where the reference's
+// own result is no better conditioned than that (operands are O(w_q), never denormal)
+template <> __device__ __forceinline__ float fast_rcp<float>(float x) { return __fdividef(1.0f, x); }
+
 template <class S, typename T>
-__device__ __forceinline__ void kbc_s(const T (&g)[S::Q], T (&s)[S::Q]) {
+__device__ __forceinline__ KbcS<T> kbc_s(const T (&g)[S::Q]) {
   T r = T(0), mxx = T(0), myy = T(0), mzz = T(0), mxy = T(0), mxz = T(0), myz = T(0);
   static_for<S::Q>([&](auto qc) {
     constexpr int q = decltype(qc)::value;
@@ -90,47 +103,58 @@ __device__ __forceinline__ void kbc_s(const T (&g)[S::Q], T (&s)[S::Q]) {
     if constexpr (ey * ez == 1) myz += g[q];
     if constexpr (ey * ez == -1) myz -= g[q];
   });
-  // m = m / rho ; m[0,0,0] = rho   (kbc_collision.py:27-30, 36-39)
-  mxx /= r; myy /= r; mzz /= r; mxy /= r; mxz /= r; myz /= r;
-  static_for<S::Q>([&](auto qc) { s[decltype(qc)::value] = T(0); });
+  // m = m / rho ; m[0,0,0] = rho   (kbc_collision.py:27-30, 36-39); one reciprocal, six products
+  const T ri = T(1) / r;
+  mxx *= ri; myy *= ri; mzz *= ri; mxy *= ri; mxz *= ri; myz *= ri;
+  KbcS<T> s;
   if constexpr (S::D == 3) {
     // kbc_collision.py:47-72
     const T Tr = mxx + myy + mzz;
     const T Nxz = mxx - mzz;
     const T Nyz = myy - mzz;
     const T sixth = T(1. / 6.), quarter = T(1. / 4);
-    s[0] = r * -Tr;
-    s[1] = sixth * r * (T(2) * Nxz - Nyz + Tr);
-    s[2] = s[1];
-    s[3] = sixth * r * (T(2) * Nyz - Nxz + Tr);
-    s[4] = s[3];
-    s[5] = sixth * r * (-Nxz - Nyz + Tr);
-    s[6] = s[5];
-    s[7] = quarter * r * myz;
-    s[8] = s[7];
-    s[9] = -quarter * r * myz;
-    s[10] = s[9];
-    s[11] = quarter * r * mxz;
-    s[12] = s[11];
-    s[13] = -quarter * r * mxz;
-    s[14] = s[13];
-    s[15] = quarter * r * mxy;
-    s[16] = s[15];
-    s[17] = -quarter * r * mxy;
-    s[18] = s[17];
+    s.s0 = r * -Tr;
+    s.sA = sixth * r * (T(2) * Nxz - Nyz + Tr);
+    s.sB = sixth * r * (T(2) * Nyz - Nxz + Tr);
+    s.sC = sixth * r * (-Nxz - Nyz + Tr);
+    s.pyz = quarter * r * myz;
+    s.pxz = quarter * r * mxz;
+    s.pxy = quarter * r * mxy;
   } else {
     // kbc_collision.py:79-92
     const T Tr = mxx + myy;
     const T N = mxx - myy;
-    s[0] = r * -Tr;
-    s[1] = T(0.5) * r * (T(0.5) * (Tr + N));
-    s[2] = T(0.5) * r * (T(0.5) * (Tr - N));
-    s[3] = s[1];
-    s[4] = s[2];
-    s[5] = T(0.25) * r * mxy;
-    s[6] = -s[5];
-    s[7] = s[5];
-    s[8] = -s[7];
+    s.s0 = r * -Tr;
+    s.sA = T(0.5) * r * (T(0.5) * (Tr + N));
+    s.sB = T(0.5) * r * (T(0.5) * (Tr - N));
+    s.sC = T(0);
+    s.pyz = T(0);
+    s.pxz = T(0);
+    s.pxy = T(0.25) * r * mxy;
+  }
+  return s;
+}
+
+// delta_s of population q from the distinct differences
+template <class S, typename T, int q>
+__device__ __forceinline__ T kbc_ds(const KbcS<T>& d) {
+  if constexpr (q == 0) return d.s0;
+  if constexpr (S::D == 3) {
+    if constexpr (q == 1 || q == 2) return d.sA;
+    else if constexpr (q == 3 || q == 4) return d.sB;
+    else if constexpr (q == 5 || q == 6) return d.sC;
+    else if constexpr (q == 7 || q == 8) return d.pyz;
+    else if constexpr (q == 9 || q == 10) return -d.pyz;
+    else if constexpr (q == 11 || q == 12) return d.pxz;
+    else if constexpr (q == 13 || q == 14) return -d.pxz;
+    else if constexpr (q == 15 || q == 16) return d.pxy;
+    else if constexpr (q == 17 || q == 18) return -d.pxy;
+    else return T(0);
+  } else {
+    if constexpr (q == 1 || q == 3) return d.sA;
+    else if constexpr (q == 2 || q == 4) return d.sB;
+    else if constexpr (q == 5 || q == 7) return d.pxy;
+    else return -d.pxy;
   }
 }
 
@@ -152,37 +176,45 @@ __device__ __forceinline__ void collide_node(T (&f)[S::Q], T rho, const T (&u)[3
         f[q] = f[q] - cp.omega * (f[q] - feq[q]);
       });
     } else if constexpr (COLL == COLL_TRT) {
-      // trt_collision.py:20-26
-      T out[S::Q];
+      // trt_collision.py:20-26, evaluated once per opposite pair (q, o): with
+      //   sp = ((f_q + f_o) - (feq_q + feq_o)) / (2 tau+),  sm = ((f_q - f_o) - (feq_q - feq_o)) / (2 tau-)
+      // the reference's values are f_q - (sp + sm) and f_o - (sp - sm): identical bit for bit, since
+      // the symmetric part is commutative and the antisymmetric part changes sign exactly.
       static_for<S::Q>([&](auto qc) {
         constexpr int q = decltype(qc)::value;
         constexpr int o = S::opp(q);
-        T d = ((f[q] + f[o]) - (feq[q] + feq[o])) * cp.inv_2tau_p;
-        d += ((f[q] - f[o]) - (feq[q] - feq[o])) * cp.inv_2tau_m;
-        out[q] = f[q] - d;
+        if constexpr (q <= o) {
+          const T sp = ((f[q] + f[o]) - (feq[q] + feq[o])) * cp.inv_2tau_p;
+          const T sm = ((f[q] - f[o]) - (feq[q] - feq[o])) * cp.inv_2tau_m;
+          const T fq = f[q], fo = f[o];
+          f[q] = fq - (sp + sm);
+          if constexpr (q < o) f[o] = fo - (sp - sm);
+        }
       });
-      static_for<S::Q>([&](auto qc) { f[decltype(qc)::value] = out[decltype(qc)::value]; });
     } else {
       // kbc_collision.py:131-158
       static_assert(S::ID != 1, "KBC is defined for D2Q9 and D3Q27 only (kbc_collision.py:101,115)");
-      T ds[S::Q], se[S::Q];
-      kbc_s<S, T>(f, ds);
-      kbc_s<S, T>(feq, se);
+      const KbcS<T> sf = kbc_s<S, T>(f);
+      const KbcS<T> se = kbc_s<S, T>(feq);
+      KbcS<T> d;   // delta_s = s(f) - s(feq), per distinct value
+      d.s0 = sf.s0 - se.s0; d.sA = sf.sA - se.sA; d.sB = sf.sB - se.sB; d.sC = sf.sC - se.sC;
+      d.pyz = sf.pyz - se.pyz; d.pxz = sf.pxz - se.pxz; d.pxy = sf.pxy - se.pxy;
       T sum_s = T(0), sum_h = T(0);
       T dh[S::Q];
       static_for<S::Q>([&](auto qc) {
         constexpr int q = decltype(qc)::value;
-        ds[q] = ds[q] - se[q];
-        dh[q] = f[q] - feq[q] - ds[q];
-        sum_s += ds[q] * dh[q] / feq[q];
-        sum_h += dh[q] * dh[q] / feq[q];
+        const T ds = kbc_ds<S, T, q>(d);
+        dh[q] = f[q] - feq[q] - ds;
+        const T w = dh[q] * fast_rcp<T>(feq[q]);   // (ds dh / feq, dh dh / feq) share 1 / feq
+        sum_s += ds * w;
+        sum_h += dh[q] * w;
       });
       T gamma = cp.inv_beta - (T(2) - cp.inv_beta) * sum_s / sum_h;
       if (gamma < T(1E-15)) gamma = T(2);   // :154
       if (gamma != gamma) gamma = T(2);     // NaN guard :156
       static_for<S::Q>([&](auto qc) {
         constexpr int q = decltype(qc)::value;
-        f[q] = f[q] - cp.beta * (T(2) * ds[q] + gamma * dh[q]);
+        f[q] = f[q] - cp.beta * (T(2) * kbc_ds<S, T, q>(d) + gamma * dh[q]);
       });
     }
   }
