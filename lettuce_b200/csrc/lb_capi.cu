@@ -140,6 +140,7 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   c.collision = d->collision;
   c.mode = p.sbits ? lb::MODE_NCM_SBITS : (p.ncm ? lb::MODE_NCM : lb::MODE_PLAIN);
   c.stream = do_stream;
+  c.halo = fl->halo != nullptr;
   c.vec = do_stream ? vector_width<T>(d, g, fl->f, fl->f_next, p.sbits != nullptr) : 1;
   p.nzv = g.nz / c.vec;
   p.n_threads = g.nx * g.ny * p.nzv;

@@ -1,0 +1,6 @@
+// explicit instantiation of the step kernels for D3Q19 f64, collision none
+#include "lb_kernels.cuh"
+namespace lb {
+LB_INSTANTIATE_COLL(D3Q19, double, 0)
+LB_INSTANTIATE_MOMENTS(D3Q19, double)
+}

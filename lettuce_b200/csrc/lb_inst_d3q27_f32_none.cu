@@ -1,0 +1,6 @@
+// explicit instantiation of the step kernels for D3Q27 f32, collision none
+#include "lb_kernels.cuh"
+namespace lb {
+LB_INSTANTIATE_COLL(D3Q27, float, 0)
+LB_INSTANTIATE_MOMENTS(D3Q27, float)
+}

@@ -172,8 +172,13 @@ __device__ __forceinline__ void reduce_observables(double e, double m2, double m
   }
 }
 
-template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM>
-__global__ void __launch_bounds__(STEP_BLOCK)
+// D3Q27 fp32 with 4 nodes per thread holds 108 population registers; asking for 3 resident blocks
+// (<= 168 registers) keeps the fused-reduction variants at the occupancy of the plain ones.
+template <class S, typename T, int V>
+constexpr int step_min_blocks() { return (S::Q == 27 && sizeof(T) == 4 && V == 4) ? 3 : 1; }
+
+template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO>
+__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V>())
 step_kernel(const __grid_constant__ StepParams<T> p) {
   static_assert(MODE != MODE_NCM_SBITS || V == 1, "masked streaming runs one node per thread");
   constexpr int Q = S::Q;
@@ -194,8 +199,8 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
   // flight together; a thread is on at most one z face unless the line is a single vector
   constexpr int NF = zface_count<S>();
   T hin[NF];
-  const bool in_lo = (p.halo_in_lo != nullptr) && (zv == 0);
-  const bool edge_in = in_lo || ((p.halo_in_hi != nullptr) && (zv == nzv - 1));
+  const bool in_lo = HALO && (p.halo_in_lo != nullptr) && (zv == 0);
+  const bool edge_in = HALO && (in_lo || ((p.halo_in_hi != nullptr) && (zv == nzv - 1)));
   if (edge_in) {
     const T* hsrc = (in_lo ? p.halo_in_lo : p.halo_in_hi) + line;
     const size_t lines = size_t(nx) * ny;
@@ -230,9 +235,7 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
     }
   }
 
-  double acc_e = 0.0, acc_mass = 0.0;
-  T acc_m2 = T(0);
-  T uo[3][V];
+  T acc_e = T(0), acc_mass = T(0), acc_m2 = T(0);   // per-thread partials over V nodes; widened below
 
   // ---- collide / boundaries, node by node, all in registers -------------------------
 #pragma unroll
@@ -244,10 +247,13 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
     if (OBS || (COLL != COLL_NONE && m == 0)) moments<S, T>(g, rho, u);
     if constexpr (OBS) {
       const T u2 = u[0] * u[0] + u[1] * u[1] + u[2] * u[2];
-      acc_e += double(T(0.5) * u2);
+      acc_e += T(0.5) * u2;
       acc_m2 = max(acc_m2, u2);
-      acc_mass += double(rho);
-      uo[0][k] = u[0]; uo[1][k] = u[1]; uo[2][k] = u[2];
+      acc_mass += rho;
+      if (p.u_out != nullptr && active) {   // only on steps that feed the enstrophy kernel
+#pragma unroll
+        for (int c = 0; c < S::D; ++c) p.u_out[c * N + node + k] = u[S::axis(c)];
+      }
     }
     if (m == 0) {
       collide_node<S, T, COLL>(g, rho, u, p.cp);
@@ -269,18 +275,6 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
       }
     }
     static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
-  }
-
-  if constexpr (OBS) {
-    if (p.u_out != nullptr && active) {
-#pragma unroll
-      for (int c = 0; c < S::D; ++c) {
-        Vec<T, V> v;
-#pragma unroll
-        for (int k = 0; k < V; ++k) v.v[k] = uo[S::axis(c)][k];
-        st_vec<T, V>(p.u_out + c * N + node, v);
-      }
-    }
   }
 
   // ---- stream: push to (x + ex, y + ey, z + ez), periodic -----------------------------
@@ -336,7 +330,7 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
         const unsigned zd = (ez > 0) ? (crosses ? 0u : z0 + 1) : (crosses ? nz - 1 : z0 - 1);
         if (active) {
           T* hp = (ez > 0) ? p.halo_hi : p.halo_lo;
-          if (crosses && hp != nullptr)
+          if (HALO && crosses && hp != nullptr)
             hp[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs + (long long)(xd * ny + yd) * p.halo_ls +
                ((ez > 0) ? p.halo_hi_off : p.halo_lo_off)] = f[q][0];
           else
@@ -357,7 +351,7 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
             for (int k = 1; k < V; ++k) dst[z0 + k] = f[q][k - 1];
           }
           if (lane == 31 || last_in_line) {
-            if (last_in_line && p.halo_hi != nullptr)
+            if (HALO && last_in_line && p.halo_hi != nullptr)
               p.halo_hi[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs +
                         (long long)(xd * ny + yd) * p.halo_ls + p.halo_hi_off] = f[q][V - 1];
             else
@@ -379,7 +373,7 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
             for (int k = 0; k < V - 1; ++k) dst[z0 + k] = f[q][k + 1];
           }
           if (lane == 0 || first_in_line) {
-            if (first_in_line && p.halo_lo != nullptr)
+            if (HALO && first_in_line && p.halo_lo != nullptr)
               p.halo_lo[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs +
                         (long long)(xd * ny + yd) * p.halo_ls + p.halo_lo_off] = f[q][0];
             else
@@ -391,8 +385,8 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
   }
 
   if constexpr (OBS) {
-    if (!active) { acc_e = 0.0; acc_m2 = T(0); acc_mass = 0.0; }
-    reduce_observables<STEP_BLOCK>(acc_e, double(acc_m2), acc_mass, p.obs_partials,
+    if (!active) { acc_e = T(0); acc_m2 = T(0); acc_mass = T(0); }
+    reduce_observables<STEP_BLOCK>(double(acc_e), double(acc_m2), double(acc_mass), p.obs_partials,
                                    p.obs_counter, p.obs_out);
   }
 }
@@ -457,20 +451,36 @@ cudaError_t launch_moments_impl(const MomentsParams<T>& p, cudaStream_t st) {
 // host-side dispatch (runtime descriptor -> template instantiation), one per (stencil, T)
 // --------------------------------------------------------------------------------------
 struct StepConfig {
-  int vec;        // 1 or 16/sizeof(T)
+  int vec;        // nodes per thread: 16 / 8 / 4(8) bytes
   int collision;  // COLL_*
   int mode;       // MODE_*
   bool obs;
   bool stream;
+  bool halo;      // z-slab halo plumbing compiled in (multi-GPU)
 };
 
-template <class S, typename T>
-cudaError_t launch_step(const StepConfig& c, const StepParams<T>& p, cudaStream_t st);
+// one explicit specialisation per (stencil, dtype, collision), each in its own translation unit
+// (lb_inst_*.cu) so that `make -j` spreads the ~400 kernel variants over all cores
+template <class S, typename T, int COLL>
+cudaError_t launch_step_coll(const StepConfig& c, const StepParams<T>& p, cudaStream_t st);
 
-template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM>
+template <class S, typename T>
+cudaError_t launch_step(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+  switch (c.collision) {
+    case COLL_NONE: return launch_step_coll<S, T, COLL_NONE>(c, p, st);
+    case COLL_BGK: return launch_step_coll<S, T, COLL_BGK>(c, p, st);
+    case COLL_TRT: return launch_step_coll<S, T, COLL_TRT>(c, p, st);
+    case COLL_KBC:
+      if constexpr (S::ID != 1) return launch_step_coll<S, T, COLL_KBC>(c, p, st);
+      else return cudaErrorNotSupported;
+  }
+  return cudaErrorInvalidValue;
+}
+
+template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO>
 cudaError_t launch_one(const StepParams<T>& p, cudaStream_t st) {
   const unsigned grid = (p.n_threads + STEP_BLOCK - 1) / STEP_BLOCK;
-  step_kernel<S, T, V, COLL, MODE, OBS, STREAM><<<grid, STEP_BLOCK, 0, st>>>(p);
+  step_kernel<S, T, V, COLL, MODE, OBS, STREAM, HALO><<<grid, STEP_BLOCK, 0, st>>>(p);
   return cudaGetLastError();
 }
 
@@ -478,16 +488,24 @@ template <class S, typename T, int V, int COLL, int MODE>
 cudaError_t launch_mode(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   if (!c.stream) {
     if constexpr (V == 1 && MODE != MODE_NCM_SBITS)
-      return launch_one<S, T, V, COLL, MODE, false, false>(p, st);
+      return launch_one<S, T, V, COLL, MODE, false, false, false>(p, st);
     else
       return cudaErrorInvalidValue;
   }
-  if (c.obs) return launch_one<S, T, V, COLL, MODE, true, true>(p, st);
-  return launch_one<S, T, V, COLL, MODE, false, true>(p, st);
+  if (c.halo) {
+    if constexpr (MODE != MODE_NCM_SBITS) {
+      if (c.obs) return launch_one<S, T, V, COLL, MODE, true, true, true>(p, st);
+      return launch_one<S, T, V, COLL, MODE, false, true, true>(p, st);
+    } else {
+      return cudaErrorNotSupported;
+    }
+  }
+  if (c.obs) return launch_one<S, T, V, COLL, MODE, true, true, false>(p, st);
+  return launch_one<S, T, V, COLL, MODE, false, true, false>(p, st);
 }
 
 template <class S, typename T, int V, int COLL>
-cudaError_t launch_coll(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+cudaError_t launch_vec(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   switch (c.mode) {
     case MODE_PLAIN: return launch_mode<S, T, V, COLL, MODE_PLAIN>(c, p, st);
     case MODE_NCM: return launch_mode<S, T, V, COLL, MODE_NCM>(c, p, st);
@@ -498,36 +516,25 @@ cudaError_t launch_coll(const StepConfig& c, const StepParams<T>& p, cudaStream_
   return cudaErrorInvalidValue;
 }
 
-template <class S, typename T, int V>
-cudaError_t launch_vec(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
-  switch (c.collision) {
-    case COLL_NONE: return launch_coll<S, T, V, COLL_NONE>(c, p, st);
-    case COLL_BGK: return launch_coll<S, T, V, COLL_BGK>(c, p, st);
-    case COLL_TRT: return launch_coll<S, T, V, COLL_TRT>(c, p, st);
-    case COLL_KBC:
-      if constexpr (S::ID != 1) return launch_coll<S, T, V, COLL_KBC>(c, p, st);
-      else return cudaErrorNotSupported;
-  }
-  return cudaErrorInvalidValue;
-}
-
-template <class S, typename T>
-cudaError_t launch_step_impl(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+template <class S, typename T, int COLL>
+cudaError_t launch_step_coll_impl(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   constexpr int VEC = 16 / sizeof(T);
-  if (c.vec == 1) return launch_vec<S, T, 1>(c, p, st);
-  if (c.vec == VEC) return launch_vec<S, T, VEC>(c, p, st);
+  if (c.vec == 1) return launch_vec<S, T, 1, COLL>(c, p, st);
+  if (c.vec == VEC) return launch_vec<S, T, VEC, COLL>(c, p, st);
   if constexpr (VEC == 4) {
-    if (c.vec == 2) return launch_vec<S, T, 2>(c, p, st);   // 64-bit accesses: nz % 4 == 2, or fewer registers
+    if (c.vec == 2) return launch_vec<S, T, 2, COLL>(c, p, st);   // 64-bit accesses: nz % 4 == 2
   }
   return cudaErrorInvalidValue;
 }
 
-#define LB_INSTANTIATE(S, T)                                                              \
+#define LB_INSTANTIATE_COLL(S, T, COLL)                                                   \
   template <>                                                                             \
-  cudaError_t lb::launch_step<S, T>(const StepConfig& c, const StepParams<T>& p,          \
-                                    cudaStream_t st) {                                    \
-    return launch_step_impl<S, T>(c, p, st);                                              \
-  }                                                                                       \
+  cudaError_t lb::launch_step_coll<S, T, COLL>(const StepConfig& c, const StepParams<T>& p, \
+                                               cudaStream_t st) {                         \
+    return launch_step_coll_impl<S, T, COLL>(c, p, st);                                   \
+  }
+
+#define LB_INSTANTIATE_MOMENTS(S, T)                                                      \
   template <>                                                                             \
   cudaError_t lb::launch_moments<S, T>(const MomentsParams<T>& p, cudaStream_t st) {      \
     return launch_moments_impl<S, T>(p, st);                                              \

@@ -81,31 +81,15 @@ struct KbcS {
 template <typename T> __device__ __forceinline__ T fast_rcp(T x) { return T(1) / x; }
 // 1 ulp reciprocal (MUFU.RCP): used only for the two sums that set gamma, where the reference's
 // own result is no better conditioned than that (operands are O(w_q), never denormal)
-template <> __device__ __forceinline__ float fast_rcp<float>(float x) { return __fdividef(1.0f, x); }
+template <> __device__ __forceinline__ float fast_rcp<float>(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));   // one MUFU.RCP, no range fix-up
+  return r;
+}
 
+// s from rho and the second moments ALREADY divided by rho
 template <class S, typename T>
-__device__ __forceinline__ KbcS<T> kbc_s(const T (&g)[S::Q]) {
-  T r = T(0), mxx = T(0), myy = T(0), mzz = T(0), mxy = T(0), mxz = T(0), myz = T(0);
-  static_for<S::Q>([&](auto qc) {
-    constexpr int q = decltype(qc)::value;
-    // lattice axes (x, y[, z]) -> kernel axes
-    constexpr int ex = S::e(q, S::axis(0));
-    constexpr int ey = S::e(q, S::axis(1));
-    constexpr int ez = (S::D == 3) ? S::e(q, S::axis(S::D == 3 ? 2 : 0)) : 0;
-    r += g[q];
-    if constexpr (ex * ex == 1) mxx += g[q];
-    if constexpr (ey * ey == 1) myy += g[q];
-    if constexpr (ez * ez == 1) mzz += g[q];
-    if constexpr (ex * ey == 1) mxy += g[q];
-    if constexpr (ex * ey == -1) mxy -= g[q];
-    if constexpr (ex * ez == 1) mxz += g[q];
-    if constexpr (ex * ez == -1) mxz -= g[q];
-    if constexpr (ey * ez == 1) myz += g[q];
-    if constexpr (ey * ez == -1) myz -= g[q];
-  });
-  // m = m / rho ; m[0,0,0] = rho   (kbc_collision.py:27-30, 36-39); one reciprocal, six products
-  const T ri = T(1) / r;
-  mxx *= ri; myy *= ri; mzz *= ri; mxy *= ri; mxz *= ri; myz *= ri;
+__device__ __forceinline__ KbcS<T> kbc_s_from_moments(T r, T mxx, T myy, T mzz, T mxy, T mxz, T myz) {
   KbcS<T> s;
   if constexpr (S::D == 3) {
     // kbc_collision.py:47-72
@@ -133,6 +117,46 @@ __device__ __forceinline__ KbcS<T> kbc_s(const T (&g)[S::Q]) {
     s.pxy = T(0.25) * r * mxy;
   }
   return s;
+}
+
+// s(f): second moments by summation, m = m / rho (kbc_collision.py:27-30, 36-39)
+template <class S, typename T>
+__device__ __forceinline__ KbcS<T> kbc_s(const T (&g)[S::Q]) {
+  T r = T(0), mxx = T(0), myy = T(0), mzz = T(0), mxy = T(0), mxz = T(0), myz = T(0);
+  static_for<S::Q>([&](auto qc) {
+    constexpr int q = decltype(qc)::value;
+    // lattice axes (x, y[, z]) -> kernel axes
+    constexpr int ex = S::e(q, S::axis(0));
+    constexpr int ey = S::e(q, S::axis(1));
+    constexpr int ez = (S::D == 3) ? S::e(q, S::axis(S::D == 3 ? 2 : 0)) : 0;
+    r += g[q];
+    if constexpr (ex * ex == 1) mxx += g[q];
+    if constexpr (ey * ey == 1) myy += g[q];
+    if constexpr (ez * ez == 1) mzz += g[q];
+    if constexpr (ex * ey == 1) mxy += g[q];
+    if constexpr (ex * ey == -1) mxy -= g[q];
+    if constexpr (ex * ez == 1) mxz += g[q];
+    if constexpr (ex * ez == -1) mxz -= g[q];
+    if constexpr (ey * ez == 1) myz += g[q];
+    if constexpr (ey * ez == -1) myz -= g[q];
+  });
+  const T ri = T(1) / r;   // one reciprocal, six products
+  return kbc_s_from_moments<S, T>(r, mxx * ri, myy * ri, mzz * ri, mxy * ri, mxz * ri, myz * ri);
+}
+
+// s(feq) in closed form.  The reference sums e_a e_b feq_q numerically (kbc_collision.py:146-147);
+// for the quadratic equilibrium on D2Q9 / D3Q27 those sums are, identically,
+//   sum_q feq_q = rho   and   sum_q e_a e_b feq_q / rho = cs^2 delta_ab + u_a u_b ,
+// so the closed form differs from the reference's sums only by their round-off (a few ulp of
+// rho), the same size as the difference between any two summation orders.  It removes a second
+// 27-term moment pass per node from a kernel that is instruction-issue bound.
+template <class S, typename T>
+__device__ __forceinline__ KbcS<T> kbc_s_equilibrium(T rho, const T (&u)[3]) {
+  constexpr T cs2 = T(LB_CS2);
+  const T ux = u[S::axis(0)], uy = u[S::axis(1)];
+  const T uz = (S::D == 3) ? u[S::axis(S::D == 3 ? 2 : 0)] : T(0);
+  return kbc_s_from_moments<S, T>(rho, cs2 + ux * ux, cs2 + uy * uy, (S::D == 3) ? cs2 + uz * uz : T(0),
+                                  ux * uy, ux * uz, uy * uz);
 }
 
 // delta_s of population q from the distinct differences
@@ -195,7 +219,7 @@ __device__ __forceinline__ void collide_node(T (&f)[S::Q], T rho, const T (&u)[3
       // kbc_collision.py:131-158
       static_assert(S::ID != 1, "KBC is defined for D2Q9 and D3Q27 only (kbc_collision.py:101,115)");
       const KbcS<T> sf = kbc_s<S, T>(f);
-      const KbcS<T> se = kbc_s<S, T>(feq);
+      const KbcS<T> se = kbc_s_equilibrium<S, T>(rho, u);
       KbcS<T> d;   // delta_s = s(f) - s(feq), per distinct value
       d.s0 = sf.s0 - se.s0; d.sA = sf.sA - se.sA; d.sB = sf.sB - se.sB; d.sC = sf.sC - se.sC;
       d.pyz = sf.pyz - se.pyz; d.pxz = sf.pxz - se.pxz; d.pxy = sf.pxy - se.pxy;

@@ -19,6 +19,7 @@ try:
 except Exception:
     pass
 quick = "--quick" in sys.argv
+only = [a.split("=", 1)[1] for a in sys.argv if a.startswith("--only=")]
 
 
 def timed(sim, steps, warm=10):
@@ -30,6 +31,10 @@ def timed(sim, steps, warm=10):
     e1.record()
     torch.cuda.synchronize()
     return e0.elapsed_time(e1) / 1e3
+
+
+def wanted(name):
+    return not only or any(o in name for o in only)
 
 
 def report(name, flow, seconds, steps, extra=None):
@@ -45,6 +50,17 @@ def report(name, flow, seconds, steps, extra=None):
     print(json.dumps(line), flush=True)
 
 
+def tgv_case(name, res, stencil, dtype, collision, steps, **kw):
+    import gc
+    if not wanted(name):
+        return
+    flow, sim, t = tgv(res, stencil, dtype, collision, steps=steps, **kw)
+    report(name, flow, t, steps)
+    del flow, sim
+    gc.collect()
+    torch.cuda.empty_cache()
+
+
 def tgv(res, stencil, dtype, collision, re=1600, ma=0.1, reporters=None, steps=100):
     ctx = lt.Context(device="cuda", dtype=dtype, use_native=True)
     flow = lt.TaylorGreenVortex(ctx, resolution=res, reynolds_number=re, mach_number=ma, stencil=stencil)
@@ -57,47 +73,41 @@ def tgv(res, stencil, dtype, collision, re=1600, ma=0.1, reporters=None, steps=1
 
 
 def main():
+    import gc
     S = 20 if quick else 100
     # config 1: TGV2D D2Q9 BGK fp64 256^2, 1000 steps (launch-latency bound)
-    flow, sim, t = tgv(256, lt.D2Q9, torch.float64, "bgk", re=100, ma=0.05, steps=1000)
-    report("cfg1 TGV2D D2Q9 BGK f64 256^2 x1000", flow, t, 1000)
+    tgv_case("cfg1 TGV2D D2Q9 BGK f64 256^2 x1000", 256, lt.D2Q9, torch.float64, "bgk", 1000, re=100, ma=0.05)
     # config 2 and its neighbours
     for coll in ("bgk", "trt", "none"):
-        flow, sim, t = tgv(256, lt.D3Q19, torch.float32, coll, steps=S)
-        report(f"cfg2 TGV3D D3Q19 {coll} f32 256^3", flow, t, S)
-        del flow, sim
-    flow, sim, t = tgv(256, lt.D3Q19, torch.float64, "bgk", steps=S)
-    report("TGV3D D3Q19 bgk f64 256^3", flow, t, S)
-    del flow, sim
-    for coll in ("bgk", "kbc"):
-        flow, sim, t = tgv(256, lt.D3Q27, torch.float32, coll, steps=S)
-        report(f"TGV3D D3Q27 {coll} f32 256^3", flow, t, S)
-        del flow, sim
+        tgv_case(f"cfg2 TGV3D D3Q19 {coll} f32 256^3", 256, lt.D3Q19, torch.float32, coll, S)
+    tgv_case("TGV3D D3Q19 bgk f64 256^3", 256, lt.D3Q19, torch.float64, "bgk", S)
+    for coll in ("bgk", "trt", "kbc"):
+        tgv_case(f"TGV3D D3Q27 {coll} f32 256^3", 256, lt.D3Q27, torch.float32, coll, S)
+    tgv_case("TGV3D D3Q27 kbc f64 256^3", 256, lt.D3Q27, torch.float64, "kbc", S)
     # config 3: obstacle 2048x1024 D2Q9 BGK, bounce-back cylinder + equilibrium inlet/outlet
     for dtype, nm in ((torch.float32, "f32"), (torch.float64, "f64")):
+        name = f"cfg3 Obstacle D2Q9 BGK {nm} 2048x1024 (bounce-back + 2 equilibrium)"
+        if not wanted(name):
+            continue
         ctx = lt.Context(device="cuda", dtype=dtype, use_native=True)
         flow = lt.Obstacle(ctx, [2048, 1024], reynolds_number=300, mach_number=0.01, domain_length_x=1)
         x, y = flow.grid
         flow.mask = ((x - 0.3 * x.max()) ** 2 + (y - 0.5 * y.max()) ** 2) < (0.05 * y.max()) ** 2
         sim = lt.Simulation(flow, lt.BGKCollision(flow.units.relaxation_parameter_lu), [])
         t = timed(sim, 5 * S)
-        report(f"cfg3 Obstacle D2Q9 BGK {nm} 2048x1024 (bounce-back + 2 equilibrium)", flow, t, 5 * S)
+        report(name, flow, t, 5 * S)
         del flow, sim
-    # 2-D large, no masks, for comparison
-    flow, sim, t = tgv([2048, 1024], lt.D2Q9, torch.float32, "bgk", steps=5 * S)
-    report("TGV2D D2Q9 BGK f32 2048x1024 (no masks)", flow, t, 5 * S)
-    del flow, sim
+        gc.collect()
+    tgv_case("TGV2D D2Q9 BGK f32 2048x1024 (no masks)", [2048, 1024], lt.D2Q9, torch.float32, "bgk", 5 * S)
+    tgv_case("TGV2D D2Q9 KBC f32 2048x1024", [2048, 1024], lt.D2Q9, torch.float32, "kbc", 5 * S)
     # config 4: TGV3D D3Q27 KBC f32 512^3 with the fused energy reporter, interval 1 / 10 / 100 / none
     if not quick:
         for interval in (1, 10, 100, None):
             reps = (lambda fl, k=interval: [lt.ObservableReporter(lt.IncompressibleKineticEnergy(fl), interval=k, out=None)]) \
                 if interval else None
-            flow, sim, t = tgv(512, lt.D3Q27, torch.float32, "kbc", reporters=reps, steps=100)
-            report(f"cfg4 TGV3D D3Q27 KBC f32 512^3 energy reporter interval={interval}", flow, t, 100)
-            del flow, sim
-            torch.cuda.empty_cache()
-        flow, sim, t = tgv(512, lt.D3Q19, torch.float32, "bgk", steps=50)
-        report("TGV3D D3Q19 bgk f32 512^3", flow, t, 50)
+            tgv_case(f"cfg4 TGV3D D3Q27 KBC f32 512^3 energy reporter interval={interval}", 512, lt.D3Q27,
+                     torch.float32, "kbc", 100, reporters=reps)
+        tgv_case("TGV3D D3Q19 bgk f32 512^3", 512, lt.D3Q19, torch.float32, "bgk", 50)
 
 
 if __name__ == "__main__":
