@@ -90,6 +90,9 @@ template <typename T>
 int vector_width(const lb_desc* d, const Geometry& g, const void* a, const void* b, bool sbits) {
   if (sbits) return 1;
   int cap = 16 / int(sizeof(T));
+  // D3Q27 KBC is bound by instruction issue / latency, not by HBM: one node per thread keeps the
+  // unrolled body inside the 32 KB instruction cache and five blocks resident (measured fastest)
+  if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_KBC) cap = 1;
   static const char* env = getenv("LB_VEC");
   if (env && atoi(env) >= 1) cap = atoi(env) < cap ? atoi(env) : cap;
   for (int v = cap; v > 1; v >>= 1)

@@ -148,8 +148,8 @@ __device__ __forceinline__ KbcS<T> kbc_s(const T (&g)[S::Q]) {
 // for the quadratic equilibrium on D2Q9 / D3Q27 those sums are, identically,
 //   sum_q feq_q = rho   and   sum_q e_a e_b feq_q / rho = cs^2 delta_ab + u_a u_b ,
 // so the closed form differs from the reference's sums only by their round-off (a few ulp of
-// rho), the same size as the difference between any two summation orders.  It removes a second
-// 27-term moment pass per node from a kernel that is instruction-issue bound.
+// rho).  NOT used by default: measured on B200 it did not make the (latency-bound) KBC kernel
+// faster, and one fp32 parity case moved from 2e-6 to 1.4e-5 relative, outside the 1e-5 bar.
 template <class S, typename T>
 __device__ __forceinline__ KbcS<T> kbc_s_equilibrium(T rho, const T (&u)[3]) {
   constexpr T cs2 = T(LB_CS2);
@@ -219,7 +219,11 @@ __device__ __forceinline__ void collide_node(T (&f)[S::Q], T rho, const T (&u)[3
       // kbc_collision.py:131-158
       static_assert(S::ID != 1, "KBC is defined for D2Q9 and D3Q27 only (kbc_collision.py:101,115)");
       const KbcS<T> sf = kbc_s<S, T>(f);
+#ifdef LB_KBC_ANALYTIC_FEQ   // experiment only: 10 % fewer instructions, one parity outlier
       const KbcS<T> se = kbc_s_equilibrium<S, T>(rho, u);
+#else
+      const KbcS<T> se = kbc_s<S, T>(feq);
+#endif
       KbcS<T> d;   // delta_s = s(f) - s(feq), per distinct value
       d.s0 = sf.s0 - se.s0; d.sA = sf.sA - se.sA; d.sB = sf.sB - se.sB; d.sC = sf.sC - se.sC;
       d.pyz = sf.pyz - se.pyz; d.pxz = sf.pxz - se.pxz; d.pxy = sf.pxy - se.pxy;
