@@ -89,12 +89,13 @@ bool aligned_to(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p
 template <typename T>
 int vector_width(const lb_desc* d, const Geometry& g, const void* a, const void* b, bool sbits) {
   if (sbits) return 1;
-  int cap = 16 / int(sizeof(T));
-  // D3Q27 KBC is bound by instruction issue / latency, not by HBM: one node per thread keeps the
-  // unrolled body inside the 32 KB instruction cache and five blocks resident (measured fastest)
-  if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_KBC) cap = 1;
+  const int widest = 16 / int(sizeof(T));
+  int cap = widest;
+  // D3Q27 KBC holds ~60 values per node in registers: fp32 runs two nodes per thread as packed F2
+  // values (164 registers, three blocks per SM), fp64 one node per thread
+  if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_KBC) cap = (sizeof(T) == 4) ? 2 : 1;
   static const char* env = getenv("LB_VEC");
-  if (env && atoi(env) >= 1) cap = atoi(env) < cap ? atoi(env) : cap;
+  if (env && atoi(env) >= 1) cap = atoi(env) < widest ? atoi(env) : widest;
   for (int v = cap; v > 1; v >>= 1)
     if (g.nz % unsigned(v) == 0 && aligned_to(a, v * sizeof(T)) && aligned_to(b, v * sizeof(T))) return v;
   return 1;

@@ -172,10 +172,82 @@ __device__ __forceinline__ void reduce_observables(double e, double m2, double m
   }
 }
 
-// D3Q27 fp32 with 4 nodes per thread holds 108 population registers; asking for 3 resident blocks
-// (<= 168 registers) keeps the fused-reduction variants at the occupancy of the plain ones.
+// One node: moments -> (fused observables) -> collision where ncm == 0, boundary i where ncm == i
+template <class S, typename T, int COLL, int MODE, bool OBS>
+__device__ __forceinline__ void node_update(T (&g)[S::Q], unsigned m, const StepParams<T>& p, unsigned x, unsigned y,
+                                            unsigned z, unsigned node, bool active, T& acc_e, T& acc_m2,
+                                            T& acc_mass) {
+  T a[N_SLOTS], b[N_SLOTS];
+  T rho = T(0), u[3] = {T(0), T(0), T(0)};
+  if (OBS || (COLL != COLL_NONE && m == 0)) {
+    pair_split<S, T>(g, a, b);
+    moments_from_pairs<S, T>(g[0], a, b, rho, u);
+  }
+  if constexpr (OBS) {
+    const T u2 = fma_(u[0], u[0], fma_(u[1], u[1], u[2] * u[2]));
+    acc_e += T(0.5) * u2;
+    acc_m2 = max_(acc_m2, u2);
+    acc_mass += rho;
+    if (p.u_out != nullptr && active) {   // only on steps that feed the enstrophy kernel
+#pragma unroll
+      for (int c = 0; c < S::D; ++c) p.u_out[c * size_t(p.n_nodes) + node] = u[S::axis(c)];
+    }
+  }
+  if (m == 0) {
+    collide_node<S, T, COLL, T>(g, a, b, rho, u, p.cp);
+  } else if constexpr (MODE != MODE_PLAIN) {
+    if (m <= unsigned(p.n_bnd)) {
+      const BoundaryDev<T>& bd = p.bnd[m - 1];
+      if (bd.kind == BND_BOUNCE_BACK) {
+        bounce_back_node<S, T>(g);
+      } else if (bd.kind == BND_EQUILIBRIUM) {
+        // equilibrium_boundary_pu.py:27-32 (rho, u already in lattice units)
+        const long long zz = z;
+        const T rb = bd.rho[x * bd.rs[0] + y * bd.rs[1] + zz * bd.rs[2]];
+        T ub[3] = {T(0), T(0), T(0)};
+        const long long off = x * bd.us[0] + y * bd.us[1] + zz * bd.us[2];
+#pragma unroll
+        for (int c = 0; c < S::D; ++c) ub[S::axis(c)] = bd.u[c * bd.ucs + off];
+        equilibrium<S, T>(rb, ub, g);
+      }
+    }
+  }
+}
+
+// Two z-adjacent fp32 fluid nodes (both ncm == 0) as one packed value per population
+template <class S, int COLL, bool OBS>
+__device__ __forceinline__ void packed_update(F2 (&g)[S::Q], const StepParams<float>& p, unsigned node, bool active,
+                                              float& acc_e, float& acc_m2, float& acc_mass) {
+  if constexpr (!OBS && COLL == COLL_NONE) return;
+  F2 a[N_SLOTS], b[N_SLOTS], rho, u[3];
+  pair_split<S, F2>(g, a, b);
+  moments_from_pairs<S, F2>(g[0], a, b, rho, u);
+  if constexpr (OBS) {
+    const F2 u2 = fma_(u[0], u[0], fma_(u[1], u[1], u[2] * u[2]));
+    acc_e += 0.5f * u2.x;
+    acc_e += 0.5f * u2.y;
+    acc_m2 = max_(acc_m2, hmax(u2));
+    acc_mass += rho.x;
+    acc_mass += rho.y;
+    if (p.u_out != nullptr && active) {
+#pragma unroll
+      for (int c = 0; c < S::D; ++c) {
+        p.u_out[c * size_t(p.n_nodes) + node] = u[S::axis(c)].x;
+        p.u_out[c * size_t(p.n_nodes) + node + 1] = u[S::axis(c)].y;
+      }
+    }
+  }
+  collide_node<S, F2, COLL, float>(g, a, b, rho, u, p.cp);
+}
+
+// Resident blocks asked of the register allocator.  D3Q19 fp32 with 4 nodes per thread: 76 population
+// registers, 4 blocks (<= 128 registers) as measured at the HBM roofline; D3Q27 fp32 with 2 or 4 nodes
+// per thread (54 / 108 population registers): 3 blocks (<= 168 registers).
 template <class S, typename T, int V>
-constexpr int step_min_blocks() { return (S::Q == 27 && sizeof(T) == 4 && V == 4) ? 3 : 1; }
+constexpr int step_min_blocks() {
+  if (sizeof(T) == 4 && V >= 2) return S::Q == 27 ? 3 : 4;
+  return 1;
+}
 
 template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO>
 __global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V>())
@@ -211,10 +283,9 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
   // ---- load: Q aligned vector loads ------------------------------------------------
   T f[Q][V];
   {
-    const T* src = p.f_in + node;
     static_for<Q>([&](auto qc) {
       constexpr int q = decltype(qc)::value;
-      const Vec<T, V> v = ld_vec<T, V>(src + q * N);
+      const Vec<T, V> v = ld_vec<T, V>(p.f_in + size_t(q) * N + node);
 #pragma unroll
       for (int k = 0; k < V; ++k) f[q][k] = v.v[k];
     });
@@ -237,44 +308,47 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
 
   T acc_e = T(0), acc_mass = T(0), acc_m2 = T(0);   // per-thread partials over V nodes; widened below
 
-  // ---- collide / boundaries, node by node, all in registers -------------------------
+  // ---- collide / boundaries, all in registers -----------------------------------------
+  // fp32 threads that own an even number of nodes run them two at a time as packed F2 values
+  // (FADD2 / FMUL2 / FFMA2); a pair that contains a boundary node, and every other case, goes node
+  // by node.  Both routes round identically (lb_physics.cuh), so the result does not depend on V.
+  constexpr bool PACK = (sizeof(T) == 4) && (V % 2 == 0);
+  if constexpr (PACK) {
 #pragma unroll
-  for (int k = 0; k < V; ++k) {
-    T g[Q];
-    static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
-    const unsigned m = (MODE == MODE_PLAIN) ? 0u : ((mword >> (8 * k)) & 0xffu);
-    T rho = T(0), u[3] = {T(0), T(0), T(0)};
-    if (OBS || (COLL != COLL_NONE && m == 0)) moments<S, T>(g, rho, u);
-    if constexpr (OBS) {
-      const T u2 = u[0] * u[0] + u[1] * u[1] + u[2] * u[2];
-      acc_e += T(0.5) * u2;
-      acc_m2 = max(acc_m2, u2);
-      acc_mass += rho;
-      if (p.u_out != nullptr && active) {   // only on steps that feed the enstrophy kernel
+    for (int kk = 0; kk < V / 2; ++kk) {
+      const unsigned m2 = (MODE == MODE_PLAIN) ? 0u : ((mword >> (16 * kk)) & 0xffffu);
+      if (m2 == 0) {
+        F2 g[Q];
+        static_for<Q>([&](auto qc) {
+          constexpr int q = decltype(qc)::value;
+          g[q] = F2(f[q][2 * kk], f[q][2 * kk + 1]);
+        });
+        packed_update<S, COLL, OBS>(g, p, node + 2 * kk, active, acc_e, acc_m2, acc_mass);
+        static_for<Q>([&](auto qc) {
+          constexpr int q = decltype(qc)::value;
+          f[q][2 * kk] = g[q].x;
+          f[q][2 * kk + 1] = g[q].y;
+        });
+      } else {
 #pragma unroll
-        for (int c = 0; c < S::D; ++c) p.u_out[c * N + node + k] = u[S::axis(c)];
-      }
-    }
-    if (m == 0) {
-      collide_node<S, T, COLL>(g, rho, u, p.cp);
-    } else if constexpr (MODE != MODE_PLAIN) {
-      if (m <= unsigned(p.n_bnd)) {
-        const BoundaryDev<T>& b = p.bnd[m - 1];
-        if (b.kind == BND_BOUNCE_BACK) {
-          bounce_back_node<S, T>(g);
-        } else if (b.kind == BND_EQUILIBRIUM) {
-          // equilibrium_boundary_pu.py:27-32 (rho, u already in lattice units)
-          const long long z = z0 + k;
-          const T rb = b.rho[x * b.rs[0] + y * b.rs[1] + z * b.rs[2]];
-          T ub[3] = {T(0), T(0), T(0)};
-          const long long off = x * b.us[0] + y * b.us[1] + z * b.us[2];
-#pragma unroll
-          for (int c = 0; c < S::D; ++c) ub[S::axis(c)] = b.u[c * b.ucs + off];
-          equilibrium<S, T>(rb, ub, g);
+        for (int k = 2 * kk; k < 2 * kk + 2; ++k) {
+          T g[Q];
+          static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
+          node_update<S, T, COLL, MODE, OBS>(g, (m2 >> (8 * (k - 2 * kk))) & 0xffu, p, x, y, z0 + k, node + k, active,
+                                             acc_e, acc_m2, acc_mass);
+          static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
         }
       }
     }
-    static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
+  } else {
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      T g[Q];
+      static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
+      const unsigned m = (MODE == MODE_PLAIN) ? 0u : ((mword >> (8 * k)) & 0xffu);
+      node_update<S, T, COLL, MODE, OBS>(g, m, p, x, y, z0 + k, node + k, active, acc_e, acc_m2, acc_mass);
+      static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
+    }
   }
 
   // ---- stream: push to (x + ex, y + ey, z + ez), periodic -----------------------------
@@ -289,21 +363,34 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
       });
     }
   } else {
+    // Addressing: one uniform 64-bit base per population (f_out + q N) plus a 32-bit element index
+    // per thread, so an address costs one wide multiply-add.  All index arithmetic sits outside the
+    // `active` / edge predicates: the guarded statements are single stores, which the compiler
+    // predicates instead of branching around.
     const unsigned xp = (x + 1 == nx) ? 0u : x + 1, xm = (x == 0) ? nx - 1 : x - 1;
     const unsigned yp = (y + 1 == ny) ? 0u : y + 1, ym = (y == 0) ? ny - 1 : y - 1;
+    const unsigned xs[3] = {xm * ny, x * ny, xp * ny};
+    const unsigned ys[3] = {ym, y, yp};
     const bool first_in_line = (zv == 0), last_in_line = (zv == nzv - 1);
     const bool has_left = (lane > 0) && !first_in_line;
     const bool has_right = (lane < 31) && !last_in_line;
+    const bool st_left = active && has_left, st_noleft = active && !has_left;
+    const bool st_right = active && has_right, st_noright = active && !has_right;
+    const bool edge_up = active && (lane == 31 || last_in_line);   // owns the element that leaves the warp upwards
+    const bool edge_dn = active && (lane == 0 || first_in_line);
+    // element offset of that edge element relative to this thread's own vector in the destination line
+    const unsigned d_up = last_in_line ? 0u - z0 : unsigned(V);
+    const unsigned d_dn = first_in_line ? nz - 1u : 0u - 1u;
     uint32_t own_bits = 0;
     if constexpr (MODE == MODE_NCM_SBITS) own_bits = p.sbits[node];
 
     static_for<Q>([&](auto qc) {
       constexpr int q = decltype(qc)::value;
       constexpr int ex = S::e(q, 0), ey = S::e(q, 1), ez = S::e(q, 2);
-      const unsigned xd = (ex == 0) ? x : (ex > 0 ? xp : xm);
-      const unsigned yd = (ey == 0) ? y : (ey > 0 ? yp : ym);
-      const unsigned dline = (xd * ny + yd) * nz;
-      T* dst = p.f_out + q * N + dline;  // start of the destination line
+      const unsigned dlines = xs[ex + 1] + ys[ey + 1];   // destination line number
+      const unsigned dline = dlines * nz;                // its first element
+      [[maybe_unused]] const unsigned idx = dline + z0;  // this thread's vector in the destination line
+      T* const bq = p.f_out + size_t(q) * N;             // uniform
 
       if constexpr (MODE == MODE_NCM_SBITS) {
         // destination-masked streaming, one node per thread
@@ -311,74 +398,64 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
                                                      : (z0 == 0 ? nz - 1 : z0 - 1));
         if (active) {
           if constexpr (q == 0) {
-            dst[zd] = f[q][0];
+            bq[dline + zd] = f[q][0];
           } else {
             const uint32_t dbits = p.sbits[dline + zd];
-            if (!((dbits >> q) & 1u)) dst[zd] = f[q][0];
-            if ((own_bits >> q) & 1u) p.f_out[q * N + node] = f[q][0];
+            if (!((dbits >> q) & 1u)) bq[dline + zd] = f[q][0];
+            if ((own_bits >> q) & 1u) bq[node] = f[q][0];
           }
         }
       } else if constexpr (ez == 0) {
-        if (active) {
-          Vec<T, V> v;
+        Vec<T, V> v;
 #pragma unroll
-          for (int k = 0; k < V; ++k) v.v[k] = f[q][k];
-          st_vec<T, V>(dst + z0, v);
-        }
+        for (int k = 0; k < V; ++k) v.v[k] = f[q][k];
+        if (active) st_vec<T, V>(bq + idx, v);
       } else if constexpr (V == 1) {
         const bool crosses = (ez > 0) ? (z0 + 1 == nz) : (z0 == 0);
         const unsigned zd = (ez > 0) ? (crosses ? 0u : z0 + 1) : (crosses ? nz - 1 : z0 - 1);
         if (active) {
           T* hp = (ez > 0) ? p.halo_hi : p.halo_lo;
           if (HALO && crosses && hp != nullptr)
-            hp[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs + (long long)(xd * ny + yd) * p.halo_ls +
+            hp[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs + (long long)(dlines) * p.halo_ls +
                ((ez > 0) ? p.halo_hi_off : p.halo_lo_off)] = f[q][0];
           else
-            dst[zd] = f[q][0];
+            bq[dline + zd] = f[q][0];
         }
       } else if constexpr (ez > 0) {
         // destination z0+k takes the source value of z0+k-1: element 0 comes from the left lane
         const T up = __shfl_up_sync(0xffffffffu, f[q][V - 1], 1);
-        if (active) {
-          if (has_left) {
-            Vec<T, V> v;
-            v.v[0] = up;
+        Vec<T, V> v;
+        v.v[0] = up;
 #pragma unroll
-            for (int k = 1; k < V; ++k) v.v[k] = f[q][k - 1];
-            st_vec<T, V>(dst + z0, v);
-          } else {
+        for (int k = 1; k < V; ++k) v.v[k] = f[q][k - 1];
+        if (st_left) st_vec<T, V>(bq + idx, v);
 #pragma unroll
-            for (int k = 1; k < V; ++k) dst[z0 + k] = f[q][k - 1];
-          }
-          if (lane == 31 || last_in_line) {
-            if (HALO && last_in_line && p.halo_hi != nullptr)
-              p.halo_hi[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs +
-                        (long long)(xd * ny + yd) * p.halo_ls + p.halo_hi_off] = f[q][V - 1];
-            else
-              dst[last_in_line ? 0u : z0 + V] = f[q][V - 1];
-          }
+        for (int k = 1; k < V; ++k)
+          if (st_noleft) bq[idx + k] = f[q][k - 1];
+        if (edge_up) {
+          if (HALO && last_in_line && p.halo_hi != nullptr)
+            p.halo_hi[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs + (long long)(dlines) * p.halo_ls +
+                      p.halo_hi_off] = f[q][V - 1];
+          else
+            bq[idx + d_up] = f[q][V - 1];
         }
       } else {
         // ez < 0: destination z0+k takes the source value of z0+k+1
         const T dn = __shfl_down_sync(0xffffffffu, f[q][0], 1);
-        if (active) {
-          if (has_right) {
-            Vec<T, V> v;
+        Vec<T, V> v;
 #pragma unroll
-            for (int k = 0; k < V - 1; ++k) v.v[k] = f[q][k + 1];
-            v.v[V - 1] = dn;
-            st_vec<T, V>(dst + z0, v);
-          } else {
+        for (int k = 0; k < V - 1; ++k) v.v[k] = f[q][k + 1];
+        v.v[V - 1] = dn;
+        if (st_right) st_vec<T, V>(bq + idx, v);
 #pragma unroll
-            for (int k = 0; k < V - 1; ++k) dst[z0 + k] = f[q][k + 1];
-          }
-          if (lane == 0 || first_in_line) {
-            if (HALO && first_in_line && p.halo_lo != nullptr)
-              p.halo_lo[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs +
-                        (long long)(xd * ny + yd) * p.halo_ls + p.halo_lo_off] = f[q][0];
-            else
-              dst[first_in_line ? nz - 1 : z0 - 1] = f[q][0];
-          }
+        for (int k = 0; k < V - 1; ++k)
+          if (st_noright) bq[idx + k] = f[q][k + 1];
+        if (edge_dn) {
+          if (HALO && first_in_line && p.halo_lo != nullptr)
+            p.halo_lo[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs + (long long)(dlines) * p.halo_ls +
+                      p.halo_lo_off] = f[q][0];
+          else
+            bq[idx + d_dn] = f[q][0];
         }
       }
     });
@@ -428,7 +505,7 @@ moments_kernel(const __grid_constant__ MomentsParams<T> p) {
     }
   }
   if constexpr (OBS) {
-    const T u2 = u[0] * u[0] + u[1] * u[1] + u[2] * u[2];
+    const T u2 = fma_(u[0], u[0], fma_(u[1], u[1], u[2] * u[2]));
     double e = active ? double(T(0.5) * u2) : 0.0;
     double m2 = active ? double(u2) : 0.0;
     double mass = active ? double(rho) : 0.0;

@@ -1,12 +1,27 @@
 // Per-node physics in registers: moments, quadratic equilibrium, BGK / TRT / KBC relaxation,
-// bounce-back and equilibrium boundaries.  One call handles ONE lattice node whose Q
-// populations live in a register array.  All loops are unrolled at compile time so the
-// stencil constants fold into immediates.
+// bounce-back and equilibrium boundaries.  One call handles ONE value `R` per population:
+// R = float / double (one node) or F2 (two fp32 nodes in packed FADD2/FMUL2/FFMA2 instructions,
+// lb_values.cuh).  All loops are unrolled at compile time so stencil constants fold away.
 //
-// Arithmetic follows the reference's torch path op for op where it matters for parity
-// (SURVEY appendix A.7-A.11); file:line citations are relative to the reference checkout.
+// Opposite-pair formulation.  Every stencil here is symmetric, so the Q-1 moving populations
+// form (Q-1)/2 opposite pairs (q, o).  With a_p = f_q + f_o and b_p = f_q - f_o
+//   rho = f_0 + sum a_p,   j = sum e_q b_p,   sum e e f = sum e_q e_q a_p        (even / odd moments)
+//   feq_q = S_p + D_p,  feq_o = S_p - D_p   with   S_p = w rho (1 - u.u/(2cs^2) + (e.u/cs^2)^2 / 2),
+//                                                  D_p = w rho (e.u/cs^2)
+// which is the reference's feq (quadratic_equilibrium.py:11-25) split into its even and odd part
+// in e.  Half the additions of the moment sums and a third of the equilibrium arithmetic of the
+// literal population-by-population evaluation; TRT's symmetric / antisymmetric parts
+// (trt_collision.py:20-25) are a_p - 2 S_p and b_p - 2 D_p directly.
+//
+// Every multiply-add that is meant to be fused is written fma_(); the library is compiled with
+// -fmad=false, so scalar and packed instantiations (and the host emulation in tests/host_emul) round
+// identically: the same node gives the same bits whichever vector width the launcher picks.
+//
+// Differences to the reference's torch arithmetic are at round-off level (it sums in torch's
+// order, divides by cs^2 where a reciprocal is multiplied here, ...) and inside the parity budget
+// (1e-12 fp64 / 1e-5 fp32); file:line citations are relative to the reference checkout.
 #pragma once
-#include "lb_stencil.cuh"
+#include "lb_values.cuh"
 
 namespace lb {
 
@@ -19,238 +34,344 @@ struct CollisionParams {
   T inv_beta;     // KBC: 1/beta as the reference evaluates `1. / self.beta` (:153)
 };
 
-// rho = sum_q f_q (_flow.py:136-138), j = sum_q e_q f_q (:152-155), u = j / rho (:161-162)
-template <class S, typename T>
-__device__ __forceinline__ void moments(const T (&f)[S::Q], T& rho, T (&u)[3]) {
-  T r = f[0];
-  T jx = T(0), jy = T(0), jz = T(0);
-  static_for<S::Q>([&](auto qc) {
-    constexpr int q = decltype(qc)::value;
-    if constexpr (q > 0) r += f[q];
-    if constexpr (S::e(q, 0) == 1) jx += f[q];
-    if constexpr (S::e(q, 0) == -1) jx -= f[q];
-    if constexpr (S::e(q, 1) == 1) jy += f[q];
-    if constexpr (S::e(q, 1) == -1) jy -= f[q];
-    if constexpr (S::e(q, 2) == 1) jz += f[q];
-    if constexpr (S::e(q, 2) == -1) jz -= f[q];
+// ---------------------------------------------------------------------------------------
+// Opposite pairs, by direction class ("slot") in kernel axes (X, Y, Z):
+//   0 X(1,0,0) 1 Y(0,1,0) 2 Z(0,0,1) | 3 (0,1,1) 4 (0,1,-1) | 5 (1,0,1) 6 (1,0,-1) |
+//   7 (1,1,0) 8 (1,-1,0) | 9 (1,1,1) 10 (1,1,-1) 11 (1,-1,1) 12 (1,-1,-1)
+// pair_q<S>(slot) = the population with that direction (its partner is S::opp), -1 if absent.
+// ---------------------------------------------------------------------------------------
+constexpr int N_SLOTS = 13;
+
+__host__ __device__ constexpr int slot_e(int slot, int a) {
+  constexpr int t[N_SLOTS][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}, {0, 1, 1},  {0, 1, -1}, {1, 0, 1},  {1, 0, -1},
+                                 {1, 1, 0}, {1, -1, 0}, {1, 1, 1}, {1, 1, -1}, {1, -1, 1}, {1, -1, -1}};
+  return t[slot][a];
+}
+template <class S>
+__host__ __device__ constexpr int pair_q(int slot) {
+  if (S::Q == 9) {
+    constexpr int t[N_SLOTS] = {-1, 1, 2, 5, 8, -1, -1, -1, -1, -1, -1, -1, -1};
+    return t[slot];
+  }
+  return (2 * slot + 1 < S::Q) ? 2 * slot + 1 : -1;
+}
+template <class S>
+__host__ __device__ constexpr bool pair_table_ok() {
+  int seen = 1;  // population 0
+  for (int s = 0; s < N_SLOTS; ++s) {
+    const int q = pair_q<S>(s);
+    if (q < 0) continue;
+    for (int a = 0; a < 3; ++a)
+      if (S::e(q, a) != slot_e(s, a) || S::e(S::opp(q), a) != -slot_e(s, a)) return false;
+    seen += 2;
+  }
+  return seen == S::Q;
+}
+static_assert(pair_table_ok<D2Q9>() && pair_table_ok<D3Q19>() && pair_table_ok<D3Q27>(), "pair tables");
+
+template <class S, int SLOT> constexpr bool has_slot = pair_q<S>(SLOT) >= 0;
+
+// a_p = f_q + f_o, b_p = f_q - f_o
+template <class S, typename R>
+__host__ __device__ __forceinline__ void pair_split(const R (&f)[S::Q], R (&a)[N_SLOTS], R (&b)[N_SLOTS]) {
+  static_for<N_SLOTS>([&](auto sc) {
+    constexpr int s = decltype(sc)::value;
+    if constexpr (has_slot<S, s>) {
+      constexpr int q = pair_q<S>(s), o = S::opp(q);
+      a[s] = f[q] + f[o];
+      b[s] = f[q] - f[o];
+    }
   });
-  rho = r;
-  // true division, as torch does
-  if constexpr (S::D == 3) u[0] = jx / r; else u[0] = T(0);  // 2-D runs with X == 1
-  u[1] = jy / r;
-  u[2] = jz / r;
 }
 
-// quadratic_equilibrium.py:11-25:
-//   feq_q = w_q * (rho * ((2 exu - uxu) / (2 cs^2) + 0.5 (exu / cs^2)^2 + 1))
-// Division by the two constants is done as multiplication by their (double-rounded-to-T)
-// reciprocals: <= 1 ulp away from the reference's division, well inside the parity budget.
-template <class S, typename T>
-__device__ __forceinline__ void equilibrium(T rho, const T (&u)[3], T (&feq)[S::Q]) {
-  constexpr T inv_cs2 = T(1.0 / LB_CS2);
-  constexpr T inv_2cs2 = T(1.0 / (2.0 * LB_CS2));
-  const T uxu = u[0] * u[0] + u[1] * u[1] + u[2] * u[2];
-  static_for<S::Q>([&](auto qc) {
-    constexpr int q = decltype(qc)::value;
-    T exu = T(0);
-    if constexpr (S::e(q, 0) == 1) exu += u[0];
-    if constexpr (S::e(q, 0) == -1) exu -= u[0];
-    if constexpr (S::e(q, 1) == 1) exu += u[1];
-    if constexpr (S::e(q, 1) == -1) exu -= u[1];
-    if constexpr (S::e(q, 2) == 1) exu += u[2];
-    if constexpr (S::e(q, 2) == -1) exu -= u[2];
-    const T a = exu * inv_cs2;
-    const T t = (T(2) * exu - uxu) * inv_2cs2 + T(0.5) * (a * a) + T(1);
-    feq[q] = T(S::w(q)) * (rho * t);
-  });
-}
-
-// ---------------------------------------------------------------------------------------
-// KBC helper: the `s` part of the moment representation (kbc_collision.py:25-94).
-// The reference builds all 27 (9) raw moments with an einsum; only rho and the six (three)
-// second moments enter s, so only those are formed here.  s has 10 (2-D: 5) distinct values:
-//   3-D  s0 | sA (q 1,2) | sB (3,4) | sC (5,6) | +-pyz (7,8 | 9,10) | +-pxz (11,12 | 13,14)
-//        | +-pxy (15,16 | 17,18) | 0 for the corner populations 19..26     (:54-72)
-//   2-D  s0 | sA (q 1,3) | sB (2,4) | +-pxy (5,7 | 6,8)                     (:84-92)
-// ---------------------------------------------------------------------------------------
-template <typename T>
-struct KbcS {
-  T s0, sA, sB, sC, pyz, pxz, pxy;
+// Even moments of a pair-symmetric quantity v_p (one value per pair):
+//   sum = sum_p v_p,  m_AB = sum_p e_A e_B v_p, shared partial sums by direction class.
+template <typename R>
+struct EvenMoments {
+  R sum, xx, yy, zz, xy, xz, yz;   // 2-D (D2Q9 runs as X = 1): only sum, yy, zz, yz are set
 };
 
-template <typename T> __device__ __forceinline__ T fast_rcp(T x) { return T(1) / x; }
-// 1 ulp reciprocal (MUFU.RCP): used only for the two sums that set gamma, where the reference's
-// own result is no better conditioned than that (operands are O(w_q), never denormal)
-template <> __device__ __forceinline__ float fast_rcp<float>(float x) {
-  float r;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));   // one MUFU.RCP, no range fix-up
-  return r;
-}
-
-// s from rho and the second moments ALREADY divided by rho
-template <class S, typename T>
-__device__ __forceinline__ KbcS<T> kbc_s_from_moments(T r, T mxx, T myy, T mzz, T mxy, T mxz, T myz) {
-  KbcS<T> s;
-  if constexpr (S::D == 3) {
-    // kbc_collision.py:47-72
-    const T Tr = mxx + myy + mzz;
-    const T Nxz = mxx - mzz;
-    const T Nyz = myy - mzz;
-    const T sixth = T(1. / 6.), quarter = T(1. / 4);
-    s.s0 = r * -Tr;
-    s.sA = sixth * r * (T(2) * Nxz - Nyz + Tr);
-    s.sB = sixth * r * (T(2) * Nyz - Nxz + Tr);
-    s.sC = sixth * r * (-Nxz - Nyz + Tr);
-    s.pyz = quarter * r * myz;
-    s.pxz = quarter * r * mxz;
-    s.pxy = quarter * r * mxy;
+template <class S, typename R>
+__host__ __device__ __forceinline__ EvenMoments<R> even_moments(const R (&v)[N_SLOTS]) {
+  EvenMoments<R> m;
+  const R eyz = v[3] + v[4];
+  m.yz = v[3] - v[4];
+  if constexpr (S::D == 2) {
+    m.yy = v[1] + eyz;
+    m.zz = v[2] + eyz;
+    m.sum = (v[1] + v[2]) + eyz;
+    m.xx = m.xy = m.xz = R(0);
   } else {
-    // kbc_collision.py:79-92
-    const T Tr = mxx + myy;
-    const T N = mxx - myy;
-    s.s0 = r * -Tr;
-    s.sA = T(0.5) * r * (T(0.5) * (Tr + N));
-    s.sB = T(0.5) * r * (T(0.5) * (Tr - N));
-    s.sC = T(0);
-    s.pyz = T(0);
-    s.pxz = T(0);
-    s.pxy = T(0.25) * r * mxy;
+    const R exz = v[5] + v[6];
+    const R exy = v[7] + v[8];
+    m.xz = v[5] - v[6];
+    m.xy = v[7] - v[8];
+    m.xx = (v[0] + exz) + exy;
+    m.yy = (v[1] + eyz) + exy;
+    m.zz = (v[2] + eyz) + exz;
+    m.sum = ((v[0] + v[1]) + v[2]) + ((eyz + exz) + exy);
+    if constexpr (S::Q == 27) {
+      const R c1 = v[9] + v[10], c2 = v[11] + v[12];
+      const R c3 = v[9] - v[10], c4 = v[11] - v[12];
+      const R c = c1 + c2;
+      m.xx += c; m.yy += c; m.zz += c; m.sum += c;
+      m.xy += c1 - c2;
+      m.xz += c3 + c4;
+      m.yz += c3 - c4;
+    }
   }
-  return s;
+  return m;
 }
 
-// s(f): second moments by summation, m = m / rho (kbc_collision.py:27-30, 36-39)
-template <class S, typename T>
-__device__ __forceinline__ KbcS<T> kbc_s(const T (&g)[S::Q]) {
-  T r = T(0), mxx = T(0), myy = T(0), mzz = T(0), mxy = T(0), mxz = T(0), myz = T(0);
-  static_for<S::Q>([&](auto qc) {
-    constexpr int q = decltype(qc)::value;
-    // lattice axes (x, y[, z]) -> kernel axes
-    constexpr int ex = S::e(q, S::axis(0));
-    constexpr int ey = S::e(q, S::axis(1));
-    constexpr int ez = (S::D == 3) ? S::e(q, S::axis(S::D == 3 ? 2 : 0)) : 0;
-    r += g[q];
-    if constexpr (ex * ex == 1) mxx += g[q];
-    if constexpr (ey * ey == 1) myy += g[q];
-    if constexpr (ez * ez == 1) mzz += g[q];
-    if constexpr (ex * ey == 1) mxy += g[q];
-    if constexpr (ex * ey == -1) mxy -= g[q];
-    if constexpr (ex * ez == 1) mxz += g[q];
-    if constexpr (ex * ez == -1) mxz -= g[q];
-    if constexpr (ey * ez == 1) myz += g[q];
-    if constexpr (ey * ez == -1) myz -= g[q];
+// first moment of a pair-antisymmetric quantity: j_A = sum_p e_A b_p
+template <class S, typename R>
+__host__ __device__ __forceinline__ void odd_moments(const R (&b)[N_SLOTS], R (&j)[3]) {
+  if constexpr (S::D == 2) {
+    j[0] = R(0);
+    j[1] = b[1] + (b[3] + b[4]);
+    j[2] = b[2] + (b[3] - b[4]);
+  } else {
+    R jx = (b[0] + (b[5] + b[6])) + (b[7] + b[8]);
+    R jy = (b[1] + (b[3] + b[4])) + (b[7] - b[8]);
+    R jz = (b[2] + (b[3] - b[4])) + (b[5] - b[6]);
+    if constexpr (S::Q == 27) {
+      const R d1 = b[9] + b[10], d2 = b[11] + b[12];
+      jx += d1 + d2;
+      jy += d1 - d2;
+      jz += (b[9] - b[10]) + (b[11] - b[12]);
+    }
+    j[0] = jx; j[1] = jy; j[2] = jz;
+  }
+}
+
+// rho = sum_q f_q (_flow.py:136-138), j = sum_q e_q f_q (:152-155), u = j / rho (:161-162, true division)
+template <class S, typename R>
+__host__ __device__ __forceinline__ void moments_from_pairs(R f0, const R (&a)[N_SLOTS], const R (&b)[N_SLOTS],
+                                                            R& rho, R (&u)[3]) {
+  const EvenMoments<R> m = even_moments<S, R>(a);   // only .sum is used; the rest is dead code
+  rho = f0 + m.sum;
+  R j[3];
+  odd_moments<S, R>(b, j);
+  u[0] = (S::D == 3) ? div_(j[0], rho) : R(0);
+  u[1] = div_(j[1], rho);
+  u[2] = div_(j[2], rho);
+}
+
+template <class S, typename R>
+__host__ __device__ __forceinline__ void moments(const R (&f)[S::Q], R& rho, R (&u)[3]) {
+  R a[N_SLOTS], b[N_SLOTS];
+  pair_split<S, R>(f, a, b);
+  moments_from_pairs<S, R>(f[0], a, b, rho, u);
+}
+
+// e_slot . v  without a zero seed (0 + x is not a no-op in IEEE arithmetic); (vx +- vy) is shared by
+// the edge and the corner directions through common-subexpression elimination
+template <int SLOT, typename R>
+__host__ __device__ __forceinline__ R slot_dot(const R (&v)[3]) {
+  constexpr int ex = slot_e(SLOT, 0), ey = slot_e(SLOT, 1), ez = slot_e(SLOT, 2);
+  if constexpr (ex != 0 && ey != 0 && ez != 0) return ez > 0 ? (ey > 0 ? (v[0] + v[1]) + v[2] : (v[0] - v[1]) + v[2])
+                                                               : (ey > 0 ? (v[0] + v[1]) - v[2] : (v[0] - v[1]) - v[2]);
+  else if constexpr (ex != 0 && ey != 0) return ey > 0 ? v[0] + v[1] : v[0] - v[1];
+  else if constexpr (ex != 0 && ez != 0) return ez > 0 ? v[0] + v[2] : v[0] - v[2];
+  else if constexpr (ey != 0 && ez != 0) return ez > 0 ? v[1] + v[2] : v[1] - v[2];
+  else if constexpr (ex != 0) return v[0];
+  else if constexpr (ey != 0) return v[1];
+  else return v[2];
+}
+
+// quadratic_equilibrium.py:11-25 in even / odd form:
+//   feq_0 = w_0 rho c0,  S_p = w rho (c0 + a^2 / 2),  D_p = w rho a,   a = e.u / cs^2,  c0 = 1 - u.u / (2 cs^2)
+template <class S, typename R>
+__host__ __device__ __forceinline__ void equilibrium_pairs(R rho, const R (&u)[3], R& feq0, R (&Sp)[N_SLOTS],
+                                                           R (&Dp)[N_SLOTS]) {
+  const R inv_cs2 = R(1.0 / LB_CS2);
+  const R U[3] = {u[0] * inv_cs2, u[1] * inv_cs2, u[2] * inv_cs2};
+  R uxu = fma_(u[2], u[2], u[1] * u[1]);
+  if constexpr (S::D == 3) uxu = fma_(u[0], u[0], uxu);
+  const R c0 = fma_(uxu, R(-1.0 / (2.0 * LB_CS2)), R(1));
+  feq0 = (R(S::w(0)) * rho) * c0;
+  static_for<N_SLOTS>([&](auto sc) {
+    constexpr int s = decltype(sc)::value;
+    if constexpr (has_slot<S, s>) {
+      const R wr = R(S::w(pair_q<S>(s))) * rho;
+      const R a = slot_dot<s, R>(U);
+      const R sym = fma_(R(0.5) * a, a, c0);
+      Sp[s] = wr * sym;
+      Dp[s] = wr * a;
+    }
   });
-  const T ri = T(1) / r;   // one reciprocal, six products
-  return kbc_s_from_moments<S, T>(r, mxx * ri, myy * ri, mzz * ri, mxy * ri, mxz * ri, myz * ri);
 }
 
-// s(feq) in closed form.  The reference sums e_a e_b feq_q numerically (kbc_collision.py:146-147);
-// for the quadratic equilibrium on D2Q9 / D3Q27 those sums are, identically,
-//   sum_q feq_q = rho   and   sum_q e_a e_b feq_q / rho = cs^2 delta_ab + u_a u_b ,
-// so the closed form differs from the reference's sums only by their round-off (a few ulp of
-// rho).  NOT used by default: measured on B200 it did not make the (latency-bound) KBC kernel
-// faster, and one fp32 parity case moved from 2e-6 to 1.4e-5 relative, outside the 1e-5 bar.
-template <class S, typename T>
-__device__ __forceinline__ KbcS<T> kbc_s_equilibrium(T rho, const T (&u)[3]) {
-  constexpr T cs2 = T(LB_CS2);
-  const T ux = u[S::axis(0)], uy = u[S::axis(1)];
-  const T uz = (S::D == 3) ? u[S::axis(S::D == 3 ? 2 : 0)] : T(0);
-  return kbc_s_from_moments<S, T>(rho, cs2 + ux * ux, cs2 + uy * uy, (S::D == 3) ? cs2 + uz * uz : T(0),
-                                  ux * uy, ux * uz, uy * uz);
-}
-
-// delta_s of population q from the distinct differences
-template <class S, typename T, int q>
-__device__ __forceinline__ T kbc_ds(const KbcS<T>& d) {
-  if constexpr (q == 0) return d.s0;
-  if constexpr (S::D == 3) {
-    if constexpr (q == 1 || q == 2) return d.sA;
-    else if constexpr (q == 3 || q == 4) return d.sB;
-    else if constexpr (q == 5 || q == 6) return d.sC;
-    else if constexpr (q == 7 || q == 8) return d.pyz;
-    else if constexpr (q == 9 || q == 10) return -d.pyz;
-    else if constexpr (q == 11 || q == 12) return d.pxz;
-    else if constexpr (q == 13 || q == 14) return -d.pxz;
-    else if constexpr (q == 15 || q == 16) return d.pxy;
-    else if constexpr (q == 17 || q == 18) return -d.pxy;
-    else return T(0);
-  } else {
-    if constexpr (q == 1 || q == 3) return d.sA;
-    else if constexpr (q == 2 || q == 4) return d.sB;
-    else if constexpr (q == 5 || q == 7) return d.pxy;
-    else return -d.pxy;
-  }
+// full equilibrium, population by population (boundaries, initialisation)
+template <class S, typename R>
+__host__ __device__ __forceinline__ void equilibrium(R rho, const R (&u)[3], R (&feq)[S::Q]) {
+  R Sp[N_SLOTS], Dp[N_SLOTS];
+  equilibrium_pairs<S, R>(rho, u, feq[0], Sp, Dp);
+  static_for<N_SLOTS>([&](auto sc) {
+    constexpr int s = decltype(sc)::value;
+    if constexpr (has_slot<S, s>) {
+      constexpr int q = pair_q<S>(s), o = S::opp(q);
+      feq[q] = Sp[s] + Dp[s];
+      feq[o] = Sp[s] - Dp[s];
+    }
+  });
 }
 
 enum { COLL_NONE = 0, COLL_BGK = 1, COLL_TRT = 2, COLL_KBC = 3 };
 
-// f <- collision(f); rho, u are the moments of the incoming f (already computed).
-template <class S, typename T, int COLL>
-__device__ __forceinline__ void collide_node(T (&f)[S::Q], T rho, const T (&u)[3],
-                                             const CollisionParams<T>& cp) {
+// ---------------------------------------------------------------------------------------
+// KBC (kbc_collision.py:25-160).  The reference builds all raw moments of f and of feq with an
+// einsum, normalises by rho, forms  T, N_xz, N_yz, Pi_ab  and from them the "shear part" s of the
+// populations (:44-94).  Written out, that shear part is simply
+//     s_0 = -(M_xx + M_yy + M_zz),  s_{+-A} = M_AA / 2,  s_{edge AB, sign} = sign * M_AB / 4,  s_corner = 0
+// with the UN-normalised second moments M_AB = sum_q e_A e_B f_q  (the 1/rho and the factor rho
+// cancel; 2-D: s_{1,3} = M_xx/2, s_{2,4} = M_yy/2, s_{5,7} = -s_{6,8} = M_xy/4), and
+// delta_s = s(f) - s(feq) is linear in f - feq:  it needs the second moments of the pair sums
+// n_p = a_p - 2 S_p of the non-equilibrium part only.  Same quantity as the reference's, with less
+// cancellation (the reference subtracts two O(rho) numbers).
+// ---------------------------------------------------------------------------------------
+template <class S, typename R>
+__host__ __device__ __forceinline__ void kbc_relax(R (&f)[S::Q], R feq0, const R (&a)[N_SLOTS], const R (&Sp)[N_SLOTS],
+                                                   const R (&Dp)[N_SLOTS], R beta, R inv_beta) {
+  static_assert(S::ID != 1, "KBC is defined for D2Q9 and D3Q27 only (kbc_collision.py:101,115)");
+  using scalar = typename ValueTraits<R>::scalar;
+  R n[N_SLOTS];
+  static_for<N_SLOTS>([&](auto sc) {
+    constexpr int s = decltype(sc)::value;
+    if constexpr (has_slot<S, s>) n[s] = fma_(R(-2), Sp[s], a[s]);
+  });
+  const EvenMoments<R> dm = even_moments<S, R>(n);   // .sum unused
+  // delta_s per direction class (index = slot; corners 9..12 have none), and for population 0
+  R ds[9];
+  R ds0;
+  if constexpr (S::D == 3) {
+    ds0 = -((dm.xx + dm.yy) + dm.zz);
+    ds[0] = R(0.5) * dm.xx;
+  } else {
+    ds0 = -(dm.yy + dm.zz);
+  }
+  ds[1] = R(0.5) * dm.yy;
+  ds[2] = R(0.5) * dm.zz;
+  ds[3] = R(0.25) * dm.yz;
+  ds[4] = -ds[3];
+  if constexpr (S::D == 3) {
+    ds[5] = R(0.25) * dm.xz;
+    ds[6] = -ds[5];
+    ds[7] = R(0.25) * dm.xy;
+    ds[8] = -ds[7];
+  }
+  // delta_h = f - feq - delta_s;  sum_s = sum ds dh / feq,  sum_h = sum dh dh / feq  (:148-152);
+  // fn = f - feq is kept for the update, feq itself is dead after this pass
+  R fn[S::Q];
+  R sum_s, sum_h;
+  {
+    fn[0] = f[0] - feq0;
+    const R dh = fn[0] - ds0;
+    const R w = dh * rcp_fast(feq0);
+    sum_s = ds0 * w;
+    sum_h = dh * w;
+  }
+  static_for<N_SLOTS>([&](auto sc) {
+    constexpr int s = decltype(sc)::value;
+    if constexpr (has_slot<S, s>) {
+      constexpr int q = pair_q<S>(s), o = S::opp(q);
+      const R fq = Sp[s] + Dp[s], fo = Sp[s] - Dp[s];
+      fn[q] = f[q] - fq;
+      fn[o] = f[o] - fo;
+      if constexpr (s < 9) {
+        const R dhq = fn[q] - ds[s], dho = fn[o] - ds[s];
+        const R wq = dhq * rcp_fast(fq), wo = dho * rcp_fast(fo);
+        sum_s = fma_(ds[s], wq, sum_s);
+        sum_s = fma_(ds[s], wo, sum_s);
+        sum_h = fma_(dhq, wq, sum_h);
+        sum_h = fma_(dho, wo, sum_h);
+      } else {
+        const R wq = fn[q] * rcp_fast(fq), wo = fn[o] * rcp_fast(fo);
+        sum_h = fma_(fn[q], wq, sum_h);
+        sum_h = fma_(fn[o], wo, sum_h);
+      }
+    }
+  });
+  // gamma = 1/beta - (2 - 1/beta) sum_s / sum_h, guards of :153-157
+  R gamma = fma_(-(R(2) - inv_beta), div_(sum_s, sum_h), inv_beta);
+  gamma = lt_select(gamma, scalar(1E-15), scalar(2));
+  gamma = nan_select(gamma, scalar(2));
+  // f - beta (2 ds + gamma dh)  =  f - beta gamma (f - feq) - beta (2 - gamma) ds   (:158)
+  const R bg = beta * gamma;
+  const R bs = beta * (R(2) - gamma);
+  f[0] = fma_(-bg, fn[0], f[0] - bs * ds0);
+  static_for<N_SLOTS>([&](auto sc) {
+    constexpr int s = decltype(sc)::value;
+    if constexpr (has_slot<S, s>) {
+      constexpr int q = pair_q<S>(s), o = S::opp(q);
+      if constexpr (s < 9) {
+        const R k = bs * ds[s];
+        f[q] = fma_(-bg, fn[q], f[q] - k);
+        f[o] = fma_(-bg, fn[o], f[o] - k);
+      } else {
+        f[q] = fma_(-bg, fn[q], f[q]);
+        f[o] = fma_(-bg, fn[o], f[o]);
+      }
+    }
+  });
+}
+
+// f <- collision(f), given the pair sums / differences and the moments of the incoming f
+template <class S, typename R, int COLL, typename T>
+__host__ __device__ __forceinline__ void collide_node(R (&f)[S::Q], const R (&a)[N_SLOTS], const R (&b)[N_SLOTS],
+                                                      R rho, const R (&u)[3], const CollisionParams<T>& cp) {
   if constexpr (COLL == COLL_NONE) {
     return;  // no_collision.py:9-11
   } else {
-    T feq[S::Q];
-    equilibrium<S, T>(rho, u, feq);
+    R feq0, Sp[N_SLOTS], Dp[N_SLOTS];
+    equilibrium_pairs<S, R>(rho, u, feq0, Sp, Dp);
     if constexpr (COLL == COLL_BGK) {
       // bgk_collision.py:22: f - 1.0/tau * (f - feq)
-      static_for<S::Q>([&](auto qc) {
-        constexpr int q = decltype(qc)::value;
-        f[q] = f[q] - cp.omega * (f[q] - feq[q]);
+      const R om = R(cp.omega);
+      f[0] = fma_(om, feq0 - f[0], f[0]);
+      static_for<N_SLOTS>([&](auto sc) {
+        constexpr int s = decltype(sc)::value;
+        if constexpr (has_slot<S, s>) {
+          constexpr int q = pair_q<S>(s), o = S::opp(q);
+          f[q] = fma_(om, (Sp[s] + Dp[s]) - f[q], f[q]);
+          f[o] = fma_(om, (Sp[s] - Dp[s]) - f[o], f[o]);
+        }
       });
     } else if constexpr (COLL == COLL_TRT) {
-      // trt_collision.py:20-26, evaluated once per opposite pair (q, o): with
-      //   sp = ((f_q + f_o) - (feq_q + feq_o)) / (2 tau+),  sm = ((f_q - f_o) - (feq_q - feq_o)) / (2 tau-)
-      // the reference's values are f_q - (sp + sm) and f_o - (sp - sm): identical bit for bit, since
-      // the symmetric part is commutative and the antisymmetric part changes sign exactly.
-      static_for<S::Q>([&](auto qc) {
-        constexpr int q = decltype(qc)::value;
-        constexpr int o = S::opp(q);
-        if constexpr (q <= o) {
-          const T sp = ((f[q] + f[o]) - (feq[q] + feq[o])) * cp.inv_2tau_p;
-          const T sm = ((f[q] - f[o]) - (feq[q] - feq[o])) * cp.inv_2tau_m;
-          const T fq = f[q], fo = f[o];
-          f[q] = fq - (sp + sm);
-          if constexpr (q < o) f[o] = fo - (sp - sm);
+      // trt_collision.py:20-26 per opposite pair:  sp = ((f_q + f_o) - (feq_q + feq_o)) / (2 tau+),
+      // sm = ((f_q - f_o) - (feq_q - feq_o)) / (2 tau-);  f_q - (sp + sm),  f_o - (sp - sm).
+      const R itp = R(cp.inv_2tau_p), itm = R(cp.inv_2tau_m);
+      f[0] = fma_(-(R(2) * itp), f[0] - feq0, f[0]);
+      static_for<N_SLOTS>([&](auto sc) {
+        constexpr int s = decltype(sc)::value;
+        if constexpr (has_slot<S, s>) {
+          constexpr int q = pair_q<S>(s), o = S::opp(q);
+          const R sp = fma_(R(-2), Sp[s], a[s]) * itp;
+          const R sm = fma_(R(-2), Dp[s], b[s]) * itm;
+          f[q] = f[q] - (sp + sm);
+          f[o] = f[o] - (sp - sm);
         }
       });
     } else {
-      // kbc_collision.py:131-158
-      static_assert(S::ID != 1, "KBC is defined for D2Q9 and D3Q27 only (kbc_collision.py:101,115)");
-      const KbcS<T> sf = kbc_s<S, T>(f);
-#ifdef LB_KBC_ANALYTIC_FEQ   // experiment only: 10 % fewer instructions, one parity outlier
-      const KbcS<T> se = kbc_s_equilibrium<S, T>(rho, u);
-#else
-      const KbcS<T> se = kbc_s<S, T>(feq);
-#endif
-      KbcS<T> d;   // delta_s = s(f) - s(feq), per distinct value
-      d.s0 = sf.s0 - se.s0; d.sA = sf.sA - se.sA; d.sB = sf.sB - se.sB; d.sC = sf.sC - se.sC;
-      d.pyz = sf.pyz - se.pyz; d.pxz = sf.pxz - se.pxz; d.pxy = sf.pxy - se.pxy;
-      T sum_s = T(0), sum_h = T(0);
-      T dh[S::Q];
-      static_for<S::Q>([&](auto qc) {
-        constexpr int q = decltype(qc)::value;
-        const T ds = kbc_ds<S, T, q>(d);
-        dh[q] = f[q] - feq[q] - ds;
-        const T w = dh[q] * fast_rcp<T>(feq[q]);   // (ds dh / feq, dh dh / feq) share 1 / feq
-        sum_s += ds * w;
-        sum_h += dh[q] * w;
-      });
-      T gamma = cp.inv_beta - (T(2) - cp.inv_beta) * sum_s / sum_h;
-      if (gamma < T(1E-15)) gamma = T(2);   // :154
-      if (gamma != gamma) gamma = T(2);     // NaN guard :156
-      static_for<S::Q>([&](auto qc) {
-        constexpr int q = decltype(qc)::value;
-        f[q] = f[q] - cp.beta * (T(2) * kbc_ds<S, T, q>(d) + gamma * dh[q]);
-      });
+      kbc_relax<S, R>(f, feq0, a, Sp, Dp, R(cp.beta), R(cp.inv_beta));
     }
+  }
+}
+
+// convenience: collision of one value from its populations alone
+template <class S, typename R, int COLL, typename T>
+__host__ __device__ __forceinline__ void collide_node(R (&f)[S::Q], const CollisionParams<T>& cp) {
+  if constexpr (COLL != COLL_NONE) {
+    R a[N_SLOTS], b[N_SLOTS], rho, u[3];
+    pair_split<S, R>(f, a, b);
+    moments_from_pairs<S, R>(f[0], a, b, rho, u);
+    collide_node<S, R, COLL, T>(f, a, b, rho, u, cp);
   }
 }
 
 // bounce_back_boundary.py:17-18: f <- f[opposite]
 template <class S, typename T>
-__device__ __forceinline__ void bounce_back_node(T (&f)[S::Q]) {
+__host__ __device__ __forceinline__ void bounce_back_node(T (&f)[S::Q]) {
   static_for<S::Q>([&](auto qc) {
     constexpr int q = decltype(qc)::value;
     constexpr int o = S::opp(q);

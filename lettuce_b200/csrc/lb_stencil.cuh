@@ -6,6 +6,16 @@
 // f[q][x][y] is run as X = 1, Y = x, Z = y, so D2Q9's (ex, ey) become (0, ex, ey).
 #pragma once
 #include <cstdint>
+#include <type_traits>
+
+// tests/host_emul compiles the arithmetic headers (lb_stencil.cuh, lb_values.cuh, lb_physics.cuh)
+// with a plain C++ compiler to study round-off of formula variants on the CPU: TEST TOOLING ONLY,
+// nothing in the product ever runs these functions on the host.
+#if !defined(__CUDACC__)
+#define __host__
+#define __device__
+#define __forceinline__ inline __attribute__((always_inline))
+#endif
 
 namespace lb {
 

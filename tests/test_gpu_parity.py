@@ -134,7 +134,8 @@ SHAPES = {
 }
 
 
-def _run_pair(stencil, dtype, res, collision, params, n_steps, seed, masks=False, amp=0.1):
+def _build_pair(stencil, dtype, res, collision, params, seed, masks=False, amp=0.1):
+    """the same seeded case as an lt.Simulation on the GPU and as oracle inputs"""
     from oracle import lbm_oracle as orc
     gu, lt = _gpu()
     rng = np.random.default_rng(seed)
@@ -159,9 +160,70 @@ def _run_pair(stencil, dtype, res, collision, params, n_steps, seed, masks=False
         ncm, nsm = orc.build_masks(lat, res, obnds, [smask])
     sim = lt.Simulation(flow, gu.make_collision(dict(collision=collision, tau=params.get("tau"),
                                                      tau_minus=params.get("tau_minus", 1.0))), [])
+    return sim, lat, f0, ncm, nsm, obnds
+
+
+def _run_pair(stencil, dtype, res, collision, params, n_steps, seed, masks=False, amp=0.1):
+    from oracle import lbm_oracle as orc
+    sim, lat, f0, ncm, nsm, obnds = _build_pair(stencil, dtype, res, collision, params, seed, masks, amp)
     sim(n_steps)
     ref = orc.run(lat, f0, n_steps, collision, params, ncm=ncm, nsm=nsm, boundaries=obnds)
     return sim.flow.f.cpu().numpy(), ref.numpy()
+
+
+# KBC in fp32 on random (unphysical) fields.  gamma = 1/beta - (2 - 1/beta) sum_s / sum_h is followed
+# by the guard `gamma < 1e-15 -> 2` (kbc_collision.py:153-157): a DISCONTINUITY.  On these fields a few
+# nodes per thousand have gamma near 0 or |gamma| >> 1, and there the reference's own fp32 result is
+# decided by its round-off: evaluated in fp64 on the same fp32 state, the reference moves by up to 1e-4
+# (measured: oracle fp32 vs oracle fp64 after ONE step 1.05e-5 on D2Q9 24x512, seed 300), i.e. it does
+# not meet the 1e-5 bar against itself.  A trajectory comparison is then a coin toss on every such
+# node, whatever the kernel does.  So these cases are compared step by step, each step restarted from
+# the GPU state:
+#  * wherever the reference is self-consistent (fp32 vs fp64 evaluation within 2e-6) and not at the
+#    guard, the kernel must match the fp32 reference to 1e-5;
+#  * on the remaining elements (< 1 %) it must match, to 1e-5, the reference evaluated in fp64 -- on
+#    either side of the guard where gamma lies within +-KBC_GUARD_BAND of it.
+KBC_GUARD_BAND = 0.05
+
+
+def kbc_f32_stepwise_errors(out, prev, orc, lat, lat64, params, ncm, nsm, obnds, obnds64):
+    """(worst error on well-conditioned elements vs the fp32 reference, worst error on the others vs
+    the fp64 reference, number of the others) for one step prev -> out"""
+    out = out.astype(np.float64)
+    ref32 = orc.step(lat, prev, "kbc", params, ncm=ncm, nsm=nsm, boundaries=obnds).numpy().astype(np.float64)
+    p64 = prev.double()
+    ref64 = orc.step(lat64, p64, "kbc", params, ncm=ncm, nsm=nsm, boundaries=obnds64).numpy()
+    lo = orc.step(lat64, p64, "kbc", dict(params, kbc_guard=-KBC_GUARD_BAND), ncm=ncm, nsm=nsm,
+                  boundaries=obnds64).numpy()
+    hi = orc.step(lat64, p64, "kbc", dict(params, kbc_guard=KBC_GUARD_BAND), ncm=ncm, nsm=nsm,
+                  boundaries=obnds64).numpy()
+    scale = np.abs(ref32).max()
+    special = (np.abs(ref32 - ref64) > 2e-6 * scale) | (lo != hi)
+    e32 = np.abs(out - ref32) / scale
+    e64 = np.minimum(np.minimum(np.abs(out - ref64), np.abs(out - lo)), np.abs(out - hi)) / scale
+    return (float(e32[~special].max()), float(e64[special].max()) if special.any() else 0.0,
+            int(special.sum()))
+
+
+def _kbc_f32_stepwise(stencil, res, params, n_steps, seed, masks, amp):
+    from oracle import lbm_oracle as orc
+    sim, lat, f0, ncm, nsm, obnds = _build_pair(stencil, "f32", res, "kbc", params, seed, masks, amp)
+    lat64 = orc.OracleLattice(stencil, torch.float64)
+    obnds64 = [orc.OracleBoundary(b.kind, b.mask, rho=None if b.rho is None else b.rho.double(),
+                                  u=None if b.u is None else b.u.double()) for b in obnds]
+    worst = 0.0
+    n_special = 0
+    for _ in range(n_steps):
+        prev = sim.flow.f.cpu().clone()
+        sim(1)
+        e32, e64, n = kbc_f32_stepwise_errors(sim.flow.f.cpu().numpy(), prev, orc, lat, lat64, params, ncm, nsm,
+                                              obnds, obnds64)
+        assert e32 <= TOL["f32"], f"{stencil} kbc f32 {res}: {e32:.3e}"
+        assert e64 <= TOL["f32"], f"{stencil} kbc f32 {res}: {e64:.3e} (vs the reference evaluated in fp64)"
+        worst = max(worst, e32)
+        n_special += n
+    assert n_special <= 0.01 * n_steps * prev.numel()
+    return worst, n_special
 
 
 @pytest.mark.parametrize("stencil", list(SHAPES))
@@ -192,6 +254,11 @@ def test_collisions_vs_oracle(stencil, collision, dtype, masks):
     if collision == "trt":
         params["tau_minus"] = 0.9
     for k, res in enumerate(SHAPES[stencil][:3]):
+        if collision == "kbc" and dtype == "f32":
+            err, n_incons = _kbc_f32_stepwise(stencil, res, params, 10, seed=300 + k, masks=masks, amp=0.02)
+            print(f"rel_err {stencil} {collision} {dtype} {res} masks={masks}: {err:.3e} per step "
+                  f"({n_incons} elements at the gamma guard or where the fp32 reference is not self-consistent)")
+            continue
         out, ref = _run_pair(stencil, dtype, res, collision, params, 10, seed=300 + k, masks=masks,
                              amp=0.02)
         err = rel_err(out, ref)
