@@ -84,6 +84,16 @@ lb::CollisionParams<T> make_cp(const lb_desc* d) {
 
 bool aligned_to(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
 
+// the largest grid any kernel launches over this lattice: one node per thread
+size_t max_blocks(const Geometry& g) { return (size_t(g.n_nodes) + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK; }
+
+// lay out the reduction scratch and zero its ticket counters
+int obs_prepare(const Geometry& g, void* scratch, lb::ObsScratch* out, cudaStream_t st) {
+  *out = lb::obs_layout(scratch, max_blocks(g));
+  LB_CUDA(cudaMemsetAsync(scratch, 0, lb::obs_counter_bytes(max_blocks(g)), st));
+  return LB_OK;
+}
+
 // nodes per thread along the contiguous axis: the widest of 16 / 8 / 4(8) bytes that divides the
 // line and matches the buffers' alignment.  LB_VEC=<n> overrides the choice (tuning experiments).
 template <typename T>
@@ -91,14 +101,66 @@ int vector_width(const lb_desc* d, const Geometry& g, const void* a, const void*
   if (sbits) return 1;
   const int widest = 16 / int(sizeof(T));
   int cap = widest;
-  // D3Q27 KBC holds ~60 values per node in registers: fp32 runs two nodes per thread as packed F2
-  // values (164 registers, three blocks per SM), fp64 one node per thread
+  // D3Q27 KBC / TRT hold ~60 values per node in registers beside the populations: fp32 runs two nodes
+  // per thread as packed F2 values (<= 168 registers, three blocks per SM; measured 0.92 / 0.97 of the
+  // HBM roofline against 0.82 / 0.91 with four nodes), fp64 KBC one node per thread
   if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_KBC) cap = (sizeof(T) == 4) ? 2 : 1;
+  if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_TRT && sizeof(T) == 4) cap = 2;
   static const char* env = getenv("LB_VEC");
   if (env && atoi(env) >= 1) cap = atoi(env) < widest ? atoi(env) : widest;
   for (int v = cap; v > 1; v >>= 1)
     if (g.nz % unsigned(v) == 0 && aligned_to(a, v * sizeof(T)) && aligned_to(b, v * sizeof(T))) return v;
   return 1;
+}
+
+// Second stage of the step kernel's fused reduction: n_blocks per-block partials -> out[0..n_out).
+// OBS_FINISH_CHUNKS blocks each sum a contiguous chunk in a fixed order; the last to finish (ticket;
+// these few blocks are all resident, nothing waits on them) sums the chunk results.  Deterministic:
+// the chunking depends on n_blocks only.
+constexpr int OBS_FINISH_CHUNKS = 128;
+constexpr int OBS_FINISH_BLOCK = 256;
+
+__global__ void __launch_bounds__(OBS_FINISH_BLOCK)
+obs_finish_kernel(lb::ObsScratch sc, unsigned n_blocks, double* out, int n_out) {
+  __shared__ bool is_last;
+  const unsigned per = (n_blocks + gridDim.x - 1) / gridDim.x;
+  const unsigned lo = blockIdx.x * per, hi = min(n_blocks, lo + per);
+  double a = 0.0, b = 0.0, c = 0.0;
+  for (unsigned i = lo + threadIdx.x; i < hi; i += OBS_FINISH_BLOCK) {
+    const double* bp = sc.block_partials + size_t(i) * lb::N_OBS_PART;
+    a += bp[0];
+    b = fmax(b, bp[1]);
+    c += bp[2];
+  }
+  lb::block_reduce3<OBS_FINISH_BLOCK>(a, b, c);
+  if (threadIdx.x == 0) {
+    double* gp = sc.group_partials + size_t(blockIdx.x) * lb::N_OBS_PART;
+    gp[0] = a; gp[1] = b; gp[2] = c;
+    __threadfence();
+    is_last = (atomicAdd(sc.global_counter, 1u) == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  a = 0.0; b = 0.0; c = 0.0;
+  if (threadIdx.x < gridDim.x) {
+    const double* gp = sc.group_partials + size_t(threadIdx.x) * lb::N_OBS_PART;
+    a = __ldcg(gp + 0); b = __ldcg(gp + 1); c = __ldcg(gp + 2);
+  }
+  lb::block_reduce3<OBS_FINISH_BLOCK>(a, b, c);
+  if (threadIdx.x == 0) {
+    out[0] = a;
+    if (n_out > 1) out[1] = b;
+    if (n_out > 2) out[2] = c;
+    *sc.global_counter = 0u;
+  }
+}
+
+cudaError_t launch_obs_finish(const lb::ObsScratch& sc, unsigned n_blocks, double* out, int n_out, cudaStream_t st) {
+  const unsigned chunks = (n_blocks + OBS_FINISH_BLOCK - 1) / OBS_FINISH_BLOCK;
+  const unsigned grid = chunks < unsigned(OBS_FINISH_CHUNKS) ? (chunks ? chunks : 1u) : unsigned(OBS_FINISH_CHUNKS);
+  obs_finish_kernel<<<grid, OBS_FINISH_BLOCK, 0, st>>>(sc, n_blocks, out, n_out);
+  return cudaGetLastError();
 }
 
 template <typename T>
@@ -149,13 +211,10 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   p.nzv = g.nz / c.vec;
   p.n_threads = g.nx * g.ny * p.nzv;
 
-  unsigned* counter = nullptr;
-  double* partials = nullptr;
   if (fl->obs_out) {
     if (!fl->obs_scratch) return fail(LB_EINVAL, "obs_out given without obs_scratch");
-    counter = static_cast<unsigned*>(fl->obs_scratch);
-    partials = reinterpret_cast<double*>(static_cast<char*>(fl->obs_scratch) + 64);
-    LB_CUDA(cudaMemsetAsync(counter, 0, 64, st));
+    rc = obs_prepare(g, fl->obs_scratch, &p.obs, st);
+    if (rc) return rc;
   }
   const lb_halo* h = fl->halo;
   bool halo_sync = false;
@@ -199,6 +258,26 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   }
   T* a = static_cast<T*>(fl->f);
   T* b = static_cast<T*>(fl->f_next);
+  static_assert(lb::OBS_STRIDE == LB_OBS_COUNT, "observable record size");
+  if (!h && do_stream && n_steps > 1) {
+    // small lattice: all n_steps in ONE cooperative launch (grid-wide barrier between steps);
+    // launch_one falls back to the per-step path when the grid is not co-resident
+    static const bool no_loop = getenv("LB_NO_LOOP") != nullptr;   // A/B timing only
+    if (!no_loop) {
+      c.loop_steps = n_steps;
+      c.obs = fl->obs_out != nullptr;
+      p.f_in = a; p.f_out = b;
+      p.obs_out = fl->obs_out;
+      p.u_out = c.obs ? static_cast<T*>(fl->u_out) : nullptr;
+      const unsigned grid = (p.n_threads + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK;
+      if (grid <= 148u * 16u) {   // cannot be co-resident beyond that; skips the occupancy query
+        cudaError_t e = lb::launch_step<S, T>(c, p, st);   // launches nothing unless it can loop
+        if (e != cudaSuccess) return fail(LB_ECUDA, "step kernel launch failed: %s", cudaGetErrorString(e));
+        if (c.looped) return LB_OK;
+      }
+      c.loop_steps = 0;
+    }
+  }
   for (int s = 0; s < n_steps; ++s) {
     if (h) {
       const int k = s & 1;
@@ -219,12 +298,14 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
     p.f_in = a;
     p.f_out = b;
     c.obs = fl->obs_out != nullptr;
-    p.obs_counter = counter;
-    p.obs_partials = partials;
     p.obs_out = c.obs ? fl->obs_out + (size_t)s * LB_OBS_COUNT : nullptr;
     p.u_out = (c.obs && s == n_steps - 1) ? static_cast<T*>(fl->u_out) : nullptr;
     cudaError_t e = lb::launch_step<S, T>(c, p, st);
     if (e != cudaSuccess) return fail(LB_ECUDA, "step kernel launch failed: %s", cudaGetErrorString(e));
+    if (c.obs) {   // second stage of the fused reduction: block partials -> obs_out[s]
+      e = launch_obs_finish(p.obs, (p.n_threads + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK, p.obs_out, lb::N_OBS_PART, st);
+      if (e != cudaSuccess) return fail(LB_ECUDA, "observable reduction launch failed: %s", cudaGetErrorString(e));
+    }
     if (h && h->mode != LB_HALO_PACKED) {
       const int k = s & 1;
       const bool push = h->mode == LB_HALO_PUSH;
@@ -302,7 +383,7 @@ __device__ __forceinline__ T diff6(const T* __restrict__ u, unsigned base, unsig
 template <typename T, int D>
 __global__ void __launch_bounds__(lb::STEP_BLOCK)
 enstrophy_kernel(const T* __restrict__ u, unsigned n0, unsigned n1, unsigned n2, unsigned n_nodes,
-                 double* partials, unsigned* counter, double* out) {
+                 lb::ObsScratch scratch, double* out) {
   // lattice axes: D == 2 -> (n0, n1), D == 3 -> (n0, n1, n2); last is contiguous
   const unsigned tid = blockIdx.x * lb::STEP_BLOCK + threadIdx.x;
   double acc = 0.0;
@@ -330,7 +411,7 @@ enstrophy_kernel(const T* __restrict__ u, unsigned n0, unsigned n1, unsigned n2,
     }
   }
   // deterministic reduction; the single sum lands in the enstrophy slot
-  lb::reduce_observables<lb::STEP_BLOCK>(acc, 0.0, 0.0, partials, counter, out + LB_OBS_ENSTROPHY, 1);
+  lb::reduce_observables<lb::STEP_BLOCK>(acc, 0.0, 0.0, scratch, out + LB_OBS_ENSTROPHY, 1);
 }
 
 }  // namespace
@@ -395,8 +476,7 @@ int lb_pack_streaming_mask(const lb_desc* desc, const uint8_t* nsm, uint32_t* bi
 size_t lb_obs_scratch_bytes(const lb_desc* desc) {
   Geometry g;
   if (check_desc(desc, &g)) return 0;
-  const size_t blocks = (size_t(g.n_nodes) + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK;
-  return 64 + blocks * lb::N_OBS_PART * sizeof(double);
+  return lb::obs_scratch_bytes(max_blocks(g));
 }
 
 }  // extern "C"
@@ -413,9 +493,8 @@ int moments_typed(const Geometry& g, const void* f, void* rho_out, void* u_out, 
   p.n_nodes = g.n_nodes;
   p.obs_out = obs_out;
   if (obs_out) {
-    p.obs_counter = static_cast<unsigned*>(scratch);
-    p.obs_partials = reinterpret_cast<double*>(static_cast<char*>(scratch) + 64);
-    LB_CUDA(cudaMemsetAsync(p.obs_counter, 0, 64, st));
+    const int rc = obs_prepare(g, scratch, &p.obs, st);
+    if (rc) return rc;
   }
   cudaError_t e = lb::launch_moments<S, T>(p, st);
   if (e != cudaSuccess) return fail(LB_ECUDA, "moments kernel launch failed: %s", cudaGetErrorString(e));
@@ -436,18 +515,17 @@ int moments_stencil(const lb_desc* d, const Geometry& g, const void* f, void* r,
 template <typename T>
 int enstrophy_typed(const lb_desc* d, const Geometry& g, const void* u, void* scratch, double* obs_out,
                     cudaStream_t st) {
-  unsigned* counter = static_cast<unsigned*>(scratch);
-  double* partials = reinterpret_cast<double*>(static_cast<char*>(scratch) + 64);
+  lb::ObsScratch sc;
+  const int rc = obs_prepare(g, scratch, &sc, st);
+  if (rc) return rc;
   const unsigned grid = (g.n_nodes + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK;
-  LB_CUDA(cudaMemsetAsync(counter, 0, 64, st));
   if (g.d == 2)
     enstrophy_kernel<T, 2><<<grid, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(u), (unsigned)d->dims[0],
-                                                           (unsigned)d->dims[1], 1u, g.n_nodes, partials,
-                                                           counter, obs_out);
+                                                           (unsigned)d->dims[1], 1u, g.n_nodes, sc, obs_out);
   else
     enstrophy_kernel<T, 3><<<grid, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(u), (unsigned)d->dims[0],
                                                            (unsigned)d->dims[1], (unsigned)d->dims[2],
-                                                           g.n_nodes, partials, counter, obs_out);
+                                                           g.n_nodes, sc, obs_out);
   LB_CUDA(cudaGetLastError());
   return LB_OK;
 }

@@ -21,9 +21,11 @@
 // value, so every (q, node) of the output is written exactly once (no race, unlike the
 // reference's generated kernel, SURVEY section 3.3 "semantic trap").
 #pragma once
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 
 #include "lb_physics.cuh"
 
@@ -35,6 +37,34 @@ constexpr int N_OBS_PART = 3;  // energy, max|u|^2, mass
 
 enum { BND_BOUNCE_BACK = 1, BND_EQUILIBRIUM = 2 };
 enum { MODE_PLAIN = 0, MODE_NCM = 1, MODE_NCM_SBITS = 2 };
+
+// Scratch of the fused reductions (lb_obs_scratch_bytes): ticket counters and per-block / per-group
+// partial results.  All counters are zero between launches (each is reset by its last user).
+constexpr int OBS_GROUP = 256;   // blocks per first-level group
+struct ObsScratch {
+  unsigned* global_counter;   // groups finished
+  unsigned* group_counters;   // [n_groups] blocks finished per group
+  double* block_partials;     // [grid][N_OBS_PART]
+  double* group_partials;     // [n_groups][N_OBS_PART]
+};
+
+__host__ __device__ inline size_t obs_groups(size_t blocks) { return (blocks + OBS_GROUP - 1) / OBS_GROUP; }
+// bytes of the counter region in front (header + group counters, padded to 64)
+__host__ __device__ inline size_t obs_counter_bytes(size_t max_blocks) {
+  return 64 + ((obs_groups(max_blocks) * sizeof(unsigned) + 63) / 64) * 64;
+}
+__host__ __device__ inline size_t obs_scratch_bytes(size_t max_blocks) {
+  return obs_counter_bytes(max_blocks) + (max_blocks + obs_groups(max_blocks)) * N_OBS_PART * sizeof(double);
+}
+inline ObsScratch obs_layout(void* scratch, size_t max_blocks) {
+  ObsScratch o;
+  char* base = static_cast<char*>(scratch);
+  o.global_counter = reinterpret_cast<unsigned*>(base);
+  o.group_counters = reinterpret_cast<unsigned*>(base + 64);
+  o.block_partials = reinterpret_cast<double*>(base + obs_counter_bytes(max_blocks));
+  o.group_partials = o.block_partials + max_blocks * N_OBS_PART;
+  return o;
+}
 
 template <typename T>
 struct BoundaryDev {
@@ -58,8 +88,7 @@ struct StepParams {
   CollisionParams<T> cp;
   int n_bnd;
   BoundaryDev<T> bnd[MAX_BND];
-  double* obs_partials;        // [gridDim.x][N_OBS_PART]
-  unsigned* obs_counter;
+  ObsScratch obs;              // scratch of the fused reductions
   double* obs_out;             // [LB_OBS_COUNT]
   T* u_out;                    // [D][n_nodes] or nullptr
   // z-slab decomposition (multi-GPU): when set, populations leaving the slab through its
@@ -115,68 +144,96 @@ __device__ __forceinline__ uint32_t ld_mask(const uint8_t* p) {
   else return *p;
 }
 
-// Deterministic block reduction (sum, max, sum) followed by the "last block finishes"
-// pattern: no atomics on the values, fixed summation order -> bitwise reproducible.
-template <int BLOCK>
-__device__ __forceinline__ void reduce_observables(double e, double m2, double mass,
-                                                   double* partials, unsigned* counter,
-                                                   double* out, int n_out = N_OBS_PART) {
+// (sum, max, sum) over the block; the result is valid in thread 0.  Fixed order: lanes by a
+// shuffle tree in the accumulator type A (float partials of an fp32 lattice stay float inside the
+// warp: 64 nodes, half the shuffles of a double), then warps in order in double.
+template <int BLOCK, typename A>
+__device__ __forceinline__ void block_reduce3(A wa, A wb, A wc, double& a, double& b, double& c) {
   __shared__ double sm[N_OBS_PART][BLOCK / 32];
-  __shared__ bool is_last;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
-    e += __shfl_down_sync(0xffffffffu, e, o);
-    m2 = fmax(m2, __shfl_down_sync(0xffffffffu, m2, o));
-    mass += __shfl_down_sync(0xffffffffu, mass, o);
+    wa += __shfl_down_sync(0xffffffffu, wa, o);
+    wb = max_(wb, __shfl_down_sync(0xffffffffu, wb, o));
+    wc += __shfl_down_sync(0xffffffffu, wc, o);
   }
-  if (lane == 0) { sm[0][warp] = e; sm[1][warp] = m2; sm[2][warp] = mass; }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double a = sm[0][0], b = sm[1][0], c = sm[2][0];
-#pragma unroll
-    for (int w = 1; w < BLOCK / 32; ++w) { a += sm[0][w]; b = fmax(b, sm[1][w]); c += sm[2][w]; }
-    partials[blockIdx.x * N_OBS_PART + 0] = a;
-    partials[blockIdx.x * N_OBS_PART + 1] = b;
-    partials[blockIdx.x * N_OBS_PART + 2] = c;
-    __threadfence();
-    const unsigned prev = atomicAdd(counter, 1u);
-    is_last = (prev == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (!is_last) return;
-  __threadfence();
-  double a = 0.0, b = 0.0, c = 0.0;
-  for (unsigned i = threadIdx.x; i < gridDim.x; i += BLOCK) {
-    a += __ldcg(&partials[i * N_OBS_PART + 0]);
-    b = fmax(b, __ldcg(&partials[i * N_OBS_PART + 1]));
-    c += __ldcg(&partials[i * N_OBS_PART + 2]);
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    a += __shfl_down_sync(0xffffffffu, a, o);
-    b = fmax(b, __shfl_down_sync(0xffffffffu, b, o));
-    c += __shfl_down_sync(0xffffffffu, c, o);
-  }
-  __syncthreads();
-  if (lane == 0) { sm[0][warp] = a; sm[1][warp] = b; sm[2][warp] = c; }
+  __syncthreads();   // sm may still be read by the previous use
+  if (lane == 0) { sm[0][warp] = double(wa); sm[1][warp] = double(wb); sm[2][warp] = double(wc); }
   __syncthreads();
   if (threadIdx.x == 0) {
     a = sm[0][0]; b = sm[1][0]; c = sm[2][0];
 #pragma unroll
     for (int w = 1; w < BLOCK / 32; ++w) { a += sm[0][w]; b = fmax(b, sm[1][w]); c += sm[2][w]; }
+  }
+}
+template <int BLOCK>
+__device__ __forceinline__ void block_reduce3(double& a, double& b, double& c) {
+  block_reduce3<BLOCK, double>(a, b, c, a, b, c);
+}
+
+// Deterministic grid reduction of (sum, max, sum) without value atomics, in two levels so that no
+// single block ever walks more than OBS_GROUP or grid / OBS_GROUP partials (a 512^3 lattice has
+// 5e5 blocks): the last block of each group of OBS_GROUP consecutive blocks to finish (atomic ticket)
+// sums that group's block partials in a fixed order; the last group to finish sums the group partials.
+// Which block does the summing varies from run to run, what it sums and in which order does not:
+// bitwise reproducible.
+template <int BLOCK>
+__device__ __forceinline__ void reduce_observables(double e, double m2, double mass, const ObsScratch& sc,
+                                                   double* out, int n_out = N_OBS_PART) {
+  __shared__ bool is_last;
+  const unsigned grid = gridDim.x, group = blockIdx.x / OBS_GROUP;
+  const unsigned n_groups = (grid + OBS_GROUP - 1) / OBS_GROUP;
+  const unsigned first = group * OBS_GROUP;
+  const unsigned group_size = min(unsigned(OBS_GROUP), grid - first);
+  block_reduce3<BLOCK>(e, m2, mass);
+  if (threadIdx.x == 0) {
+    double* bp = sc.block_partials + size_t(blockIdx.x) * N_OBS_PART;
+    bp[0] = e; bp[1] = m2; bp[2] = mass;
+    __threadfence();
+    is_last = (atomicAdd(&sc.group_counters[group], 1u) == group_size - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  double a = 0.0, b = 0.0, c = 0.0;
+  for (unsigned i = threadIdx.x; i < group_size; i += BLOCK) {
+    const double* bp = sc.block_partials + size_t(first + i) * N_OBS_PART;
+    a += __ldcg(bp + 0);
+    b = fmax(b, __ldcg(bp + 1));
+    c += __ldcg(bp + 2);
+  }
+  block_reduce3<BLOCK>(a, b, c);
+  if (threadIdx.x == 0) {
+    double* gp = sc.group_partials + size_t(group) * N_OBS_PART;
+    gp[0] = a; gp[1] = b; gp[2] = c;
+    sc.group_counters[group] = 0u;
+    __threadfence();
+    is_last = (atomicAdd(sc.global_counter, 1u) == n_groups - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  __threadfence();
+  a = 0.0; b = 0.0; c = 0.0;
+  for (unsigned i = threadIdx.x; i < n_groups; i += BLOCK) {
+    const double* gp = sc.group_partials + size_t(i) * N_OBS_PART;
+    a += __ldcg(gp + 0);
+    b = fmax(b, __ldcg(gp + 1));
+    c += __ldcg(gp + 2);
+  }
+  block_reduce3<BLOCK>(a, b, c);
+  if (threadIdx.x == 0) {
     out[0] = a;                  // LB_OBS_ENERGY (or the single sum when n_out == 1)
     if (n_out > 1) out[1] = b;   // LB_OBS_MAXU2
     if (n_out > 2) out[2] = c;   // LB_OBS_MASS
-    *counter = 0u;
+    *sc.global_counter = 0u;
   }
 }
 
 // One node: moments -> (fused observables) -> collision where ncm == 0, boundary i where ncm == i
 template <class S, typename T, int COLL, int MODE, bool OBS>
-__device__ __forceinline__ void node_update(T (&g)[S::Q], unsigned m, const StepParams<T>& p, unsigned x, unsigned y,
-                                            unsigned z, unsigned node, bool active, T& acc_e, T& acc_m2,
-                                            T& acc_mass) {
+__device__ __forceinline__ void node_update(T (&g)[S::Q], unsigned m, const StepParams<T>& p, T* u_out, unsigned x,
+                                            unsigned y, unsigned z, unsigned node, bool active, T& acc_e,
+                                            T& acc_m2, T& acc_mass) {
   T a[N_SLOTS], b[N_SLOTS];
   T rho = T(0), u[3] = {T(0), T(0), T(0)};
   if (OBS || (COLL != COLL_NONE && m == 0)) {
@@ -188,9 +245,9 @@ __device__ __forceinline__ void node_update(T (&g)[S::Q], unsigned m, const Step
     acc_e += T(0.5) * u2;
     acc_m2 = max_(acc_m2, u2);
     acc_mass += rho;
-    if (p.u_out != nullptr && active) {   // only on steps that feed the enstrophy kernel
+    if (u_out != nullptr && active) {   // only on steps that feed the enstrophy kernel
 #pragma unroll
-      for (int c = 0; c < S::D; ++c) p.u_out[c * size_t(p.n_nodes) + node] = u[S::axis(c)];
+      for (int c = 0; c < S::D; ++c) u_out[c * size_t(p.n_nodes) + node] = u[S::axis(c)];
     }
   }
   if (m == 0) {
@@ -216,8 +273,8 @@ __device__ __forceinline__ void node_update(T (&g)[S::Q], unsigned m, const Step
 
 // Two z-adjacent fp32 fluid nodes (both ncm == 0) as one packed value per population
 template <class S, int COLL, bool OBS>
-__device__ __forceinline__ void packed_update(F2 (&g)[S::Q], const StepParams<float>& p, unsigned node, bool active,
-                                              float& acc_e, float& acc_m2, float& acc_mass) {
+__device__ __forceinline__ void packed_update(F2 (&g)[S::Q], const StepParams<float>& p, float* u_out, unsigned node,
+                                              bool active, float& acc_e, float& acc_m2, float& acc_mass) {
   if constexpr (!OBS && COLL == COLL_NONE) return;
   F2 a[N_SLOTS], b[N_SLOTS], rho, u[3];
   pair_split<S, F2>(g, a, b);
@@ -229,11 +286,11 @@ __device__ __forceinline__ void packed_update(F2 (&g)[S::Q], const StepParams<fl
     acc_m2 = max_(acc_m2, hmax(u2));
     acc_mass += rho.x;
     acc_mass += rho.y;
-    if (p.u_out != nullptr && active) {
+    if (u_out != nullptr && active) {
 #pragma unroll
       for (int c = 0; c < S::D; ++c) {
-        p.u_out[c * size_t(p.n_nodes) + node] = u[S::axis(c)].x;
-        p.u_out[c * size_t(p.n_nodes) + node + 1] = u[S::axis(c)].y;
+        u_out[c * size_t(p.n_nodes) + node] = u[S::axis(c)].x;
+        u_out[c * size_t(p.n_nodes) + node + 1] = u[S::axis(c)].y;
       }
     }
   }
@@ -241,17 +298,19 @@ __device__ __forceinline__ void packed_update(F2 (&g)[S::Q], const StepParams<fl
 }
 
 // Resident blocks asked of the register allocator.  D3Q19 fp32 with 4 nodes per thread: 76 population
-// registers, 4 blocks (<= 128 registers) as measured at the HBM roofline; D3Q27 fp32 with 2 or 4 nodes
-// per thread (54 / 108 population registers): 3 blocks (<= 168 registers).
-template <class S, typename T, int V>
+// registers, 4 blocks (<= 128 registers) as measured at the HBM roofline -- except TRT, whose packed
+// pair form keeps a_p, b_p, S_p, D_p of two nodes live and spills below 168; D3Q27 fp32 with 2 or 4
+// nodes per thread (54 / 108 population registers): 3 blocks (<= 168 registers).
+template <class S, typename T, int V, int COLL>
 constexpr int step_min_blocks() {
-  if (sizeof(T) == 4 && V >= 2) return S::Q == 27 ? 3 : 4;
+  if (sizeof(T) == 4 && V >= 2) return (S::Q == 27 || (COLL == COLL_TRT && V == 4)) ? 3 : 4;
   return 1;
 }
 
-template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO>
-__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V>())
-step_kernel(const __grid_constant__ StepParams<T> p) {
+// One time step of the lattice for this thread: f_in -> f_out (+ observables of f_in when OBS)
+template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO, bool TICKET>
+__device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __restrict__ f_in, T* __restrict__ f_out,
+                                          double* obs_out, T* u_out) {
   static_assert(MODE != MODE_NCM_SBITS || V == 1, "masked streaming runs one node per thread");
   constexpr int Q = S::Q;
   const unsigned lane = threadIdx.x & 31u;
@@ -285,7 +344,7 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
   {
     static_for<Q>([&](auto qc) {
       constexpr int q = decltype(qc)::value;
-      const Vec<T, V> v = ld_vec<T, V>(p.f_in + size_t(q) * N + node);
+      const Vec<T, V> v = ld_vec<T, V>(f_in + size_t(q) * N + node);
 #pragma unroll
       for (int k = 0; k < V; ++k) f[q][k] = v.v[k];
     });
@@ -323,7 +382,7 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
           constexpr int q = decltype(qc)::value;
           g[q] = F2(f[q][2 * kk], f[q][2 * kk + 1]);
         });
-        packed_update<S, COLL, OBS>(g, p, node + 2 * kk, active, acc_e, acc_m2, acc_mass);
+        packed_update<S, COLL, OBS>(g, p, u_out, node + 2 * kk, active, acc_e, acc_m2, acc_mass);
         static_for<Q>([&](auto qc) {
           constexpr int q = decltype(qc)::value;
           f[q][2 * kk] = g[q].x;
@@ -334,7 +393,7 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
         for (int k = 2 * kk; k < 2 * kk + 2; ++k) {
           T g[Q];
           static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
-          node_update<S, T, COLL, MODE, OBS>(g, (m2 >> (8 * (k - 2 * kk))) & 0xffu, p, x, y, z0 + k, node + k, active,
+          node_update<S, T, COLL, MODE, OBS>(g, (m2 >> (8 * (k - 2 * kk))) & 0xffu, p, u_out, x, y, z0 + k, node + k, active,
                                              acc_e, acc_m2, acc_mass);
           static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
         }
@@ -346,7 +405,7 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
       T g[Q];
       static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
       const unsigned m = (MODE == MODE_PLAIN) ? 0u : ((mword >> (8 * k)) & 0xffu);
-      node_update<S, T, COLL, MODE, OBS>(g, m, p, x, y, z0 + k, node + k, active, acc_e, acc_m2, acc_mass);
+      node_update<S, T, COLL, MODE, OBS>(g, m, p, u_out, x, y, z0 + k, node + k, active, acc_e, acc_m2, acc_mass);
       static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
     }
   }
@@ -359,7 +418,7 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
         Vec<T, V> v;
 #pragma unroll
         for (int k = 0; k < V; ++k) v.v[k] = f[q][k];
-        st_vec<T, V>(p.f_out + q * N + node, v);
+        st_vec<T, V>(f_out + q * N + node, v);
       });
     }
   } else {
@@ -390,7 +449,7 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
       const unsigned dlines = xs[ex + 1] + ys[ey + 1];   // destination line number
       const unsigned dline = dlines * nz;                // its first element
       [[maybe_unused]] const unsigned idx = dline + z0;  // this thread's vector in the destination line
-      T* const bq = p.f_out + size_t(q) * N;             // uniform
+      T* const bq = f_out + size_t(q) * N;               // uniform
 
       if constexpr (MODE == MODE_NCM_SBITS) {
         // destination-masked streaming, one node per thread
@@ -461,10 +520,53 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
     });
   }
 
+  // ---- fused observables of f_in ------------------------------------------------------------
   if constexpr (OBS) {
     if (!active) { acc_e = T(0); acc_m2 = T(0); acc_mass = T(0); }
-    reduce_observables<STEP_BLOCK>(double(acc_e), double(acc_m2), double(acc_mass), p.obs_partials,
-                                   p.obs_counter, p.obs_out);
+    if constexpr (TICKET) {
+      reduce_observables<STEP_BLOCK>(double(acc_e), double(acc_m2), double(acc_mass), p.obs, obs_out);
+    } else {
+      // one partial per block, no fence and no ticket: with 5e5 blocks that live ~4 us each, a global
+      // round trip per block on the critical path cost 18 % of the step.  obs_finish_kernel, launched
+      // right behind this grid, adds the partials up (the kernel boundary makes them visible).
+      double a, b, c;
+      block_reduce3<STEP_BLOCK, T>(acc_e, acc_m2, acc_mass, a, b, c);
+      if (threadIdx.x == 0) {
+        double* bp = p.obs.block_partials + size_t(blockIdx.x) * N_OBS_PART;
+        bp[0] = a; bp[1] = b; bp[2] = c;
+      }
+    }
+  }
+}
+
+template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO>
+__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V, COLL>())
+step_kernel(const __grid_constant__ StepParams<T> p) {
+  // Programmatic dependent launch: let the next step's grid be scheduled while this one drains, and
+  // wait here -- before the first global access -- until the previous step's grid has completed and
+  // its stores are visible.  Both are no-ops for a launch without the PDL attribute.
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  step_body<S, T, V, COLL, MODE, OBS, STREAM, HALO, false>(p, p.f_in, p.f_out, p.obs_out, p.u_out);
+}
+
+// Small lattices (the whole grid co-resident on the 148 SMs, state in L2): ONE cooperative launch
+// advances n_loop time steps, ping-ponging f_in / f_out with a grid-wide barrier between steps, so
+// a step costs a barrier (~1 us) instead of a kernel launch.  Step s writes its observables to
+// obs_out + s * OBS_STRIDE; u_out belongs to the last step.  After the call the state is in f_out
+// when n_loop is odd, in f_in when it is even -- the same convention as n_loop separate launches.
+constexpr int OBS_STRIDE = 4;   // == LB_OBS_COUNT (include/lettuce_b200.h)
+
+template <class S, typename T, int V, int COLL, int MODE, bool OBS>
+__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V, COLL>())
+step_loop_kernel(const __grid_constant__ StepParams<T> p, int n_loop) {
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  for (int s = 0; s < n_loop; ++s) {
+    const T* fi = (s & 1) ? p.f_out : p.f_in;
+    T* fo = (s & 1) ? const_cast<T*>(p.f_in) : p.f_out;
+    step_body<S, T, V, COLL, MODE, OBS, true, false, true>(p, fi, fo, OBS ? p.obs_out + size_t(s) * OBS_STRIDE : nullptr,
+                                                     (s == n_loop - 1) ? p.u_out : nullptr);
+    if (s + 1 < n_loop) grid.sync();
   }
 }
 
@@ -478,8 +580,7 @@ struct MomentsParams {
   T* rho_out;   // [n_nodes] or nullptr
   T* u_out;     // [D][n_nodes] or nullptr
   unsigned n_nodes;
-  double* obs_partials;
-  unsigned* obs_counter;
+  ObsScratch obs;
   double* obs_out;  // nullptr: no reduction
 };
 
@@ -509,7 +610,7 @@ moments_kernel(const __grid_constant__ MomentsParams<T> p) {
     double e = active ? double(T(0.5) * u2) : 0.0;
     double m2 = active ? double(u2) : 0.0;
     double mass = active ? double(rho) : 0.0;
-    reduce_observables<STEP_BLOCK>(e, m2, mass, p.obs_partials, p.obs_counter, p.obs_out);
+    reduce_observables<STEP_BLOCK>(e, m2, mass, p.obs, p.obs_out);
   }
 }
 
@@ -528,6 +629,8 @@ cudaError_t launch_moments_impl(const MomentsParams<T>& p, cudaStream_t st) {
 // host-side dispatch (runtime descriptor -> template instantiation), one per (stencil, T)
 // --------------------------------------------------------------------------------------
 struct StepConfig {
+  int loop_steps = 0;   // > 1: try ONE cooperative launch that advances this many steps (small lattices)
+  bool looped = false;  // out: the cooperative launch was used (all loop_steps steps are enqueued)
   int vec;        // nodes per thread: 16 / 8 / 4(8) bytes
   int collision;  // COLL_*
   int mode;       // MODE_*
@@ -539,10 +642,10 @@ struct StepConfig {
 // one explicit specialisation per (stencil, dtype, collision), each in its own translation unit
 // (lb_inst_*.cu) so that `make -j` spreads the ~400 kernel variants over all cores
 template <class S, typename T, int COLL>
-cudaError_t launch_step_coll(const StepConfig& c, const StepParams<T>& p, cudaStream_t st);
+cudaError_t launch_step_coll(StepConfig& c, const StepParams<T>& p, cudaStream_t st);
 
 template <class S, typename T>
-cudaError_t launch_step(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+cudaError_t launch_step(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   switch (c.collision) {
     case COLL_NONE: return launch_step_coll<S, T, COLL_NONE>(c, p, st);
     case COLL_BGK: return launch_step_coll<S, T, COLL_BGK>(c, p, st);
@@ -554,35 +657,77 @@ cudaError_t launch_step(const StepConfig& c, const StepParams<T>& p, cudaStream_
   return cudaErrorInvalidValue;
 }
 
+// blocks of a kernel that fit on the device at once (cached per instantiation)
+template <class K>
+int coresident_blocks(K kernel) {
+  static int cached = -1;
+  if (cached < 0) {
+    int dev = 0, sms = 0, per_sm = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, STEP_BLOCK, 0) != cudaSuccess) {
+      (void)cudaGetLastError();
+      return 0;
+    }
+    cached = sms * per_sm;
+  }
+  return cached;
+}
+
 template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO>
-cudaError_t launch_one(const StepParams<T>& p, cudaStream_t st) {
+cudaError_t launch_one(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   const unsigned grid = (p.n_threads + STEP_BLOCK - 1) / STEP_BLOCK;
-  step_kernel<S, T, V, COLL, MODE, OBS, STREAM, HALO><<<grid, STEP_BLOCK, 0, st>>>(p);
-  return cudaGetLastError();
+  if (c.loop_steps > 1) {
+    // request for ONE launch covering loop_steps steps: honoured if the grid is co-resident, otherwise
+    // nothing is launched and the caller (c.looped == false) issues one launch per step
+    if constexpr (STREAM && !HALO) {
+      auto kernel = step_loop_kernel<S, T, V, COLL, MODE, OBS>;
+      if (int(grid) <= coresident_blocks(kernel)) {
+        int n_loop = c.loop_steps;
+        void* args[] = {const_cast<StepParams<T>*>(&p), &n_loop};
+        const cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(kernel), dim3(grid), dim3(STEP_BLOCK),
+                                                          args, 0, st);
+        if (e == cudaSuccess) c.looped = true;
+        else (void)cudaGetLastError();   // e.g. cooperative launch not supported
+      }
+    }
+    return cudaSuccess;
+  }
+  static const bool no_pdl = getenv("LB_NO_PDL") != nullptr;   // A/B timing only
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(STEP_BLOCK);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = no_pdl ? 0 : 1;
+  return cudaLaunchKernelEx(&cfg, step_kernel<S, T, V, COLL, MODE, OBS, STREAM, HALO>, p);
 }
 
 template <class S, typename T, int V, int COLL, int MODE>
-cudaError_t launch_mode(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+cudaError_t launch_mode(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   if (!c.stream) {
     if constexpr (V == 1 && MODE != MODE_NCM_SBITS)
-      return launch_one<S, T, V, COLL, MODE, false, false, false>(p, st);
+      return launch_one<S, T, V, COLL, MODE, false, false, false>(c, p, st);
     else
       return cudaErrorInvalidValue;
   }
   if (c.halo) {
     if constexpr (MODE != MODE_NCM_SBITS) {
-      if (c.obs) return launch_one<S, T, V, COLL, MODE, true, true, true>(p, st);
-      return launch_one<S, T, V, COLL, MODE, false, true, true>(p, st);
+      if (c.obs) return launch_one<S, T, V, COLL, MODE, true, true, true>(c, p, st);
+      return launch_one<S, T, V, COLL, MODE, false, true, true>(c, p, st);
     } else {
       return cudaErrorNotSupported;
     }
   }
-  if (c.obs) return launch_one<S, T, V, COLL, MODE, true, true, false>(p, st);
-  return launch_one<S, T, V, COLL, MODE, false, true, false>(p, st);
+  if (c.obs) return launch_one<S, T, V, COLL, MODE, true, true, false>(c, p, st);
+  return launch_one<S, T, V, COLL, MODE, false, true, false>(c, p, st);
 }
 
 template <class S, typename T, int V, int COLL>
-cudaError_t launch_vec(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+cudaError_t launch_vec(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   switch (c.mode) {
     case MODE_PLAIN: return launch_mode<S, T, V, COLL, MODE_PLAIN>(c, p, st);
     case MODE_NCM: return launch_mode<S, T, V, COLL, MODE_NCM>(c, p, st);
@@ -594,7 +739,7 @@ cudaError_t launch_vec(const StepConfig& c, const StepParams<T>& p, cudaStream_t
 }
 
 template <class S, typename T, int COLL>
-cudaError_t launch_step_coll_impl(const StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+cudaError_t launch_step_coll_impl(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   constexpr int VEC = 16 / sizeof(T);
   if (c.vec == 1) return launch_vec<S, T, 1, COLL>(c, p, st);
   if (c.vec == VEC) return launch_vec<S, T, VEC, COLL>(c, p, st);
@@ -606,7 +751,7 @@ cudaError_t launch_step_coll_impl(const StepConfig& c, const StepParams<T>& p, c
 
 #define LB_INSTANTIATE_COLL(S, T, COLL)                                                   \
   template <>                                                                             \
-  cudaError_t lb::launch_step_coll<S, T, COLL>(const StepConfig& c, const StepParams<T>& p, \
+  cudaError_t lb::launch_step_coll<S, T, COLL>(StepConfig& c, const StepParams<T>& p,       \
                                                cudaStream_t st) {                         \
     return launch_step_coll_impl<S, T, COLL>(c, p, st);                                   \
   }
