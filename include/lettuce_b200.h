@@ -184,6 +184,19 @@ LB_API int lb_pack_streaming_mask(const lb_desc* desc, const uint8_t* nsm, uint3
 /* rho_out [*res] and/or u_out [d][*res] (either may be NULL) */
 LB_API int lb_moments(const lb_desc* desc, const void* f, void* rho_out, void* u_out, void* stream);
 
+/* Initial populations from (rho, u) in lattice units -- replaces `Flow.initialize`
+ * (lettuce/_flow.py:106-122: f = equilibrium(rho, u)) and, with `with_fneq` != 0, its first-order
+ * non-equilibrium correction `initialize_f_neq` (lettuce/_flow.py:309-336):
+ *   f_q = feq_q(rho, u) - w_q * sum_ab (desc->tau * rho * d_b u_a / cs^2) * (e_qa e_qb - cs^2 delta_ab)
+ * with the 6th-order central difference of `torch_gradient` (lettuce/util/utility.py:37-99, dx = 1).
+ * rho [*res_ext] and u [d][*res_ext] carry `ghost` extra planes on both sides of the LAST axis
+ * (res_ext = res with res[d-1] + 2 ghost; ghost must be 0 or >= 3): ghost = 0 differentiates
+ * periodically, ghost >= 3 reads the neighbouring slab's values from the ghost planes (z-slabs).
+ * f [q][*res] receives the interior.  Nothing larger than (1 + d) / q of f is ever materialised,
+ * which is what lets a 1024^3 lattice be initialised slab by slab. */
+LB_API int lb_initialize(const lb_desc* desc, const void* rho, const void* u, int ghost, int with_fneq,
+                  void* f, void* stream);
+
 /* Standalone reduction of LB_OBS_* over state f into obs_out[LB_OBS_COUNT] (device, double).
  * `want_enstrophy` != 0 additionally needs u_scratch [d][*res] of dtype. */
 LB_API size_t lb_obs_scratch_bytes(const lb_desc* desc);

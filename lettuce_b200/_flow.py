@@ -68,7 +68,7 @@ class Flow(ABC):
         self.torch_stencil = TorchStencil(stencil, context)
         self.equilibrium = equilibrium
         self.i = 0
-        self.f = context.empty_tensor([stencil.q, *resolution])
+        self.f = None          # allocated by initialize() (the reference allocates an empty tensor first, _flow.py:89-91)
         self._f_next = None
         self.initialize()
 
@@ -84,7 +84,8 @@ class Flow(ABC):
 
     def initialize(self):
         """equilibrium of the initial (p, u), optionally with first-order non-equilibrium
-        (_flow.py:106-122)"""
+        (_flow.py:106-122).  On a CUDA context the populations are written by the engine's
+        `lb_initialize` kernel straight from (rho, u): no [q, *res]-sized temporaries."""
         initial_p, initial_u = self.initial_pu()
         initial_rho = self.context.convert_to_tensor(
             self.units.convert_pressure_pu_to_density_lu(initial_p))
@@ -92,9 +93,34 @@ class Flow(ABC):
         if self.initialize_pressure:
             raise NotImplementedError("pressure-Poisson initialisation is outside the hot-path "
                                       "scope (SURVEY.md section 2, row 2)")
+        if self._native_initialize_ok(initial_rho, initial_u):
+            self.f = self._native_initialize(initial_rho, initial_u, ghost=0)
+            return
         self.f = self.equilibrium(self, rho=initial_rho, u=initial_u)
         if self.initialize_fneq:
             self.f = initialize_f_neq(self)
+
+    def _native_initialize_ok(self, rho, u, ghost: int = 0) -> bool:
+        from ._equilibrium import QuadraticEquilibrium
+        ext = list(self.resolution[:-1]) + [self.resolution[-1] + 2 * ghost]
+        return (rho.is_cuda and u.is_cuda and rho.dtype in nat.DTYPE_IDS and u.dtype == rho.dtype
+                and type(self.stencil).__name__ in nat.STENCIL_IDS
+                and type(self.equilibrium) is QuadraticEquilibrium
+                and list(rho.shape) == [1, *ext] and list(u.shape) == [self.stencil.d, *ext]
+                and (not self.initialize_fneq or min(self.resolution) >= 3))
+
+    def _native_initialize(self, rho, u, ghost: int) -> torch.Tensor:
+        """lb_initialize: rho [1, *res_ext], u [d, *res_ext] (lattice units; `ghost` extra planes on
+        both sides of the last axis) -> f [q, *res]"""
+        desc = nat.make_desc(type(self.stencil).__name__, rho.dtype, self.resolution,
+                             tau=float(self.units.relaxation_parameter_lu))
+        rho, u = rho.contiguous(), u.contiguous()
+        f = torch.empty([self.stencil.q, *self.resolution], dtype=rho.dtype, device=rho.device)
+        with torch.cuda.device(rho.device):
+            nat.check(nat.lib().lb_initialize(desc, rho.data_ptr(), u.data_ptr(), int(ghost),
+                                              int(bool(self.initialize_fneq)), f.data_ptr(),
+                                              nat.current_stream_ptr(rho.device)))
+        return f
 
     # ---- second buffer (lazy, _flow.py:124-134) ------------------------------------------
     @property

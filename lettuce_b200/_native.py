@@ -28,7 +28,7 @@ DTYPE_IDS = {torch.float32: LB_F32, torch.float64: LB_F64}
 # every symbol include/lettuce_b200.h declares (checked by tests/test_capi_symbols.py)
 EXPORTED_SYMBOLS = (
     "lb_abi_version", "lb_last_error", "lb_step", "lb_collide", "lb_stream",
-    "lb_pack_streaming_mask", "lb_moments", "lb_obs_scratch_bytes", "lb_observables",
+    "lb_pack_streaming_mask", "lb_moments", "lb_initialize", "lb_obs_scratch_bytes", "lb_observables",
     "lb_enstrophy", "lb_run_host", "lb_stencil_q", "lb_bytes_per_update", "lb_vector_width",
     "lb_unpack_halo", "lb_zface_count", "lb_ipc_alloc", "lb_ipc_free", "lb_ipc_export",
     "lb_ipc_open", "lb_ipc_close",
@@ -95,6 +95,8 @@ def lib() -> C.CDLL:
     L.lb_stream.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.lb_pack_streaming_mask.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p]
     L.lb_moments.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.lb_initialize.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
+                                C.c_void_p]
     L.lb_obs_scratch_bytes.argtypes = [C.POINTER(LbDesc)]
     L.lb_obs_scratch_bytes.restype = C.c_size_t
     L.lb_observables.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
@@ -113,7 +115,7 @@ def lib() -> C.CDLL:
     L.lb_bytes_per_update.argtypes = [C.POINTER(LbDesc)]
     L.lb_bytes_per_update.restype = C.c_size_t
     L.lb_vector_width.argtypes = [C.POINTER(LbDesc), C.c_int]
-    for name in ("lb_step", "lb_collide", "lb_stream", "lb_pack_streaming_mask", "lb_moments",
+    for name in ("lb_step", "lb_collide", "lb_stream", "lb_pack_streaming_mask", "lb_moments", "lb_initialize",
                  "lb_observables", "lb_enstrophy", "lb_run_host", "lb_stencil_q", "lb_vector_width",
                  "lb_unpack_halo", "lb_zface_count", "lb_ipc_alloc", "lb_ipc_free", "lb_ipc_export",
                  "lb_ipc_open", "lb_ipc_close"):

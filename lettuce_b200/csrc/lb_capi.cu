@@ -532,6 +532,132 @@ int enstrophy_typed(const lb_desc* d, const Geometry& g, const void* u, void* sc
 
 }  // namespace
 
+namespace {
+
+// 6th-order central difference along one axis (utility.py:37-99).  `i` is the coordinate along
+// the axis, `n` its length, `stride` its element stride, `base` the element with that coordinate
+// set to 0; PERIODIC wraps the index, otherwise the caller guarantees 3 valid planes either side.
+template <typename T, bool PERIODIC>
+__device__ __forceinline__ T diff6_at(const T* __restrict__ u, size_t base, long long i, long long n, size_t stride) {
+  auto at = [&](int s) {
+    long long j = i + s;
+    if (PERIODIC) { if (j < 0) j += n; if (j >= n) j -= n; }
+    return u[base + size_t(j) * stride];
+  };
+  return T(-1.0 / 60) * at(-3) + T(3.0 / 20) * at(-2) + T(-3.0 / 4) * at(-1) + T(3.0 / 4) * at(1) +
+         T(-3.0 / 20) * at(2) + T(1.0 / 60) * at(3);
+}
+
+// one thread per interior node; kernel axes (X, Y, Z), Z contiguous and the only axis with ghosts
+template <class S, typename T>
+__global__ void __launch_bounds__(lb::STEP_BLOCK)
+initialize_kernel(const T* __restrict__ rho, const T* __restrict__ u, T* __restrict__ f, unsigned nx, unsigned ny,
+                  unsigned nz, unsigned ghost, T tau, int with_fneq) {
+  const size_t tid = size_t(blockIdx.x) * lb::STEP_BLOCK + threadIdx.x;
+  const size_t n = size_t(nx) * ny * nz;
+  if (tid >= n) return;
+  const unsigned z = unsigned(tid % nz);
+  const unsigned y = unsigned((tid / nz) % ny);
+  const unsigned x = unsigned(tid / (size_t(nz) * ny));
+  const unsigned nze = nz + 2 * ghost;
+  const size_t n_ext = size_t(nx) * ny * nze;
+  const size_t e = (size_t(x) * ny + y) * nze + z + ghost;   // this node in the extended arrays
+  const T r = rho[e];
+  T uu[3] = {T(0), T(0), T(0)};
+#pragma unroll
+  for (int c = 0; c < S::D; ++c) uu[S::axis(c)] = u[c * n_ext + e];
+  T feq[S::Q];
+  lb::equilibrium<S, T>(r, uu, feq);
+  if (with_fneq) {
+    // S[a][b] = d u_a / d x_b in kernel axes (_flow.py:314)
+    T g[3][3] = {};
+#pragma unroll
+    for (int c = 0; c < S::D; ++c) {
+      const int a = S::axis(c);
+      const T* ua = u + c * n_ext;
+      if (S::D == 3) g[a][0] = diff6_at<T, true>(ua, size_t(y) * nze + z + ghost, x, nx, size_t(ny) * nze);
+      g[a][1] = diff6_at<T, true>(ua, size_t(x) * ny * nze + z + ghost, y, ny, nze);
+      g[a][2] = ghost ? diff6_at<T, false>(ua, (size_t(x) * ny + y) * nze, (long long)z + ghost, nze, 1)
+                      : diff6_at<T, true>(ua, (size_t(x) * ny + y) * nze, z, nz, 1);
+    }
+    // Pi_1 = 1.0 * tau * rho * S / cs^2 (:315); fneq_q = w_q sum_ab Pi_1[a][b] (e_qa e_qb - cs^2 delta_ab) (:316-321)
+    const T cs2 = T(LB_CS2);
+    // the reference builds delta_ab cs^2 as `torch.eye(d) * cs ** 2` (_flow.py:328-330): torch.eye defaults
+    // to float32, so that term carries cs^2 rounded to float32 whatever the lattice dtype
+    const T cs2_eye = T(float(LB_CS2));
+    T pi[3][3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+      for (int b = 0; b < 3; ++b) pi[a][b] = tau * r * g[a][b] / cs2;
+    lb::static_for<S::Q>([&](auto qc) {
+      constexpr int q = decltype(qc)::value;
+      T acc = T(0);
+#pragma unroll
+      for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int b = 0; b < 3; ++b) {
+          if (S::D == 2 && (a == 0 || b == 0)) continue;
+          const T qab = T(S::e(q, a) * S::e(q, b)) - (a == b ? cs2_eye : T(0));
+          acc += pi[a][b] * qab;
+        }
+      feq[q] -= T(S::w(q)) * acc;
+    });
+  }
+  lb::static_for<S::Q>([&](auto qc) {
+    constexpr int q = decltype(qc)::value;
+    f[q * n + tid] = feq[q];
+  });
+}
+
+template <class S, typename T>
+int initialize_typed(const lb_desc* d, const Geometry& g, const void* rho, const void* u, int ghost, int with_fneq,
+                     void* f, cudaStream_t st) {
+  const size_t n = size_t(g.n_nodes);
+  const unsigned grid = unsigned((n + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK);
+  initialize_kernel<S, T><<<grid, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(rho), static_cast<const T*>(u),
+                                                        static_cast<T*>(f), g.nx, g.ny, g.nz, unsigned(ghost),
+                                                        T(d->tau), with_fneq);
+  LB_CUDA(cudaGetLastError());
+  return LB_OK;
+}
+
+template <typename T>
+int initialize_stencil(const lb_desc* d, const Geometry& g, const void* rho, const void* u, int ghost, int with_fneq,
+                       void* f, cudaStream_t st) {
+  switch (d->stencil) {
+    case LB_D2Q9: return initialize_typed<lb::D2Q9, T>(d, g, rho, u, ghost, with_fneq, f, st);
+    case LB_D3Q19: return initialize_typed<lb::D3Q19, T>(d, g, rho, u, ghost, with_fneq, f, st);
+    case LB_D3Q27: return initialize_typed<lb::D3Q27, T>(d, g, rho, u, ghost, with_fneq, f, st);
+  }
+  return fail(LB_EINVAL, "bad stencil");
+}
+
+}  // namespace
+
+extern "C" {
+
+int lb_initialize(const lb_desc* desc, const void* rho, const void* u, int ghost, int with_fneq, void* f,
+                  void* stream) {
+  Geometry g;
+  lb_desc dd;
+  if (!desc) return fail(LB_EINVAL, "null descriptor");
+  dd = *desc;
+  dd.collision = LB_COLL_NONE;   // tau is only read when with_fneq; do not require it otherwise
+  int rc = check_desc(&dd, &g);
+  if (rc) return rc;
+  if (!rho || !u || !f) return fail(LB_EINVAL, "null pointer");
+  if (ghost != 0 && ghost < 3) return fail(LB_EINVAL, "ghost = %d: must be 0 (periodic) or >= 3 (stencil radius)", ghost);
+  if (with_fneq && !(desc->tau > 0.0)) return fail(LB_EINVAL, "tau must be > 0 for the non-equilibrium part");
+  if (with_fneq && (g.nz < 3 || g.ny < 3 || (g.d == 3 && g.nx < 3)))
+    return fail(LB_EUNSUPPORTED, "the 6th-order gradient needs at least 3 nodes per axis");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return desc->dtype == LB_F32 ? initialize_stencil<float>(desc, g, rho, u, ghost, with_fneq, f, st)
+                               : initialize_stencil<double>(desc, g, rho, u, ghost, with_fneq, f, st);
+}
+
+}  // extern "C"
+
 extern "C" {
 
 int lb_moments(const lb_desc* desc, const void* f, void* rho_out, void* u_out, void* stream) {
