@@ -198,7 +198,7 @@ def run_native(args):
         flow = SlabTaylorGreenVortex(ctx, [res, res, res * world], reynolds_number=1600, mach_number=0.1,
                                      stencil=lt.D3Q19, rank=rank, world=world)
         sim = SlabSimulation(flow, lt.BGKCollision(tau=flow.units.relaxation_parameter_lu), [],
-                             transport=os.environ.get("LB_SLAB_TRANSPORT", "p2p"))
+                             transport=os.environ.get("LB_SLAB_TRANSPORT", "p2p-packed"))
     nodes_local = res ** 3
     f_bytes = flow.f.numel() * flow.f.element_size()
 

@@ -98,7 +98,7 @@ typedef struct lb_boundary {
 /* z-slab decomposition across GPUs (BASELINE.json: slabs along the contiguous z axis; the
  * reference itself is single-device).  With lb_fields.halo set, the
  * populations that leave the local slab through z = nz-1 (ez = +1, "hi" face) or z = 0
- * (ez = -1, "lo" face) are not wrapped around locally.  Three modes:
+ * (ez = -1, "lo" face) are not wrapped around locally.  Four modes:
  *
  * LB_HALO_PACKED  the step kernel stores them into send_hi[0] / send_lo[0], packed as
  *     [zface][lines] (zface = 3 / 5 / 9 directions for D2Q9 / D3Q19 / D3Q27, ascending q;
@@ -116,14 +116,19 @@ typedef struct lb_boundary {
  * LB_HALO_DIRECT  the step kernel stores the crossing populations straight into the neighbours'
  *     population buffers (peer_up_f / peer_down_f, the buffers matching this rank's f_next [0]
  *     and f [1]) followed by the handshake.  No staging at all, but 4-byte remote stores.
+ * LB_HALO_REMOTE  as PUSH without the copy: the step kernel writes its packed z-face elements,
+ *     staged per thread block into contiguous runs, straight into the neighbours' recv_lo /
+ *     recv_hi (peer_up_recv_lo / peer_down_recv_hi) and a one-block kernel does the handshake;
+ *     received halos are consumed at load time and scattered once at the end of the call.
+ *     No send buffers, no isolated remote stores: the transport that scales to 1024^2 faces.
  *
- * Handshake (PUSH, DIRECT): the rank stores the step counter into both neighbours' wait slots
+ * Handshake (PUSH, DIRECT, REMOTE): the rank stores the step counter into both neighbours' wait slots
  * (signal_up / signal_down, peer-mapped) and spins until both of its own slots reached it, so
  * that step t+1 never reads a halo its neighbour has not delivered, nor overwrites one its
  * neighbour still reads.  A call performs n_steps + 1 handshakes with the values
  * epoch+1 .. epoch+n_steps+1; the caller advances epoch by n_steps + 1.  A wait that exceeds
  * ~10 s sets wait_slots[2] = 1 and gives up instead of hanging the GPU. */
-enum { LB_HALO_PACKED = 1, LB_HALO_PUSH = 2, LB_HALO_DIRECT = 3 };
+enum { LB_HALO_PACKED = 1, LB_HALO_PUSH = 2, LB_HALO_DIRECT = 3, LB_HALO_REMOTE = 4 };
 
 typedef struct lb_halo {
   int32_t mode;

@@ -55,7 +55,7 @@ class LbBoundary(C.Structure):
                 ("u_comp_stride", C.c_int64)]
 
 
-LB_HALO_PACKED, LB_HALO_PUSH, LB_HALO_DIRECT = 1, 2, 3
+LB_HALO_PACKED, LB_HALO_PUSH, LB_HALO_DIRECT, LB_HALO_REMOTE = 1, 2, 3, 4
 
 
 class LbHalo(C.Structure):

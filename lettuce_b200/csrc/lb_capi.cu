@@ -236,6 +236,13 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
         if (!h->wait_slots || !h->signal_up || !h->signal_down) return fail(LB_EINVAL, "LB_HALO_PUSH needs the handshake slots");
         halo_sync = !debug_nosync;
         break;
+      case LB_HALO_REMOTE:
+        for (int k = 0; k < 2; ++k)
+          if (!h->recv_lo[k] || !h->recv_hi[k] || !h->peer_up_recv_lo[k] || !h->peer_down_recv_hi[k])
+            return fail(LB_EINVAL, "LB_HALO_REMOTE needs both parities of the receive buffers, local and peer-mapped");
+        if (!h->wait_slots || !h->signal_up || !h->signal_down) return fail(LB_EINVAL, "LB_HALO_REMOTE needs the handshake slots");
+        halo_sync = !debug_nosync;
+        break;
       case LB_HALO_DIRECT:
         if (!h->peer_up_f[0] || !h->peer_down_f[0] || (n_steps > 1 && (!h->peer_up_f[1] || !h->peer_down_f[1])))
           return fail(LB_EINVAL, "LB_HALO_DIRECT needs the neighbours' population buffers");
@@ -249,6 +256,15 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
       p.halo_qs = g.n_nodes; p.halo_ls = g.nz; p.halo_hi_off = 0; p.halo_lo_off = g.nz - 1; p.halo_compact = 0;
     } else {
       p.halo_qs = (long long)g.nx * g.ny; p.halo_ls = 1; p.halo_hi_off = 0; p.halo_lo_off = 0; p.halo_compact = 1;
+      // packed layout: stage the z-face elements per block (lb_kernels.cuh).  A block of STEP_BLOCK threads
+      // touches at most STEP_BLOCK / nzv + 2 lines; slots per (face, population) = next power of two.
+      static const bool no_stage = getenv("LB_HALO_NO_STAGE") != nullptr;   // A/B timing only
+      const unsigned lines_per_block = lb::STEP_BLOCK / p.nzv + 2;
+      if (c.vec > 1 && lines_per_block <= unsigned(lb::HALO_STAGE_LINES) && !no_stage) {
+        int sh = 1;
+        while ((1u << sh) < lines_per_block) ++sh;
+        p.halo_stage_shift = sh;
+      }
     }
     if (halo_sync) {  // everybody has entered the call: the neighbours' buffers are ours to write
       rc = lb::launch_halo_push(nullptr, nullptr, nullptr, nullptr, 0, h->signal_up, h->signal_down,
@@ -285,8 +301,12 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
         p.halo_hi = static_cast<T*>(h->peer_up_f[k]); p.halo_lo = static_cast<T*>(h->peer_down_f[k]);
       } else {
         const int ks = h->mode == LB_HALO_PACKED ? 0 : k;
-        p.halo_hi = static_cast<T*>(h->send_hi[ks]); p.halo_lo = static_cast<T*>(h->send_lo[ks]);
-        if (h->mode == LB_HALO_PUSH && s > 0) {   // consume what the previous step's push delivered
+        if (h->mode == LB_HALO_REMOTE) {   // straight into the neighbours' receive buffers
+          p.halo_hi = static_cast<T*>(h->peer_up_recv_lo[k]); p.halo_lo = static_cast<T*>(h->peer_down_recv_hi[k]);
+        } else {
+          p.halo_hi = static_cast<T*>(h->send_hi[ks]); p.halo_lo = static_cast<T*>(h->send_lo[ks]);
+        }
+        if ((h->mode == LB_HALO_PUSH || h->mode == LB_HALO_REMOTE) && s > 0) {   // consume what the previous step delivered
           p.halo_in_lo = static_cast<const T*>(h->recv_lo[k ^ 1]);
           p.halo_in_hi = static_cast<const T*>(h->recv_hi[k ^ 1]);
         } else if (h->mode == LB_HALO_PACKED) {   // optional: a halo received but not yet unpacked
@@ -320,7 +340,7 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
     }
     T* t = a; a = b; b = t;
   }
-  if (h && h->mode == LB_HALO_PUSH && n_steps > 0) {
+  if (h && (h->mode == LB_HALO_PUSH || h->mode == LB_HALO_REMOTE) && n_steps > 0) {
     // make the population buffer canonical again: scatter the last received halo into it
     const int k = (n_steps - 1) & 1;
     rc = lb_unpack_halo(d, a, h->recv_lo[k], h->recv_hi[k], st);

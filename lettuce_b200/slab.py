@@ -8,10 +8,15 @@ Transports behind one class:
           CUDA-IPC peer pointers over NVLink (128-bit stores) and does the neighbour handshake;
           the next step kernel consumes the received halo at load time.  No host involvement
           between steps: simulation(n) is one C call.
-  'p2p'   (default on CUDA, LB_HALO_DIRECT) the step kernel itself stores the crossing populations
+  'p2p'   (LB_HALO_DIRECT) the step kernel itself stores the crossing populations
           straight into the neighbours' boundary planes through CUDA-IPC peer pointers over NVLink:
           compute and exchange in ONE kernel, no pack / copy / unpack; a one-block handshake kernel
-          follows each step.  Fastest of the three (measured).
+          follows each step.  Cheapest on small faces, but isolated 4-byte remote stores into planes
+          that the receiver is writing too: up to 20 % of a step on 1024^2 faces.
+  'p2p-packed'  (default on CUDA, LB_HALO_REMOTE) the step kernel stages its packed z-face elements per thread block
+          and writes them as contiguous runs straight into the neighbours' receive buffers (peer
+          pointers); a one-block handshake kernel follows each step; received halos are consumed at
+          load time.  No isolated remote stores: the transport for large faces (1024^2).
   'nccl'  (LB_HALO_PACKED) packed send buffers, torch.distributed send/recv, lb_unpack_halo:
           the baseline design north_star names.
   'host'  same exchange logic over any torch.distributed backend with an injected local stepper;
@@ -148,8 +153,8 @@ class SlabSimulation(Simulation):
         self.down = (self.rank - 1) % self.world
         self.local_stepper = local_stepper
         if transport is None:
-            transport = 'host' if local_stepper is not None else 'p2p'
-        if transport not in ('p2p-push', 'p2p', 'nccl', 'host'):
+            transport = 'host' if local_stepper is not None else 'p2p-packed'
+        if transport not in ('p2p-push', 'p2p-packed', 'p2p', 'nccl', 'host'):
             raise ValueError(transport)
         self.transport = transport
         self._epoch = 0
@@ -171,7 +176,7 @@ class SlabSimulation(Simulation):
         for n in flow.resolution[:-1]:
             self.lines *= n
         if self.world > 1:
-            if transport == 'p2p-push':
+            if transport in ('p2p-push', 'p2p-packed'):
                 self._setup_push()
             elif transport == 'p2p':
                 self._setup_direct()
@@ -236,9 +241,9 @@ class SlabSimulation(Simulation):
         flow = self.flow
         h = nat.LbHalo()
         h.epoch = epoch
-        if self.transport == 'p2p-push':
+        if self.transport in ('p2p-push', 'p2p-packed'):
             up, down = self._peer[self.up], self._peer[self.down]
-            h.mode = nat.LB_HALO_PUSH
+            h.mode = nat.LB_HALO_PUSH if self.transport == 'p2p-push' else nat.LB_HALO_REMOTE
             for k in range(2):
                 h.send_hi[k], h.send_lo[k] = self._send[k].data_ptr(), self._send[2 + k].data_ptr()
                 h.recv_lo[k], h.recv_hi[k] = self._recv[k].data_ptr(), self._recv[2 + k].data_ptr()
@@ -278,7 +283,7 @@ class SlabSimulation(Simulation):
             return
         if self.world == 1:
             return Simulation._advance(self, n, obs_out, u_out)
-        if self.transport in ('p2p-push', 'p2p'):
+        if self.transport in ('p2p-push', 'p2p-packed', 'p2p'):
             Simulation._advance(self, n, obs_out, u_out)
             self._epoch += n + 1
             return
@@ -343,13 +348,13 @@ class SlabSimulation(Simulation):
             self.flow.i += num_steps
             return num_steps * self.flow.f[0].numel() * self.world / 1e6 / (timer() - beg)
         mlups_local = Simulation.__call__(self, num_steps)
-        if self.world > 1 and self.transport in ('p2p-push', 'p2p'):
+        if self.world > 1 and self.transport in ('p2p-push', 'p2p-packed', 'p2p'):
             if int(self._flags[2].item()) != 0:
                 raise RuntimeError("halo handshake timed out: a neighbour rank did not reach the same step")
         return mlups_local * self.world
 
     def close(self):
-        if self.world > 1 and self.transport in ('p2p-push', 'p2p'):
+        if self.world > 1 and self.transport in ('p2p-push', 'p2p-packed', 'p2p'):
             torch.cuda.synchronize(self.context.device)
             dist.barrier(group=self.group)
             for r, ptrs in self._peer.items():

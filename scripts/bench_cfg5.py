@@ -24,7 +24,7 @@ ap.add_argument("--nxy", type=int, default=1024)
 ap.add_argument("--nz", type=int, default=None, help="global (strong) / per-GPU (weak) extent along z")
 ap.add_argument("--steps", type=int, default=50)
 ap.add_argument("--warmup", type=int, default=10)
-ap.add_argument("--transport", default="p2p")
+ap.add_argument("--transport", default="p2p-packed")
 a = ap.parse_args()
 
 world, rank, local = int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0))

@@ -12,6 +12,8 @@ import lettuce_b200 as lt  # noqa: E402
 nat = lt.native
 L = nat.lib()
 res = [int(os.environ.get("RES", 256))] * 3
+if os.environ.get("RES3"):
+    res = [int(v) for v in os.environ["RES3"].split("x")]
 steps = int(os.environ.get("STEPS", 100))
 ctx = lt.Context(device="cuda", dtype=torch.float32, use_native=True)
 flow = lt.TaylorGreenVortex(ctx, resolution=res, reynolds_number=1600, mach_number=0.1, stencil=lt.D3Q19)

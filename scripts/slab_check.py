@@ -43,7 +43,7 @@ def main():
             rep = lt.ObservableReporter(lt.IncompressibleKineticEnergy(g), interval=7, out=None)
             lt.Simulation(g, collision(g), [rep])(a.steps)
             want, e_want = g.f, [r[2] for r in rep.out]
-        for transport in ("p2p", "p2p-push", "nccl"):
+        for transport in ("p2p", "p2p-packed", "p2p-push", "nccl"):
             flow = SlabTaylorGreenVortex(ctx, res, 400, 0.1, stencil, rank=rank, world=world)
             rep = lt.ObservableReporter(lt.IncompressibleKineticEnergy(flow), interval=7, out=None)
             sim = SlabSimulation(flow, collision(flow), [rep], transport=transport)

@@ -106,6 +106,8 @@ CASES = [
     ("D3Q19", "f32", [6, 5, 32], 2), ("D3Q19", "f32", [4, 4, 512], 4), ("D3Q19", "f64", [3, 5, 12], 4),
     ("D3Q19", "f32", [3, 4, 15], 3), ("D3Q27", "f32", [4, 3, 24], 2), ("D3Q27", "f64", [3, 3, 9], 3),
     ("D2Q9", "f64", [7, 16], 4), ("D2Q9", "f32", [5, 6], 2), ("D3Q19", "f32", [4, 4, 2], 2),
+    # staged packed-halo stores with thread blocks that cut lines: 48 and 12 vectors per line
+    ("D3Q19", "f32", [3, 5, 384], 2), ("D3Q27", "f32", [5, 7, 96], 2), ("D2Q9", "f64", [40, 112], 2),
 ]
 
 
