@@ -225,7 +225,10 @@ def run_native(args):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_total = float(ms.item())
-    launches = args.steps * T
+    launches = args.steps * T                      # step kernels per rank in the timed region
+    # z-slabs add, per simulation(T) call and rank: one handshake kernel up front, one after every
+    # step, and the final scatter of the last received halo (lb_capi.cu step_typed)
+    launches_all = launches if world == 1 else args.steps * (2 * T + 2)
     mlups = nodes_local * world * launches / 1e6 / (ms_total / 1e3)
     assert bool(torch.isfinite(flow.f).all()), "populations became non-finite"
 
@@ -274,14 +277,16 @@ def run_native(args):
                      "traffic": profiled_traffic(), "peak_source": peak_src,
                      "bytes_per_launch": bytes_per_launch, "avg_launch_us": avg_launch_s * 1e6,
                      "kernel": "lb::step_kernel<D3Q19,float,V=4,BGK>"},
-        "clocks": clocks, "gpu_launches": launches,
+        "clocks": clocks, "gpu_launches": launches_all,
     }
     if e2e is not None:
         line["e2e"] = e2e
     if world == 1 and not args.no_cpu_baseline:
-        v, dt, cores = cpu_oracle_mlups(128, 6)
+        n_cpu = 12
+        v, dt, cores = cpu_oracle_mlups(res, n_cpu)
         line["cpu_baseline"] = {"value": v, "unit": "MLUPS", "cores": cores, "kind": "port",
-                                "sample": f"6 time steps of the same flow at 128^3 ({dt:.1f} s), torch-CPU restatement of the reference path"}
+                                "sample": f"{n_cpu} time steps of the same {res}^3 lattice ({dt:.1f} s of CPU work), "
+                                          "torch-CPU restatement of the reference path, all host threads"}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -241,7 +241,10 @@ class Simulation:
 
         torch.cuda.synchronize(self.context.device)
         end = timer()
-        return num_steps * flow.rho().numel() / 1e6 / (end - beg)
+        n_nodes = 1
+        for n in flow.resolution:     # == flow.rho().numel() (_simulation.py:207) without a moments pass
+            n_nodes *= int(n)
+        return num_steps * n_nodes / 1e6 / (end - beg)
 
     def _finalize_obs(self, obs: torch.Tensor) -> torch.Tensor:
         """device [n, LB_OBS_COUNT] -> host; the slab driver all-reduces across ranks here"""
