@@ -43,13 +43,14 @@ extern "C" {
 #define LB_API
 #endif
 
-#define LB_ABI_VERSION 3
+#define LB_ABI_VERSION 4
 #define LB_MAX_BOUNDARIES 8
 
 enum { LB_D2Q9 = 0, LB_D3Q19 = 1, LB_D3Q27 = 2 };                     /* lb_desc.stencil   */
 enum { LB_F32 = 0, LB_F64 = 1 };                                      /* lb_desc.dtype     */
 enum { LB_COLL_NONE = 0, LB_COLL_BGK = 1, LB_COLL_TRT = 2, LB_COLL_KBC = 3 }; /* .collision */
-enum { LB_BND_BOUNCE_BACK = 1, LB_BND_EQUILIBRIUM = 2 };              /* lb_boundary.kind  */
+enum { LB_BND_BOUNCE_BACK = 1, LB_BND_EQUILIBRIUM = 2,                 /* lb_boundary.kind  */
+       LB_BND_ABB_OUTLET = 3, LB_BND_EQ_OUTLET_P = 4 };
 
 enum {
   LB_OK = 0,
@@ -84,15 +85,28 @@ typedef struct lb_desc {
  *   rho[x*rho_stride[0] + y*rho_stride[1] + z*rho_stride[2]]
  *   u  [c*u_comp_stride + x*u_stride[0] + y*u_stride[1] + z*u_stride[2]]
  * with strides in ELEMENTS; a stride of 0 broadcasts that axis
- * (equilibrium_boundary_pu.py:21-32; tests/boundary/test_equilibrium_bc_pu.py:125-148). */
+ * (equilibrium_boundary_pu.py:21-32; tests/boundary/test_equilibrium_bc_pu.py:125-148).
+ *
+ * The two outlet kinds act on a whole boundary PLANE of the domain (`direction`), in place and
+ * whatever no_collision_mask says there, exactly like the reference objects:
+ *   LB_BND_ABB_OUTLET   AntiBounceBackOutlet (anti_bounce_back_outlet.py:71-86): for every q with
+ *       e_q . direction = 1:  f_opp(q) = -f_q + w_q rho (2 + (e_q.u_w)^2 / cs^4 - |u_w|^2 / cs^2),
+ *       u_w = u + (u - u_neighbour) / 2, with rho, u of the plane node and u of the node next to it.
+ *   LB_BND_EQ_OUTLET_P  EquilibriumOutletP (equilibrium_outlet_p.py:63-71): f = feq(value, u_neighbour).
+ * Their streaming masks (which populations of the plane keep their local value) come through
+ * lb_fields.streaming_bits like any other no_streaming_mask.  The neighbour's velocity is taken
+ * from its state at the start of the step, corrected for a bounce-back or equilibrium boundary of
+ * LOWER index on that node (collisions conserve rho and u); a lower-index OUTLET plane crossing the
+ * neighbour plane is not supported (the host mirror refuses it). */
 typedef struct lb_boundary {
   int32_t kind;
-  int32_t _pad;
+  int32_t direction;   /* outlet kinds: +-(lattice axis + 1), e.g. +1 = the x = nx-1 side, -2 = the y = 0 side */
   const void* rho;
   const void* u;
   int64_t rho_stride[3];
   int64_t u_stride[3];
   int64_t u_comp_stride;
+  double value;        /* LB_BND_EQ_OUTLET_P: rho_outlet (lattice units) */
 } lb_boundary;
 
 /* z-slab decomposition across GPUs (BASELINE.json: slabs along the contiguous z axis; the

@@ -8,7 +8,7 @@ from typing import List, Optional, Union
 import numpy as np
 import torch
 
-from ._boundary import BounceBackBoundary, EquilibriumBoundaryPU
+from ._boundary import AntiBounceBackOutlet, BounceBackBoundary, EquilibriumBoundaryPU
 from ._equilibrium import QuadraticEquilibrium
 from ._flow import Flow
 from ._stencil import D1Q3, D2Q9, D3Q19
@@ -115,12 +115,9 @@ def TaylorGreenVortex2D(context, resolution, reynolds_number, mach_number, stenc
 
 
 class Obstacle(ExtFlow):
-    """Flow around an obstacle given by a boolean mask (obstacle.py:16-125).
-
-    The reference's stock boundary list uses AntiBounceBackOutlet, which is a "next" row of the
-    scope table and not part of this engine yet.  `boundaries` therefore
-    returns the all-local reading BASELINE config 3 names: equilibrium inlet on x = 0,
-    equilibrium outlet on x = nx-1, bounce-back on the mask."""
+    """Flow around an obstacle given by a boolean mask (obstacle.py:16-125), with the reference's
+    stock boundary list: equilibrium inlet on x = 0, AntiBounceBackOutlet on the +x side,
+    bounce-back on the mask (obstacle.py:107-122)."""
 
     def __init__(self, context, resolution, reynolds_number, mach_number, domain_length_x,
                  char_length=1, char_velocity=1, stencil=None, equilibrium=None):
@@ -168,8 +165,7 @@ class Obstacle(ExtFlow):
         x = self.grid[0]
         u_in = self.units.characteristic_velocity_pu * self._unit_vector()
         return [EquilibriumBoundaryPU(context=self.context, mask=torch.abs(x) < 1e-6, velocity=u_in),
-                EquilibriumBoundaryPU(context=self.context, mask=torch.abs(x - x.max()) < 1e-6,
-                                      velocity=u_in),
+                AntiBounceBackOutlet(self._unit_vector().tolist(), self),
                 BounceBackBoundary(self.mask)]
 
     def _unit_vector(self, i=0):

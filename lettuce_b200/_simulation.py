@@ -78,6 +78,7 @@ class Simulation:
         for b in self.boundaries[1:]:
             if not (b.native_available() and hasattr(b, 'native_descriptor')):
                 raise NotImplementedError(f"boundary '{type(b).__name__}' has no native kernel")
+        self._check_outlets()
         if len(self.boundaries) - 1 > nat.LB_MAX_BOUNDARIES:
             raise NotImplementedError(f"at most {nat.LB_MAX_BOUNDARIES} boundary objects are supported")
 
@@ -86,6 +87,24 @@ class Simulation:
         self._obs_scratch = None
         self._keepalive = []
         self._collide_and_stream = self._native_seam
+
+    def _check_outlets(self):
+        """The kernel takes the velocity next to an outlet plane from that node's state at the start
+        of the step, corrected for a lower-index bounce-back / equilibrium boundary on it
+        (include/lettuce_b200.h).  What it cannot reproduce is an outlet of LOWER index whose plane
+        crosses the neighbour plane of another outlet: refuse that combination."""
+        from ._boundary import AntiBounceBackOutlet
+        outlets = [(i, b) for i, b in enumerate(self.boundaries[1:], start=1) if isinstance(b, AntiBounceBackOutlet)]
+        for i, b in outlets:
+            if min(self.flow.resolution) < 2:
+                raise ValueError("outlet boundaries need at least 2 nodes along every axis")
+            axis = next(a for a, v in enumerate(b.direction) if v != 0)
+            for j, other in outlets:
+                if j < i and next(a for a, v in enumerate(other.direction) if v != 0) != axis:
+                    raise NotImplementedError(
+                        f"outlet boundary {i} ({type(b).__name__}, direction {b.direction}): the lower-index "
+                        f"outlet {j} (direction {other.direction}) crosses its neighbour plane; this ordering "
+                        f"is not supported by the native kernel")
 
     # ------------------------------------------------------------------------------------------
     def step(self, num_steps: int):
@@ -130,6 +149,8 @@ class Simulation:
         for k, b in enumerate(self.boundaries[1:]):
             d = b.native_descriptor(self.flow)
             arr[k].kind = d['kind']
+            arr[k].direction = int(d.get('direction', 0))
+            arr[k].value = float(d.get('value', 0.0))
             if d['kind'] == nat.LB_BND_EQUILIBRIUM:
                 rho, u = d['rho'], d['u']
                 if u.shape[0] != self.flow.stencil.d:

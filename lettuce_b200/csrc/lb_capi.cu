@@ -175,8 +175,19 @@ int fill_boundaries(const lb_desc* d, const Geometry& g, const lb_boundary* b, i
     o.rho = static_cast<const T*>(b[i].rho);
     o.u = static_cast<const T*>(b[i].u);
     o.ucs = b[i].u_comp_stride;
-    if (o.kind != LB_BND_BOUNCE_BACK && o.kind != LB_BND_EQUILIBRIUM)
+    if (o.kind < LB_BND_BOUNCE_BACK || o.kind > LB_BND_EQ_OUTLET_P)
       return fail(LB_EINVAL, "boundary %d: unknown kind %d", i, o.kind);
+    o.axis = 0; o.sign = 0; o.value = T(b[i].value);
+    if (o.kind == LB_BND_ABB_OUTLET || o.kind == LB_BND_EQ_OUTLET_P) {
+      const int dir = b[i].direction, la = (dir < 0 ? -dir : dir) - 1;   // lattice axis
+      if (dir == 0 || la >= g.d) return fail(LB_EINVAL, "boundary %d: outlet direction %d on a %d-D lattice", i, dir, g.d);
+      o.axis = (g.d == 2) ? la + 1 : la;   // lattice axis -> kernel axis (2-D runs as X = 1)
+      o.sign = dir > 0 ? 1 : -1;
+      const unsigned n = o.axis == 0 ? g.nx : (o.axis == 1 ? g.ny : g.nz);
+      if (n < 2) return fail(LB_EINVAL, "boundary %d: the outlet needs at least 2 planes along its axis", i);
+      if (!p->ncm) return fail(LB_EINVAL, "boundary %d: outlet boundaries need no_collision_mask", i);
+      p->has_outlet = 1;
+    }
     if (o.kind == LB_BND_EQUILIBRIUM && (!o.rho || !o.u))
       return fail(LB_EINVAL, "boundary %d: equilibrium boundary needs rho and u", i);
     // lattice axes -> kernel axes (2-D: X unused)
@@ -207,7 +218,7 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   c.mode = p.sbits ? lb::MODE_NCM_SBITS : (p.ncm ? lb::MODE_NCM : lb::MODE_PLAIN);
   c.stream = do_stream;
   c.halo = fl->halo != nullptr;
-  c.vec = do_stream ? vector_width<T>(d, g, fl->f, fl->f_next, p.sbits != nullptr) : 1;
+  c.vec = do_stream ? vector_width<T>(d, g, fl->f, fl->f_next, p.sbits != nullptr || p.has_outlet) : 1;
   p.nzv = g.nz / c.vec;
   p.n_threads = g.nx * g.ny * p.nzv;
 

@@ -36,7 +36,7 @@ constexpr int STEP_BLOCK = 128;
 constexpr int N_OBS_PART = 3;  // energy, max|u|^2, mass
 constexpr int HALO_STAGE_LINES = 64;  // most lines of which a block can stage the halo elements
 
-enum { BND_BOUNCE_BACK = 1, BND_EQUILIBRIUM = 2 };
+enum { BND_BOUNCE_BACK = 1, BND_EQUILIBRIUM = 2, BND_ABB_OUTLET = 3, BND_EQ_OUTLET_P = 4 };
 enum { MODE_PLAIN = 0, MODE_NCM = 1, MODE_NCM_SBITS = 2 };
 
 // Scratch of the fused reductions (lb_obs_scratch_bytes): ticket counters and per-block / per-group
@@ -75,6 +75,9 @@ struct BoundaryDev {
   long long rs[3];  // strides (elements) along kernel axes X, Y, Z
   long long us[3];
   long long ucs;    // stride between velocity components (lattice order)
+  int axis;         // outlet kinds: kernel axis (0 X, 1 Y, 2 Z) normal to the plane ...
+  int sign;         // ... and the side: +1 = the last plane of that axis, -1 = the first
+  T value;          // BND_EQ_OUTLET_P: rho_outlet
 };
 
 template <typename T>
@@ -88,6 +91,7 @@ struct StepParams {
   unsigned n_threads;          // nx * ny * nzv
   CollisionParams<T> cp;
   int n_bnd;
+  int has_outlet;              // some boundary is an outlet plane: boundaries are applied in index order
   BoundaryDev<T> bnd[MAX_BND];
   ObsScratch obs;              // scratch of the fused reductions
   double* obs_out;             // [LB_OBS_COUNT]
@@ -231,9 +235,71 @@ __device__ __forceinline__ void reduce_observables(double e, double m2, double m
   }
 }
 
+// equilibrium_boundary_pu.py:27-32: prescribed (rho, u) of boundary `bd` at node (x, y, z), lattice units
+template <class S, typename T>
+__device__ __forceinline__ void boundary_values(const BoundaryDev<T>& bd, unsigned x, unsigned y, unsigned z, T& rb,
+                                                T (&ub)[3]) {
+  const long long zz = z;
+  rb = bd.rho[x * bd.rs[0] + y * bd.rs[1] + zz * bd.rs[2]];
+  ub[0] = ub[1] = ub[2] = T(0);
+  const long long off = x * bd.us[0] + y * bd.us[1] + zz * bd.us[2];
+#pragma unroll
+  for (int c = 0; c < S::D; ++c) ub[S::axis(c)] = bd.u[c * bd.ucs + off];
+}
+
+// Velocity the reference's outlet boundary `i` (1-based) sees on the node next to its plane, i.e. of
+// that node's state after the collision and the boundaries of lower index.  Collisions conserve rho
+// and u, so it is taken from the node's incoming populations and corrected for a bounce-back
+// (u -> -u) or equilibrium boundary (u -> prescribed u) of lower index on that node.
+template <class S, typename T>
+__device__ __forceinline__ void outlet_neighbour_velocity(const StepParams<T>& p, const T* __restrict__ f_in, int i,
+                                                          unsigned xn, unsigned yn, unsigned zn, T (&un)[3]) {
+  const size_t N = p.n_nodes;
+  const unsigned nb = (xn * p.ny + yn) * p.nz + zn;
+  T h[S::Q], rn;
+  static_for<S::Q>([&](auto qc) { h[decltype(qc)::value] = f_in[decltype(qc)::value * N + nb]; });
+  moments<S, T>(h, rn, un);
+  const int mn = p.ncm[nb];
+  if (mn > 0 && mn < i) {
+    const BoundaryDev<T>& bn = p.bnd[mn - 1];
+    if (bn.kind == BND_BOUNCE_BACK) {
+      un[0] = -un[0]; un[1] = -un[1]; un[2] = -un[2];
+    } else if (bn.kind == BND_EQUILIBRIUM) {
+      T rb;
+      boundary_values<S, T>(bn, xn, yn, zn, rb, un);
+    }
+  }
+}
+
+// The outlet boundaries: in place on their plane (anti_bounce_back_outlet.py:71-86,
+// equilibrium_outlet_p.py:63-71)
+template <class S, typename T>
+__device__ __forceinline__ void outlet_node(T (&g)[S::Q], const BoundaryDev<T>& bd, const T (&un)[3]) {
+  if (bd.kind == BND_EQ_OUTLET_P) {
+    equilibrium<S, T>(bd.value, un, g);
+    return;
+  }
+  T rho, u[3];
+  moments<S, T>(g, rho, u);
+  const T uw[3] = {u[0] + T(0.5) * (u[0] - un[0]), u[1] + T(0.5) * (u[1] - un[1]), u[2] + T(0.5) * (u[2] - un[2])};
+  const T uw2 = fma_(uw[0], uw[0], fma_(uw[1], uw[1], uw[2] * uw[2]));
+  const T inv_cs2 = T(1.0 / LB_CS2), inv_cs4 = T(1.0 / (LB_CS2 * LB_CS2));
+  static_for<S::Q>([&](auto qc) {
+    constexpr int q = decltype(qc)::value;
+    const int ed = (bd.axis == 0 ? S::e(q, 0) : (bd.axis == 1 ? S::e(q, 1) : S::e(q, 2))) * bd.sign;
+    if (ed == 1) {   // leaves through the plane: its opposite is rebuilt
+      const T eu = T(S::e(q, 0)) * uw[0] + T(S::e(q, 1)) * uw[1] + T(S::e(q, 2)) * uw[2];
+      g[S::opp(q)] = T(S::w(q)) * rho * (T(2) + eu * eu * inv_cs4 - uw2 * inv_cs2) - g[q];
+    }
+  });
+}
+
 // One node: moments -> (fused observables) -> collision where ncm == 0, boundary i where ncm == i
-template <class S, typename T, int COLL, int MODE, bool OBS>
-__device__ __forceinline__ void node_update(T (&g)[S::Q], unsigned m, const StepParams<T>& p, T* u_out, unsigned x,
+// OUTLETS: compile the in-order boundary loop that outlet planes need (one-node-per-thread kernels
+// only: outlets always come with a streaming mask, which runs one node per thread)
+template <class S, typename T, int COLL, int MODE, bool OBS, bool OUTLETS>
+__device__ __forceinline__ void node_update(T (&g)[S::Q], unsigned m, const StepParams<T>& p,
+                                            const T* __restrict__ f_in, T* u_out, unsigned x,
                                             unsigned y, unsigned z, unsigned node, bool active, T& acc_e,
                                             T& acc_m2, T& acc_mass) {
   T a[N_SLOTS], b[N_SLOTS];
@@ -255,19 +321,41 @@ __device__ __forceinline__ void node_update(T (&g)[S::Q], unsigned m, const Step
   if (m == 0) {
     collide_node<S, T, COLL, T>(g, a, b, rho, u, p.cp);
   } else if constexpr (MODE != MODE_PLAIN) {
-    if (m <= unsigned(p.n_bnd)) {
-      const BoundaryDev<T>& bd = p.bnd[m - 1];
-      if (bd.kind == BND_BOUNCE_BACK) {
-        bounce_back_node<S, T>(g);
-      } else if (bd.kind == BND_EQUILIBRIUM) {
-        // equilibrium_boundary_pu.py:27-32 (rho, u already in lattice units)
-        const long long zz = z;
-        const T rb = bd.rho[x * bd.rs[0] + y * bd.rs[1] + zz * bd.rs[2]];
-        T ub[3] = {T(0), T(0), T(0)};
-        const long long off = x * bd.us[0] + y * bd.us[1] + zz * bd.us[2];
-#pragma unroll
-        for (int c = 0; c < S::D; ++c) ub[S::axis(c)] = bd.u[c * bd.ucs + off];
-        equilibrium<S, T>(rb, ub, g);
+    if (!OUTLETS || !p.has_outlet) {
+      if (m <= unsigned(p.n_bnd)) {
+        const BoundaryDev<T>& bd = p.bnd[m - 1];
+        if (bd.kind == BND_BOUNCE_BACK) {
+          bounce_back_node<S, T>(g);
+        } else if (bd.kind == BND_EQUILIBRIUM) {
+          T rb, ub[3];
+          boundary_values<S, T>(bd, x, y, z, rb, ub);
+          equilibrium<S, T>(rb, ub, g);
+        }
+      }
+    } else {
+      // with outlet planes the boundaries act one after the other, in index order (_simulation.py:186-188):
+      // a mask boundary where ncm == i, an outlet on every node of its plane (a plane node always has ncm != 0)
+      for (int i = 1; i <= p.n_bnd; ++i) {
+        const BoundaryDev<T>& bd = p.bnd[i - 1];
+        if (bd.kind == BND_ABB_OUTLET || bd.kind == BND_EQ_OUTLET_P) {
+          const unsigned c = bd.axis == 0 ? x : (bd.axis == 1 ? y : z);
+          const unsigned n = bd.axis == 0 ? p.nx : (bd.axis == 1 ? p.ny : p.nz);
+          if (c == (bd.sign > 0 ? n - 1u : 0u)) {
+            const unsigned cn = bd.sign > 0 ? n - 2u : 1u;
+            T un[3];
+            outlet_neighbour_velocity<S, T>(p, f_in, i, bd.axis == 0 ? cn : x, bd.axis == 1 ? cn : y,
+                                            bd.axis == 2 ? cn : z, un);
+            outlet_node<S, T>(g, bd, un);
+          }
+        } else if (m == unsigned(i)) {
+          if (bd.kind == BND_BOUNCE_BACK) {
+            bounce_back_node<S, T>(g);
+          } else if (bd.kind == BND_EQUILIBRIUM) {
+            T rb, ub[3];
+            boundary_values<S, T>(bd, x, y, z, rb, ub);
+            equilibrium<S, T>(rb, ub, g);
+          }
+        }
       }
     }
   }
@@ -395,7 +483,7 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
         for (int k = 2 * kk; k < 2 * kk + 2; ++k) {
           T g[Q];
           static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
-          node_update<S, T, COLL, MODE, OBS>(g, (m2 >> (8 * (k - 2 * kk))) & 0xffu, p, u_out, x, y, z0 + k, node + k, active,
+          node_update<S, T, COLL, MODE, OBS, false>(g, (m2 >> (8 * (k - 2 * kk))) & 0xffu, p, f_in, u_out, x, y, z0 + k, node + k, active,
                                              acc_e, acc_m2, acc_mass);
           static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
         }
@@ -407,7 +495,7 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
       T g[Q];
       static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
       const unsigned m = (MODE == MODE_PLAIN) ? 0u : ((mword >> (8 * k)) & 0xffu);
-      node_update<S, T, COLL, MODE, OBS>(g, m, p, u_out, x, y, z0 + k, node + k, active, acc_e, acc_m2, acc_mass);
+      node_update<S, T, COLL, MODE, OBS, V == 1>(g, m, p, f_in, u_out, x, y, z0 + k, node + k, active, acc_e, acc_m2, acc_mass);
       static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
     }
   }

@@ -65,6 +65,24 @@ class TaggedBounceBack(lt.BounceBackBoundary):
         return f"boundary_{self._tag:03d}"
 
 
+class TaggedABBOutlet(lt.AntiBounceBackOutlet):
+    def __init__(self, direction, flow, tag=0):
+        super().__init__(direction, flow)
+        self._tag = tag
+
+    def __str__(self):
+        return f"boundary_{self._tag:03d}"
+
+
+class TaggedEqOutletP(lt.EquilibriumOutletP):
+    def __init__(self, direction, flow, rho_outlet=1.0, tag=0):
+        super().__init__(direction, flow, rho_outlet=rho_outlet)
+        self._tag = tag
+
+    def __str__(self):
+        return f"boundary_{self._tag:03d}"
+
+
 def make_collision(meta):
     c = meta["collision"]
     if c == "none":
@@ -98,7 +116,15 @@ def simulation_from_case(case, reporters=(), device="cuda"):
                 flow.boundaries.append(LUEquilibriumBoundary(
                     ctx, mask, torch.from_numpy(case[f"b{i}_rho"]), torch.from_numpy(case[f"b{i}_u"]),
                     nsm=this_nsm, tag=i))
+            elif b["kind"] in ("abb_outlet", "eq_outlet_p"):
+                # the real classes: their own masks must reproduce the reference's (checked below)
+                cls = TaggedABBOutlet if b["kind"] == "abb_outlet" else TaggedEqOutletP
+                kw = dict(rho_outlet=b["rho_outlet"]) if b["kind"] == "eq_outlet_p" else {}
+                flow.boundaries.append(cls(b["direction"], flow, tag=i, **kw))
             else:
+                if f"b{i}_mask" in case:          # outlet files store the bounce-back mask itself
+                    mask = torch.from_numpy(case[f"b{i}_mask"])
+                    this_nsm = None
                 flow.boundaries.append(TaggedBounceBack(mask, nsm=this_nsm, tag=i))
     sim = lt.Simulation(flow, make_collision(meta), list(reporters))
     return sim

@@ -306,8 +306,8 @@ def test_full_size_bgk_conservation_d3q19_256():
 
 
 def test_full_size_obstacle_2048x1024():
-    """config 3: D2Q9 BGK 2048x1024 with bounce-back cylinder + equilibrium inlet/outlet:
-    solid interior stays at rest state, inlet/outlet columns hold their equilibrium."""
+    """config 3 size with the stock lt.Obstacle boundary list (equilibrium inlet, anti-bounce-back
+    outlet, bounce-back cylinder): stays finite, flows in +x, expected mask indices."""
     gu, lt = _gpu()
     ctx = lt.Context(device="cuda", dtype=torch.float32, use_native=True)
     flow = lt.Obstacle(ctx, [2048, 1024], reynolds_number=300, mach_number=0.01, domain_length_x=1)
@@ -335,3 +335,57 @@ def test_kbc_d3q27_energy_reporter_interval():
     assert sorted(outs[1]) == [0, 10, 20, 30]
     for i in outs[1]:
         assert outs[1][i] == pytest.approx(outs[0][i], rel=1e-6)
+
+
+# ------------------------------------------------------------------------------------------
+# (4) outlet boundaries
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", [n for n in golden_names() if n.startswith("outlet_")])
+def test_outlet_masks_match_reference(name):
+    """the host mirror's AntiBounceBackOutlet / EquilibriumOutletP build the masks the reference built"""
+    gu, lt = _gpu()
+    case = load_case(name)
+    sim = gu.simulation_from_case(case)
+    assert np.array_equal(sim.no_collision_mask.cpu().numpy(), case["ncm"])
+    assert np.array_equal(sim.no_streaming_mask.cpu().numpy().astype(bool), case["nsm"].astype(bool))
+
+
+def test_stock_obstacle_vs_oracle():
+    """lt.Obstacle with its stock boundaries (obstacle.py:107-122) on the GPU against the oracle"""
+    from oracle import lbm_oracle as orc
+    gu, lt = _gpu()
+    res = [40, 24]
+    ctx = lt.Context(device="cuda", dtype=torch.float64, use_native=True)
+    flow = lt.Obstacle(ctx, res, reynolds_number=100, mach_number=0.05, domain_length_x=1)
+    x, y = flow.grid
+    cyl = ((x - 0.3 * x.max()) ** 2 + (y - 0.5 * y.max()) ** 2) < (0.12 * y.max()) ** 2
+    flow.mask = cyl
+    f0 = flow.f.cpu().clone()
+    tau = max(float(flow.units.relaxation_parameter_lu), 0.6)
+    sim = lt.Simulation(flow, lt.BGKCollision(tau=tau), [])
+    kinds = [type(b).__name__ for b in sim.boundaries[1:]]
+    assert kinds == ["AntiBounceBackOutlet", "BounceBackBoundary", "EquilibriumBoundaryPU"]
+    lat = orc.OracleLattice("D2Q9", torch.float64)
+    eq = sim.boundaries[3]
+    rho_b, u_b = eq._lattice_units(flow)
+    inlet = torch.zeros(res, dtype=torch.bool)
+    inlet[0] = True
+    obnds = [orc.OracleBoundary("abb_outlet", direction=[1, 0]),
+             orc.OracleBoundary("bounce_back", cyl.cpu()),
+             orc.OracleBoundary("equilibrium", inlet, rho=rho_b.cpu().double(), u=u_b.cpu().double())]
+    ncm, nsm = orc.build_masks(lat, res, obnds)
+    assert torch.equal(ncm, sim.no_collision_mask.cpu())
+    sim(30)
+    ref = orc.run(lat, f0, 30, "bgk", dict(tau=tau), ncm=ncm, nsm=nsm, boundaries=obnds)
+    assert rel_err(flow.f.cpu().numpy(), ref.numpy()) <= TOL["f64"]
+
+
+def test_crossing_outlets_are_refused():
+    gu, lt = _gpu()
+    ctx = lt.Context(device="cuda", dtype=torch.float64, use_native=True)
+    f0 = torch.ones([9, 8, 8], dtype=torch.float64) / 9
+    flow = gu.FieldFlow(ctx, [8, 8], lt.D2Q9, f0)
+    flow.boundaries.append(gu.TaggedABBOutlet([1, 0], flow, tag=1))
+    flow.boundaries.append(gu.TaggedABBOutlet([0, 1], flow, tag=2))
+    with pytest.raises(NotImplementedError):
+        lt.Simulation(flow, lt.BGKCollision(0.8), [])

@@ -81,13 +81,17 @@ def test_mask_construction_later_index_wins():
     flow.mask = m
     bnds = [None] + sorted(flow.boundaries, key=lambda b: str(b))
     names = [type(b).__name__ for b in bnds[1:]]
-    assert names == ["BounceBackBoundary", "EquilibriumBoundaryPU", "EquilibriumBoundaryPU"]
+    # the stock list of obstacle.py:107-122 in the reference's sorted order
+    assert names == ["AntiBounceBackOutlet", "BounceBackBoundary", "EquilibriumBoundaryPU"]
     ncm, nsm = lt.build_masks(flow, bnds, ctx)
     assert ncm.dtype == torch.uint8 and nsm.dtype == torch.uint8
-    assert list(nsm.shape) == [9, 12, 8] and not nsm.any()
-    assert (ncm[1:3, 2:5] == 1).all()                 # bounce-back
-    assert (ncm[0, :] >= 2).all()                     # inlet overwrote the overlap
-    assert set(ncm[-1, :].tolist()) <= {2, 3} and (ncm[-1, :] >= 2).all()
+    assert list(nsm.shape) == [9, 12, 8]
+    assert (ncm[1:3, 2:5] == 2).all()                 # bounce-back
+    assert (ncm[0, :] == 3).all()                     # inlet overwrote the overlap (later index wins)
+    assert (ncm[-1, :] == 1).all()                    # the outlet plane
+    # anti_bounce_back_outlet.py:88-93: the populations opposite to the outgoing ones stay on the plane
+    kept = [q for q in range(9) if nsm[q].any()]
+    assert kept == [3, 6, 7] and all(bool(nsm[q, -1, :].all()) and not bool(nsm[q, :-1, :].any()) for q in kept)
     assert lt.build_masks(flow, [None], ctx) == (None, None)
 
 

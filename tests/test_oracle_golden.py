@@ -21,6 +21,9 @@ def oracle_inputs(case):
             bnds.append(orc.OracleBoundary("equilibrium", None,
                                            rho=torch.from_numpy(case[f"b{i}_rho"]),
                                            u=torch.from_numpy(case[f"b{i}_u"])))
+        elif b["kind"] in ("abb_outlet", "eq_outlet_p"):
+            bnds.append(orc.OracleBoundary(b["kind"], None, direction=b["direction"],
+                                           rho_outlet=b.get("rho_outlet", 1.0)))
         else:
             bnds.append(orc.OracleBoundary("bounce_back", None))
     return lat, f0, ncm, nsm, bnds
@@ -57,3 +60,19 @@ def test_oracle_observables(name):
         assert e == pytest.approx(case[okey][0], rel=tol)
         assert m == pytest.approx(case[okey][1], rel=tol)
         assert w == pytest.approx(case[okey][2], rel=10 * tol)
+
+
+@pytest.mark.parametrize("name", [n for n in golden_names() if n.startswith("outlet_")])
+def test_oracle_outlet_masks(name):
+    """the oracle's restatement of make_no_collision_mask / make_no_streaming_mask of the outlet
+    boundaries reproduces the masks the reference built"""
+    case = load_case(name)
+    meta = case["meta"]
+    lat, f0, ncm, nsm, bnds = oracle_inputs(case)
+    for i, (b, mb) in enumerate(zip(bnds, meta["boundaries"]), start=1):
+        if mb["kind"] == "bounce_back":
+            b.mask = torch.from_numpy(case[f"b{i}_mask"])
+        elif mb["kind"] == "equilibrium":
+            b.mask = ncm == i
+    ncm2, nsm2 = orc.build_masks(lat, meta["res"], bnds)
+    assert torch.equal(ncm2, ncm) and torch.equal(nsm2, nsm)
