@@ -8,6 +8,7 @@
 // After it, (a) the neighbours' stores into our planes are visible, so step t+1 may read them,
 // and (b) the neighbours have finished reading the buffer step t+1 will overwrite remotely.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "../../include/lettuce_b200.h"
@@ -39,6 +40,11 @@ halo_push_kernel(const uint4* __restrict__ src_hi, uint4* __restrict__ dst_hi,
                  const uint4* __restrict__ src_lo, uint4* __restrict__ dst_lo, size_t n_vec, size_t tail_bytes,
                  uint32_t* signal_up, uint32_t* signal_down, uint32_t* wait_slots, uint32_t value,
                  long long timeout_cycles) {
+  // Programmatic dependent launch, as in the step kernel: this grid is scheduled while the step kernel
+  // in front of it drains and waits here until that kernel has completed and its stores are visible;
+  // the step kernel behind it is scheduled likewise and waits for THIS grid (its prerequisite).
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
   const size_t stride = size_t(gridDim.x) * PUSH_BLOCK;
   if (src_hi != nullptr)
     for (size_t i = size_t(blockIdx.x) * PUSH_BLOCK + threadIdx.x; i < n_vec; i += stride) dst_hi[i] = src_hi[i];
@@ -79,11 +85,21 @@ int launch_halo_push(const void* src_hi, void* dst_hi, const void* src_lo, void*
   const bool copy = bytes != 0 && (src_hi != nullptr || src_lo != nullptr);
   const int grid = copy ? PUSH_GRID : 1;
   // ~10 s at 2 GHz: far beyond any legitimate skew between neighbours inside one node
-  halo_push_kernel<<<grid, PUSH_BLOCK, 0, st>>>(
-      copy ? static_cast<const uint4*>(src_hi) : nullptr, static_cast<uint4*>(dst_hi),
+  static const bool no_pdl = getenv("LB_NO_PDL") != nullptr;   // A/B timing only
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(PUSH_BLOCK);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = no_pdl ? 0 : 1;
+  const cudaError_t e = cudaLaunchKernelEx(
+      &cfg, halo_push_kernel, copy ? static_cast<const uint4*>(src_hi) : nullptr, static_cast<uint4*>(dst_hi),
       copy ? static_cast<const uint4*>(src_lo) : nullptr, static_cast<uint4*>(dst_lo), n_vec, tail,
       signal_up, signal_down, wait_slots, value, 20000000000ll);
-  return cudaGetLastError() == cudaSuccess ? 0 : -1;
+  return e == cudaSuccess ? 0 : -1;
 }
 
 // packed [zface][lines] -> f[q][line * nz + z_edge]
