@@ -197,7 +197,10 @@ LB_API int lb_collide(const lb_desc* desc, const void* f_in, void* f_out,
 LB_API int lb_stream(const lb_desc* desc, const void* f_in, void* f_out,
               const uint32_t* streaming_bits, void* stream);
 
-/* bits[x] |= (nsm[q][x] == 1) << q   (nsm: uint8 [q][*res]) */
+/* bits[x] = OR_q (nsm[q][x] == 1) << q   (nsm: uint8 [q][*res]); bit 31 of a word is a hint written by
+ * this function ("this node or one of its 26 periodic neighbours keeps a population") from which the
+ * step kernel decides per warp whether streaming needs masked stores: lb_fields.streaming_bits must
+ * come from this function. */
 LB_API int lb_pack_streaming_mask(const lb_desc* desc, const uint8_t* nsm, uint32_t* bits, void* stream);
 
 /* rho_out [*res] and/or u_out [d][*res] (either may be NULL) */
@@ -248,7 +251,8 @@ LB_API int lb_ipc_close(void* dptr);
 /* Introspection for tests / roofline arithmetic */
 LB_API int lb_stencil_q(int stencil);
 LB_API size_t lb_bytes_per_update(const lb_desc* desc); /* 2 * Q * sizeof(dtype) */
-LB_API int lb_vector_width(const lb_desc* desc, int has_streaming_bits); /* nodes per thread chosen */
+LB_API int lb_vector_width(const lb_desc* desc, int has_streaming_bits); /* nodes per thread chosen for aligned
+                                                                           fields (the flag no longer matters) */
 
 #ifdef __cplusplus
 }

@@ -97,8 +97,9 @@ int obs_prepare(const Geometry& g, void* scratch, lb::ObsScratch* out, cudaStrea
 // nodes per thread along the contiguous axis: the widest of 16 / 8 / 4(8) bytes that divides the
 // line and matches the buffers' alignment.  LB_VEC=<n> overrides the choice (tuning experiments).
 template <typename T>
-int vector_width(const lb_desc* d, const Geometry& g, const void* a, const void* b, bool sbits) {
-  if (sbits) return 1;
+int vector_width(const lb_desc* d, const Geometry& g, const void* a, const void* b, const void* ncm, const void* sbits,
+                 bool scalar_only) {
+  if (scalar_only) return 1;
   const int widest = 16 / int(sizeof(T));
   int cap = widest;
   // D3Q27 KBC / TRT hold ~60 values per node in registers beside the populations: fp32 runs two nodes
@@ -109,7 +110,9 @@ int vector_width(const lb_desc* d, const Geometry& g, const void* a, const void*
   static const char* env = getenv("LB_VEC");
   if (env && atoi(env) >= 1) cap = atoi(env) < widest ? atoi(env) : widest;
   for (int v = cap; v > 1; v >>= 1)
-    if (g.nz % unsigned(v) == 0 && aligned_to(a, v * sizeof(T)) && aligned_to(b, v * sizeof(T))) return v;
+    if (g.nz % unsigned(v) == 0 && aligned_to(a, v * sizeof(T)) && aligned_to(b, v * sizeof(T)) &&
+        aligned_to(ncm, v) && aligned_to(sbits, v * sizeof(uint32_t)))
+      return v;
   return 1;
 }
 
@@ -218,9 +221,21 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   c.mode = p.sbits ? lb::MODE_NCM_SBITS : (p.ncm ? lb::MODE_NCM : lb::MODE_PLAIN);
   c.stream = do_stream;
   c.halo = fl->halo != nullptr;
-  c.vec = do_stream ? vector_width<T>(d, g, fl->f, fl->f_next, p.sbits != nullptr || p.has_outlet) : 1;
+  c.vec = do_stream ? vector_width<T>(d, g, fl->f, fl->f_next, p.ncm, p.sbits, p.has_outlet && p.sbits == nullptr) : 1;
   p.nzv = g.nz / c.vec;
   p.n_threads = g.nx * g.ny * p.nzv;
+  // an outlet on the far side of the slowest axis: its plane is the last tiles of the grid -> run them first
+  for (int i = 0; i < p.n_bnd && do_stream; ++i) {
+    const lb::BoundaryDev<T>& o = p.bnd[i];
+    const bool outlet = o.kind == LB_BND_ABB_OUTLET || o.kind == LB_BND_EQ_OUTLET_P;
+    const int slowest = g.nx > 1 ? 0 : 1;
+    if (outlet && o.sign > 0 && o.axis == slowest) {
+      const unsigned grid = (p.n_threads + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK;
+      const unsigned plane_threads = p.n_threads / (slowest == 0 ? g.nx : g.ny);
+      const unsigned plane_blocks = plane_threads / lb::STEP_BLOCK + 2;
+      if (plane_blocks < grid) p.block_rot = grid - plane_blocks;
+    }
+  }
 
   if (fl->obs_out) {
     if (!fl->obs_scratch) return fail(LB_EINVAL, "obs_out given without obs_scratch");
@@ -393,6 +408,27 @@ __global__ void pack_sbits_kernel(const uint8_t* __restrict__ nsm, uint32_t* __r
   bits[i] = w;
 }
 
+// Second pass: bit 31 (LB_SBITS_NEAR) of a node's word = "this node or one of its 26 periodic neighbours
+// keeps a population".  The step kernel decides from this one bit, per warp, whether streaming needs the
+// masked stores at all.  Runs in place: only bit 31 changes, the reads look at the low bits.
+__global__ void mark_sbits_neighbourhood_kernel(uint32_t* bits, unsigned nx, unsigned ny, unsigned nz) {
+  const unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nx * ny * nz) return;
+  const unsigned z = i % nz, y = (i / nz) % ny, x = i / (nz * ny);
+  uint32_t any = 0;
+  for (int dx = -1; dx <= 1; ++dx) {
+    const unsigned xx = (x + nx + dx) % nx;
+    for (int dy = -1; dy <= 1; ++dy) {
+      const unsigned yy = (y + ny + dy) % ny;
+      for (int dz = -1; dz <= 1; ++dz) {
+        const unsigned zz = (z + nz + dz) % nz;
+        any |= bits[(size_t(xx) * ny + yy) * nz + zz] & ~lb::SBITS_NEAR;
+      }
+    }
+  }
+  if (any) atomicOr(bits + i, lb::SBITS_NEAR);
+}
+
 // ---- enstrophy: sum |curl u|^2 with the 6th-order periodic central difference -------------
 // reference/lettuce/util/utility.py:37-99 (weights [-1/60, 3/20, -3/4, 3/4, -3/20, 1/60] on
 // roll shifts [+3, +2, +1, -1, -2, -3], i.e. on u[x-3] ... u[x+3]) and
@@ -463,8 +499,9 @@ int lb_vector_width(const lb_desc* d, int has_streaming_bits) {
   Geometry g;
   if (check_desc(d, &g)) return -1;
   static char dummy[16] __attribute__((aligned(16)));
-  return d->dtype == LB_F64 ? vector_width<double>(d, g, dummy, dummy, has_streaming_bits != 0)
-                            : vector_width<float>(d, g, dummy, dummy, has_streaming_bits != 0);
+  (void)has_streaming_bits;   // masked streaming runs at the same width since ABI 4
+  return d->dtype == LB_F64 ? vector_width<double>(d, g, dummy, dummy, nullptr, nullptr, false)
+                            : vector_width<float>(d, g, dummy, dummy, nullptr, nullptr, false);
 }
 
 int lb_step(const lb_desc* desc, const lb_fields* fields, int n_steps, void* stream) {
@@ -500,6 +537,8 @@ int lb_pack_streaming_mask(const lb_desc* desc, const uint8_t* nsm, uint32_t* bi
   if (!nsm || !bits) return fail(LB_EINVAL, "null mask pointer");
   const unsigned block = 256, grid = (g.n_nodes + block - 1) / block;
   pack_sbits_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(nsm, bits, g.n_nodes, g.q);
+  LB_CUDA(cudaGetLastError());
+  mark_sbits_neighbourhood_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(bits, g.nx, g.ny, g.nz);
   LB_CUDA(cudaGetLastError());
   return LB_OK;
 }

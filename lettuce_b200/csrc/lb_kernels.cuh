@@ -38,6 +38,7 @@ constexpr int HALO_STAGE_LINES = 64;  // most lines of which a block can stage t
 
 enum { BND_BOUNCE_BACK = 1, BND_EQUILIBRIUM = 2, BND_ABB_OUTLET = 3, BND_EQ_OUTLET_P = 4 };
 enum { MODE_PLAIN = 0, MODE_NCM = 1, MODE_NCM_SBITS = 2 };
+constexpr uint32_t SBITS_NEAR = 0x80000000u;   // streaming_bits: neighbourhood hint, see lb_pack_streaming_mask
 
 // Scratch of the fused reductions (lb_obs_scratch_bytes): ticket counters and per-block / per-group
 // partial results.  All counters are zero between launches (each is reset by its last user).
@@ -113,6 +114,10 @@ struct StepParams {
   unsigned halo_hi_off, halo_lo_off;
   int halo_compact;
   int halo_stage_shift;   // see step_body: 0 = isolated stores, else log2(slots per (face, population))
+  // Block b of the grid works on tile (b + block_rot) mod grid.  The host rotates the tiles of an outlet
+  // plane at the END of the lattice to the front: they run the long boundary path (neighbour loads,
+  // masked stores), and as the last blocks of the grid that path was a tail of 6-9 us per step.
+  unsigned block_rot;
 };
 
 // number of directions q' < q that leave through the same z face as q
@@ -127,6 +132,15 @@ __host__ __device__ constexpr int zface_count() {
   int n = 0;
   for (int k = 0; k < S::Q; ++k) n += (S::e(k, 2) == 1) ? 1 : 0;
   return n;
+}
+
+// bit q set for the populations q >= 1 whose velocity is (ex, ey, ez) in kernel axes
+template <class S>
+__host__ __device__ constexpr uint32_t line_populations(int ex, int ey, int ez) {
+  uint32_t m = 0;
+  for (int k = 1; k < S::Q; ++k)
+    if (S::e(k, 0) == ex && S::e(k, 1) == ey && S::e(k, 2) == ez) m |= (1u << k);
+  return m;
 }
 
 template <typename T, int V>
@@ -391,8 +405,10 @@ __device__ __forceinline__ void packed_update(F2 (&g)[S::Q], const StepParams<fl
 // registers, 4 blocks (<= 128 registers) as measured at the HBM roofline -- except TRT, whose packed
 // pair form keeps a_p, b_p, S_p, D_p of two nodes live and spills below 168; D3Q27 fp32 with 2 or 4
 // nodes per thread (54 / 108 population registers): 3 blocks (<= 168 registers).
-template <class S, typename T, int V, int COLL>
+template <class S, typename T, int V, int COLL, int MODE = MODE_PLAIN>
 constexpr int step_min_blocks() {
+  // masked streaming keeps a few more registers per thread (destination bits): one block less
+  if (sizeof(T) == 4 && V >= 2 && MODE == MODE_NCM_SBITS) return (S::Q == 27) ? 2 : 3;
   if (sizeof(T) == 4 && V >= 2) return (S::Q == 27 || (COLL == COLL_TRT && V == 4)) ? 3 : 4;
   return 1;
 }
@@ -401,10 +417,11 @@ constexpr int step_min_blocks() {
 template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO, bool TICKET>
 __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __restrict__ f_in, T* __restrict__ f_out,
                                           double* obs_out, T* u_out) {
-  static_assert(MODE != MODE_NCM_SBITS || V == 1, "masked streaming runs one node per thread");
   constexpr int Q = S::Q;
   const unsigned lane = threadIdx.x & 31u;
-  const unsigned tid = blockIdx.x * STEP_BLOCK + threadIdx.x;
+  unsigned blk = blockIdx.x + p.block_rot;
+  if (blk >= gridDim.x) blk -= gridDim.x;
+  const unsigned tid = blk * STEP_BLOCK + threadIdx.x;
   const bool active = tid < p.n_threads;
   const unsigned t = active ? tid : p.n_threads - 1u;  // clamp: keeps address math valid
   const unsigned nzv = p.nzv, nz = p.nz, ny = p.ny, nx = p.nx;
@@ -428,6 +445,19 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
 #pragma unroll
     for (int k = 0; k < NF; ++k) hin[k] = hsrc[k * lines];
   }
+
+  // ---- masked streaming (no_streaming_mask packed as one bit per population and node, p.sbits) ----
+  // Bit 31 of a node's word says that the node or one of its 26 neighbours keeps a population
+  // (lb_pack_streaming_mask).  Loaded HERE with the populations; a warp none of whose nodes has it set --
+  // almost all of them -- streams with the plain vector stores.
+  constexpr bool SB = (MODE == MODE_NCM_SBITS) && STREAM;
+  [[maybe_unused]] uint32_t near_kept = 0;
+  if constexpr (SB) {
+    const Vec<uint32_t, V> ow = ld_vec<uint32_t, V>(p.sbits + node);
+#pragma unroll
+    for (int k = 0; k < V; ++k) near_kept |= ow.v[k];
+  }
+  [[maybe_unused]] auto kept = [](uint32_t bits, int q) { return ((bits >> q) & 1u) != 0u; };
 
   // ---- load: Q aligned vector loads ------------------------------------------------
   T f[Q][V];
@@ -462,6 +492,9 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
   // (FADD2 / FMUL2 / FFMA2); a pair that contains a boundary node, and every other case, goes node
   // by node.  Both routes round identically (lb_physics.cuh), so the result does not depend on V.
   constexpr bool PACK = (sizeof(T) == 4) && (V % 2 == 0);
+  // the outlet kinds are compiled into the kernels that can meet them: outlets come with a
+  // no-streaming mask (MODE_NCM_SBITS); collide-only calls and odd layouts run V == 1
+  constexpr bool OUTL = (V == 1) || (MODE == MODE_NCM_SBITS);
   if constexpr (PACK) {
 #pragma unroll
     for (int kk = 0; kk < V / 2; ++kk) {
@@ -483,7 +516,7 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
         for (int k = 2 * kk; k < 2 * kk + 2; ++k) {
           T g[Q];
           static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
-          node_update<S, T, COLL, MODE, OBS, false>(g, (m2 >> (8 * (k - 2 * kk))) & 0xffu, p, f_in, u_out, x, y, z0 + k, node + k, active,
+          node_update<S, T, COLL, MODE, OBS, OUTL>(g, (m2 >> (8 * (k - 2 * kk))) & 0xffu, p, f_in, u_out, x, y, z0 + k, node + k, active,
                                              acc_e, acc_m2, acc_mass);
           static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
         }
@@ -495,7 +528,7 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
       T g[Q];
       static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
       const unsigned m = (MODE == MODE_PLAIN) ? 0u : ((mword >> (8 * k)) & 0xffu);
-      node_update<S, T, COLL, MODE, OBS, V == 1>(g, m, p, f_in, u_out, x, y, z0 + k, node + k, active, acc_e, acc_m2, acc_mass);
+      node_update<S, T, COLL, MODE, OBS, OUTL>(g, m, p, f_in, u_out, x, y, z0 + k, node + k, active, acc_e, acc_m2, acc_mass);
       static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
     }
   }
@@ -530,8 +563,6 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
     // element offset of that edge element relative to this thread's own vector in the destination line
     const unsigned d_up = last_in_line ? 0u - z0 : unsigned(V);
     const unsigned d_dn = first_in_line ? nz - 1u : 0u - 1u;
-    uint32_t own_bits = 0;
-    if constexpr (MODE == MODE_NCM_SBITS) own_bits = p.sbits[node];
 
     // z-slab halos in the PACKED layout [z-face population][line]: the one element per line and
     // population that leaves through a z face is staged in shared memory and written by consecutive
@@ -545,9 +576,49 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
     __shared__ unsigned stage_dst[(HALO && V > 1) ? 2 * NF * HALO_STAGE_LINES : 1];
     const unsigned sshift = HALO ? unsigned(p.halo_stage_shift) : 0u;
     const bool staged = HALO && V > 1 && sshift != 0u;
-    const unsigned first_line_blk = (blockIdx.x * unsigned(STEP_BLOCK)) / nzv;
+    const unsigned first_line_blk = (blk * unsigned(STEP_BLOCK)) / nzv;
     [[maybe_unused]] const unsigned lline = line - first_line_blk;
 
+    // The masked variant of the loop below (element-by-element stores under the no-streaming bits) is a
+    // SECOND copy of the code, entered by whole warps: a warp none of whose lanes saw a set bit -- almost
+    // all of them -- runs exactly the unmasked stores.  (One copy with per-population tests was measured
+    // at 1640 instructions per warp and 0.70 of the roofline: the compiler predicates the rare path in.)
+    auto stream_all = [&](auto masked_c) {
+    constexpr bool MASKED = SB && decltype(masked_c)::value;
+    // masked copy: ALL the bits it will test in one batch of independent loads (tested one load at a time,
+    // the blocks on an outlet plane were a 9 us tail of the step):
+    //   own_m[k]   bit q: this thread's node k keeps its own value of population q
+    //   dst_m[k]   bit q: element k of the aligned vector this thread writes for population q falls on a
+    //              kept node of the DESTINATION line (one vector load of bits per (ex, ey) neighbour line)
+    //   edge_m_up / edge_m_dn: the same for the single element that leaves the thread's vector upwards /
+    //              downwards (ez = +1 / -1; with V == 1 every destination of ez != 0 is such an element)
+    [[maybe_unused]] uint32_t own_m[V], dst_m[V];
+    [[maybe_unused]] uint32_t own_any = 0, dst_any = 0, edge_m_up = 0, edge_m_dn = 0;
+    if constexpr (MASKED) {
+      const bool ld_up = active && (V == 1 || edge_up), ld_dn = active && (V == 1 || edge_dn);
+      const Vec<uint32_t, V> ow = ld_vec<uint32_t, V>(p.sbits + node);
+#pragma unroll
+      for (int k = 0; k < V; ++k) { own_m[k] = ow.v[k]; own_any |= ow.v[k]; dst_m[k] = 0u; }
+      static_for<9>([&](auto cc) {
+        constexpr int c = decltype(cc)::value;
+        constexpr int ex = c / 3 - 1, ey = c % 3 - 1;
+        constexpr uint32_t m0 = line_populations<S>(ex, ey, 0), mu = line_populations<S>(ex, ey, 1),
+                           md = line_populations<S>(ex, ey, -1);
+        constexpr uint32_t in_vec = (V == 1) ? m0 : (m0 | mu | md);
+        if constexpr ((m0 | mu | md) != 0) {
+          const unsigned i0 = (xs[ex + 1] + ys[ey + 1]) * nz + z0;
+          if constexpr (in_vec != 0) {
+            const Vec<uint32_t, V> w = ld_vec<uint32_t, V>(p.sbits + i0);
+#pragma unroll
+            for (int k = 0; k < V; ++k) dst_m[k] |= w.v[k] & in_vec;
+          }
+          if constexpr (mu != 0) edge_m_up |= (ld_up ? p.sbits[i0 + d_up] : 0u) & mu;
+          if constexpr (md != 0) edge_m_dn |= (ld_dn ? p.sbits[i0 + d_dn] : 0u) & md;
+        }
+      });
+#pragma unroll
+      for (int k = 0; k < V; ++k) dst_any |= dst_m[k];
+    }
     static_for<Q>([&](auto qc) {
       constexpr int q = decltype(qc)::value;
       constexpr int ex = S::e(q, 0), ey = S::e(q, 1), ez = S::e(q, 2);
@@ -556,19 +627,60 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
       [[maybe_unused]] const unsigned idx = dline + z0;  // this thread's vector in the destination line
       T* const bq = f_out + size_t(q) * N;               // uniform
 
-      if constexpr (MODE == MODE_NCM_SBITS) {
-        // destination-masked streaming, one node per thread
-        const unsigned zd = (ez == 0) ? z0 : (ez > 0 ? (z0 + 1 == nz ? 0u : z0 + 1)
-                                                     : (z0 == 0 ? nz - 1 : z0 - 1));
+      if constexpr (MASKED && q != 0) {
+        // own values that streaming must not overwrite (the destination tests below keep every other
+        // thread from writing there)
+        if (active && kept(own_any, q)) {
+#pragma unroll
+          for (int k = 0; k < V; ++k)
+            if (kept(own_m[k], q)) bq[node + k] = f[q][k];
+        }
+      }
+      if constexpr (MASKED && q != 0 && ez == 0) {
+        Vec<T, V> v;
+#pragma unroll
+        for (int k = 0; k < V; ++k) v.v[k] = f[q][k];
         if (active) {
-          if constexpr (q == 0) {
-            bq[dline + zd] = f[q][0];
+          if (!kept(dst_any, q)) {
+            st_vec<T, V>(bq + idx, v);
           } else {
-            const uint32_t dbits = p.sbits[dline + zd];
-            if (!((dbits >> q) & 1u)) bq[dline + zd] = f[q][0];
-            if ((own_bits >> q) & 1u) bq[node] = f[q][0];
+#pragma unroll
+            for (int k = 0; k < V; ++k)
+              if (!kept(dst_m[k], q)) bq[idx + k] = v.v[k];
           }
         }
+      } else if constexpr (MASKED && q != 0 && V == 1) {
+        // one node per thread: its destination is the "edge" element (d_up = 1 or the wrap)
+        if constexpr (ez > 0) { if (active && !kept(edge_m_up, q)) bq[idx + d_up] = f[q][0]; }
+        else { if (active && !kept(edge_m_dn, q)) bq[idx + d_dn] = f[q][0]; }
+      } else if constexpr (MASKED && q != 0 && ez > 0) {
+        const T up = __shfl_up_sync(0xffffffffu, f[q][V - 1], 1);
+        Vec<T, V> v;
+        v.v[0] = up;
+#pragma unroll
+        for (int k = 1; k < V; ++k) v.v[k] = f[q][k - 1];
+        if (st_left && !kept(dst_any, q)) {
+          st_vec<T, V>(bq + idx, v);
+        } else if (active) {
+#pragma unroll
+          for (int k = 0; k < V; ++k)
+            if ((k > 0 || has_left) && !kept(dst_m[k], q)) bq[idx + k] = v.v[k];
+        }
+        if (edge_up && !kept(edge_m_up, q)) bq[idx + d_up] = f[q][V - 1];
+      } else if constexpr (MASKED && q != 0) {
+        const T dn = __shfl_down_sync(0xffffffffu, f[q][0], 1);
+        Vec<T, V> v;
+#pragma unroll
+        for (int k = 0; k < V - 1; ++k) v.v[k] = f[q][k + 1];
+        v.v[V - 1] = dn;
+        if (st_right && !kept(dst_any, q)) {
+          st_vec<T, V>(bq + idx, v);
+        } else if (active) {
+#pragma unroll
+          for (int k = 0; k < V; ++k)
+            if ((k < V - 1 || has_right) && !kept(dst_m[k], q)) bq[idx + k] = v.v[k];
+        }
+        if (edge_dn && !kept(edge_m_dn, q)) bq[idx + d_dn] = f[q][0];
       } else if constexpr (ez == 0) {
         Vec<T, V> v;
 #pragma unroll
@@ -636,11 +748,18 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
         }
       }
     });
+    };
+    if constexpr (SB) {
+      if (__any_sync(0xffffffffu, (near_kept & SBITS_NEAR) != 0u)) stream_all(std::true_type{});
+      else stream_all(std::false_type{});
+    } else {
+      stream_all(std::false_type{});
+    }
 
     if constexpr (HALO && V > 1) {
       if (staged) {   // block-uniform
         __syncthreads();
-        const unsigned t0 = blockIdx.x * unsigned(STEP_BLOCK);
+        const unsigned t0 = blk * unsigned(STEP_BLOCK);
         const unsigned t1 = min(t0 + unsigned(STEP_BLOCK), p.n_threads);
         for (unsigned e = threadIdx.x; e < (unsigned(2 * NF) << sshift); e += STEP_BLOCK) {
           const unsigned pair = e >> sshift, j = e & ((1u << sshift) - 1u);
@@ -676,7 +795,7 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
 }
 
 template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO>
-__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V, COLL>())
+__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V, COLL, MODE>())
 step_kernel(const __grid_constant__ StepParams<T> p) {
   // Programmatic dependent launch: let the next step's grid be scheduled while this one drains, and
   // wait here -- before the first global access -- until the previous step's grid has completed and
@@ -694,7 +813,7 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
 constexpr int OBS_STRIDE = 4;   // == LB_OBS_COUNT (include/lettuce_b200.h)
 
 template <class S, typename T, int V, int COLL, int MODE, bool OBS>
-__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V, COLL>())
+__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V, COLL, MODE>())
 step_loop_kernel(const __grid_constant__ StepParams<T> p, int n_loop) {
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
   for (int s = 0; s < n_loop; ++s) {
@@ -867,9 +986,7 @@ cudaError_t launch_vec(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   switch (c.mode) {
     case MODE_PLAIN: return launch_mode<S, T, V, COLL, MODE_PLAIN>(c, p, st);
     case MODE_NCM: return launch_mode<S, T, V, COLL, MODE_NCM>(c, p, st);
-    case MODE_NCM_SBITS:
-      if constexpr (V == 1) return launch_mode<S, T, V, COLL, MODE_NCM_SBITS>(c, p, st);
-      else return cudaErrorInvalidValue;
+    case MODE_NCM_SBITS: return launch_mode<S, T, V, COLL, MODE_NCM_SBITS>(c, p, st);
   }
   return cudaErrorInvalidValue;
 }

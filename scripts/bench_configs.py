@@ -112,7 +112,7 @@ def main():
         del flow, sim
         gc.collect()
     # the stock lt.Obstacle boundary list: AntiBounceBackOutlet on +x (per-population streaming mask ->
-    # the one-node-per-thread masked-streaming kernel)
+    # the masked-streaming kernel)
     name = "stock lt.Obstacle D2Q9 BGK f32 2048x1024 (equilibrium inlet, anti-bounce-back outlet, bounce-back)"
     if wanted(name):
         ctx = lt.Context(device="cuda", dtype=torch.float32, use_native=True)
@@ -122,6 +122,20 @@ def main():
         sim = lt.Simulation(flow, lt.BGKCollision(flow.units.relaxation_parameter_lu), [])
         t = timed(sim, 5 * S)
         report(name, flow, t, 5 * S)
+        del flow, sim
+        gc.collect()
+    # the same boundary list in 3-D: a sphere in a 384 x 192 x 192 channel, D3Q19 and D3Q27
+    for st, nm in ((lt.D3Q19, "D3Q19"), (lt.D3Q27, "D3Q27")):
+        name = f"stock lt.Obstacle {nm} BGK f32 384x192x192 (equilibrium inlet, anti-bounce-back outlet, bounce-back)"
+        if not wanted(name):
+            continue
+        ctx = lt.Context(device="cuda", dtype=torch.float32, use_native=True)
+        flow = lt.Obstacle(ctx, [384, 192, 192], reynolds_number=300, mach_number=0.01, domain_length_x=2, stencil=st)
+        x, y, z = flow.grid
+        flow.mask = ((x - 0.3 * x.max()) ** 2 + (y - 0.5 * y.max()) ** 2 + (z - 0.5 * z.max()) ** 2) < (0.1 * y.max()) ** 2
+        sim = lt.Simulation(flow, lt.BGKCollision(flow.units.relaxation_parameter_lu), [])
+        t = timed(sim, S)
+        report(name, flow, t, S)
         del flow, sim
         gc.collect()
     tgv_case("TGV2D D2Q9 BGK f32 2048x1024 (no masks)", [2048, 1024], lt.D2Q9, torch.float32, "bgk", 5 * S)

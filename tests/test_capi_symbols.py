@@ -39,7 +39,7 @@ def test_descriptor_validation_needs_no_gpu():
     assert [L.lb_stencil_q(i) for i in range(4)] == [9, 19, 27, -1]
     d = nat.make_desc("D3Q19", torch.float32, [256, 256, 256], nat.LB_COLL_BGK, 0.6)
     assert L.lb_bytes_per_update(d) == 152            # 2 * Q * sizeof(float), BASELINE.md section 3
-    assert L.lb_vector_width(d, 0) == 4 and L.lb_vector_width(d, 1) == 1
+    assert L.lb_vector_width(d, 0) == 4 and L.lb_vector_width(d, 1) == 4   # masked streaming is vectorised too
     d64 = nat.make_desc("D2Q9", torch.float64, [256, 256], nat.LB_COLL_BGK, 0.6)
     assert L.lb_bytes_per_update(d64) == 144 and L.lb_vector_width(d64, 0) == 2
     odd = nat.make_desc("D3Q27", torch.float32, [5, 7, 9])
