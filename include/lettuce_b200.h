@@ -43,12 +43,16 @@ extern "C" {
 #define LB_API
 #endif
 
-#define LB_ABI_VERSION 4
+#define LB_ABI_VERSION 5
 #define LB_MAX_BOUNDARIES 8
 
 enum { LB_D2Q9 = 0, LB_D3Q19 = 1, LB_D3Q27 = 2 };                     /* lb_desc.stencil   */
 enum { LB_F32 = 0, LB_F64 = 1 };                                      /* lb_desc.dtype     */
-enum { LB_COLL_NONE = 0, LB_COLL_BGK = 1, LB_COLL_TRT = 2, LB_COLL_KBC = 3 }; /* .collision */
+enum { LB_COLL_NONE = 0, LB_COLL_BGK = 1, LB_COLL_TRT = 2, LB_COLL_KBC = 3,
+       LB_COLL_REGULARIZED = 4, /* regularized_collision.py:17-44; tau as the reference reads it from the units */
+       LB_COLL_SMAGORINSKY = 5  /* smagorinsky_collision.py:19-36; lb_desc.tau_minus carries the Smagorinsky
+                                   constant (default 0.17), two fixed-point iterations for tau_eff */
+}; /* .collision */
 enum { LB_BND_BOUNCE_BACK = 1, LB_BND_EQUILIBRIUM = 2,                 /* lb_boundary.kind  */
        LB_BND_ABB_OUTLET = 3, LB_BND_EQ_OUTLET_P = 4 };
 
@@ -76,7 +80,7 @@ typedef struct lb_desc {
   int32_t ndim;        /* 2 or 3 (must match stencil)   */
   int64_t dims[3];     /* resolution, dims[ndim-1] is the contiguous axis */
   double tau;          /* BGK: tau; TRT: tau_plus; KBC: tau (beta = 1/(2 tau)) */
-  double tau_minus;    /* TRT only (trt_collision.py:12-14) */
+  double tau_minus;    /* TRT: tau_minus (trt_collision.py:12-14); Smagorinsky: the constant (:13) */
 } lb_desc;
 
 /* One entry per boundary object, in the order lettuce sorted them

@@ -5,7 +5,9 @@ used on its own, e.g. by conservation tests (reference/tests/collision/*).
 
 BGK  reference/lettuce/ext/_collision/bgk_collision.py:12-35
 TRT  .../trt_collision.py:6-27        KBC  .../kbc_collision.py:11-167
-None .../no_collision.py:9-17"""
+None .../no_collision.py:9-17
+Regularized .../regularized_collision.py:8-49   Smagorinsky .../smagorinsky_collision.py:7-41
+(the reference has no native kernels for these two)"""
 import warnings
 from abc import ABC, abstractmethod
 
@@ -14,7 +16,7 @@ import torch
 from . import _native as nat
 
 __all__ = ['Collision', 'BGKCollision', 'TRTCollision', 'KBCCollision', 'KBCCollision2D',
-           'KBCCollision3D', 'NoCollision']
+           'KBCCollision3D', 'NoCollision', 'RegularizedCollision', 'SmagorinskyCollision']
 
 
 class Collision(ABC):
@@ -112,3 +114,39 @@ class KBCCollision3D(KBCCollision):
     def __init__(self, tau: float = None):
         warnings.warn("KBCCollision2D is is deprecated! Use KBCCollision instead!")
         super().__init__()
+
+
+class RegularizedCollision(Collision):
+    """Regularized LBM according to Jonas Latt and Bastien Chopard (2006).  As in the reference, the
+    constructor's tau is ignored: tau is read from flow.units.relaxation_parameter_lu at first use
+    (regularized_collision.py:18-19)."""
+
+    def __init__(self, tau: float = None):
+        self.tau = tau
+        self._bound = False
+
+    def native_descriptor(self, flow):
+        if not self._bound:
+            self.tau = flow.units.relaxation_parameter_lu
+            self._bound = True
+        return dict(collision=nat.LB_COLL_REGULARIZED, tau=float(self.tau))
+
+
+class SmagorinskyCollision(Collision):
+    """Smagorinsky large eddy simulation (LES) collision model with BGK operator
+    (smagorinsky_collision.py:7-36): two fixed-point iterations for the effective relaxation time per
+    node, inside the step kernel.  `tau_eff` of the reference is a per-node field that exists only in
+    registers here."""
+
+    def __init__(self, tau, smagorinsky_constant=0.17, force=None):
+        if force is not None:
+            raise NotImplementedError("forcing schemes are outside the hot-path scope (SURVEY.md "
+                                      "section 2 row 7); the reference's native path has none either")
+        self.force = force
+        self.tau = tau
+        self.iterations = 2
+        self.constant = smagorinsky_constant
+
+    def native_descriptor(self, flow):
+        # lb_desc.tau_minus carries the Smagorinsky constant (include/lettuce_b200.h)
+        return dict(collision=nat.LB_COLL_SMAGORINSKY, tau=float(self.tau), tau_minus=float(self.constant))

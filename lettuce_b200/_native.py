@@ -17,10 +17,11 @@ LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "liblettuce_
 LB_D2Q9, LB_D3Q19, LB_D3Q27 = 0, 1, 2
 LB_F32, LB_F64 = 0, 1
 LB_COLL_NONE, LB_COLL_BGK, LB_COLL_TRT, LB_COLL_KBC = 0, 1, 2, 3
+LB_COLL_REGULARIZED, LB_COLL_SMAGORINSKY = 4, 5
 LB_BND_BOUNCE_BACK, LB_BND_EQUILIBRIUM, LB_BND_ABB_OUTLET, LB_BND_EQ_OUTLET_P = 1, 2, 3, 4
 LB_OBS_ENERGY, LB_OBS_MAXU2, LB_OBS_MASS, LB_OBS_ENSTROPHY, LB_OBS_COUNT = 0, 1, 2, 3, 4
 LB_MAX_BOUNDARIES = 8
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 STENCIL_IDS = {"D2Q9": LB_D2Q9, "D3Q19": LB_D3Q19, "D3Q27": LB_D3Q27}
 DTYPE_IDS = {torch.float32: LB_F32, torch.float64: LB_F64}

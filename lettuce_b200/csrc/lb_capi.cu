@@ -49,7 +49,7 @@ int check_desc(const lb_desc* d, Geometry* g) {
   if (q < 0) return fail(LB_EINVAL, "unknown stencil id %d", d->stencil);
   if (d->ndim != dim) return fail(LB_EINVAL, "stencil is %d-D but ndim = %d", dim, d->ndim);
   if (d->dtype != LB_F32 && d->dtype != LB_F64) return fail(LB_EINVAL, "unknown dtype %d", d->dtype);
-  if (d->collision < LB_COLL_NONE || d->collision > LB_COLL_KBC)
+  if (d->collision < LB_COLL_NONE || d->collision > LB_COLL_SMAGORINSKY)
     return fail(LB_EINVAL, "unknown collision id %d", d->collision);
   if (d->collision == LB_COLL_KBC && d->stencil == LB_D3Q19)
     return fail(LB_EUNSUPPORTED, "KBC collision is only implemented for D2Q9 and D3Q27");
@@ -61,6 +61,8 @@ int check_desc(const lb_desc* d, Geometry* g) {
   }
   if (d->collision != LB_COLL_NONE && !(d->tau > 0.0)) return fail(LB_EINVAL, "tau must be > 0");
   if (d->collision == LB_COLL_TRT && !(d->tau_minus > 0.0)) return fail(LB_EINVAL, "tau_minus must be > 0");
+  if (d->collision == LB_COLL_SMAGORINSKY && !(d->tau_minus >= 0.0))
+    return fail(LB_EINVAL, "the Smagorinsky constant (tau_minus) must be >= 0");
   g->q = q;
   g->d = dim;
   if (dim == 2) { g->nx = 1; g->ny = (unsigned)d->dims[0]; g->nz = (unsigned)d->dims[1]; }
@@ -79,6 +81,10 @@ lb::CollisionParams<T> make_cp(const lb_desc* d) {
   const double beta = 1. / (2 * d->tau);
   cp.beta = T(beta);
   cp.inv_beta = T(1. / beta);
+  cp.reg_c = T(1. - 1. / d->tau);
+  cp.smag_tau = T(d->tau);
+  cp.smag_nu = T((d->tau - 0.5) / 3.0);
+  cp.smag_c2 = T(d->tau_minus * d->tau_minus);   // LB_COLL_SMAGORINSKY: tau_minus = the Smagorinsky constant
   return cp;
 }
 

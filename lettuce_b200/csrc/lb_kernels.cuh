@@ -409,7 +409,7 @@ template <class S, typename T, int V, int COLL, int MODE = MODE_PLAIN>
 constexpr int step_min_blocks() {
   // masked streaming keeps a few more registers per thread (destination bits): one block less
   if (sizeof(T) == 4 && V >= 2 && MODE == MODE_NCM_SBITS) return (S::Q == 27) ? 2 : 3;
-  if (sizeof(T) == 4 && V >= 2) return (S::Q == 27 || (COLL == COLL_TRT && V == 4)) ? 3 : 4;
+  if (sizeof(T) == 4 && V >= 2) return (S::Q == 27 || ((COLL == COLL_TRT || COLL >= COLL_REGULARIZED) && V == 4)) ? 3 : 4;
   return 1;
 }
 
@@ -908,6 +908,8 @@ cudaError_t launch_step(StepConfig& c, const StepParams<T>& p, cudaStream_t st) 
     case COLL_KBC:
       if constexpr (S::ID != 1) return launch_step_coll<S, T, COLL_KBC>(c, p, st);
       else return cudaErrorNotSupported;
+    case COLL_REGULARIZED: return launch_step_coll<S, T, COLL_REGULARIZED>(c, p, st);
+    case COLL_SMAGORINSKY: return launch_step_coll<S, T, COLL_SMAGORINSKY>(c, p, st);
   }
   return cudaErrorInvalidValue;
 }

@@ -32,6 +32,10 @@ struct CollisionParams {
   T inv_2tau_m;   // TRT: 1/(2 tau_minus)  (trt_collision.py:23-25)
   T beta;         // KBC: 1/(2 tau)        (kbc_collision.py:98-99)
   T inv_beta;     // KBC: 1/beta as the reference evaluates `1. / self.beta` (:153)
+  T reg_c;        // Regularized: 1 - 1/tau  (regularized_collision.py:41)
+  T smag_tau;     // Smagorinsky: tau, nu = (tau - 0.5) / 3.0, constant ** 2  (smagorinsky_collision.py:27-33)
+  T smag_nu;
+  T smag_c2;
 };
 
 // ---------------------------------------------------------------------------------------
@@ -217,7 +221,108 @@ __host__ __device__ __forceinline__ void equilibrium(R rho, const R (&u)[3], R (
   });
 }
 
-enum { COLL_NONE = 0, COLL_BGK = 1, COLL_TRT = 2, COLL_KBC = 3 };
+enum { COLL_NONE = 0, COLL_BGK = 1, COLL_TRT = 2, COLL_KBC = 3, COLL_REGULARIZED = 4, COLL_SMAGORINSKY = 5 };
+
+// Second moments of the non-equilibrium part, Pi_AB = sum_q e_A e_B (f_q - feq_q)  (Flow.shear_tensor of
+// f - feq, _flow.py:202-208): population 0 does not contribute and an opposite pair contributes through
+// n_p = (f_q + f_o) - (feq_q + feq_o) = a_p - 2 S_p only.
+template <class S, typename R>
+__host__ __device__ __forceinline__ EvenMoments<R> nonequilibrium_shear(const R (&a)[N_SLOTS], const R (&Sp)[N_SLOTS]) {
+  R n[N_SLOTS];
+  static_for<N_SLOTS>([&](auto sc) {
+    constexpr int s = decltype(sc)::value;
+    if constexpr (has_slot<S, s>) n[s] = fma_(R(-2), Sp[s], a[s]);
+  });
+  return even_moments<S, R>(n);   // .sum unused
+}
+
+// e . Pi . e for the direction of a slot (D2Q9 has no slot with an x component)
+template <int SLOT, typename R>
+__host__ __device__ __forceinline__ R slot_quadratic_form(const EvenMoments<R>& m) {
+  constexpr int ex = slot_e(SLOT, 0), ey = slot_e(SLOT, 1), ez = slot_e(SLOT, 2);
+  if constexpr (ex != 0 && ey != 0 && ez != 0) {
+    R off = (ex * ey > 0) ? m.xy : -m.xy;
+    off = (ex * ez > 0) ? off + m.xz : off - m.xz;
+    off = (ey * ez > 0) ? off + m.yz : off - m.yz;
+    return fma_(R(2), off, (m.xx + m.yy) + m.zz);
+  } else if constexpr (ex != 0 && ey != 0) {
+    return fma_(R(2 * ex * ey), m.xy, m.xx + m.yy);
+  } else if constexpr (ex != 0 && ez != 0) {
+    return fma_(R(2 * ex * ez), m.xz, m.xx + m.zz);
+  } else if constexpr (ey != 0 && ez != 0) {
+    return fma_(R(2 * ey * ez), m.yz, m.yy + m.zz);
+  } else if constexpr (ex != 0) {
+    return m.xx;
+  } else if constexpr (ey != 0) {
+    return m.yy;
+  } else {
+    return m.zz;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// Regularized LBM, Latt & Chopard 2006 (regularized_collision.py:17-44):
+//   Pi = shear_tensor(f - feq);  fi1_q = w_q (Q_q : Pi) / (2 cs^4),  Q_q,ab = e_a e_b - cs^2 delta_ab;
+//   f_q = feq_q + (1 - 1/tau) fi1_q.
+// Q_q : Pi = e.Pi.e - cs^2 tr Pi is even in e, so both members of a pair get the same fi1.
+// ---------------------------------------------------------------------------------------
+template <class S, typename R>
+__host__ __device__ __forceinline__ void regularized_relax(R (&f)[S::Q], R feq0, const R (&a)[N_SLOTS],
+                                                           const R (&Sp)[N_SLOTS], const R (&Dp)[N_SLOTS], R c) {
+  const EvenMoments<R> pi = nonequilibrium_shear<S, R>(a, Sp);
+  const R trace = (S::D == 3) ? (pi.xx + pi.yy) + pi.zz : pi.yy + pi.zz;
+  const R cs2_trace = R(LB_CS2) * trace;
+  const R k = c * R(1.0 / (2.0 * LB_CS2 * LB_CS2));   // (1 - 1/tau) / (2 cs^4)
+  f[0] = fma_(-(k * R(S::w(0))), cs2_trace, feq0);
+  static_for<N_SLOTS>([&](auto sc) {
+    constexpr int s = decltype(sc)::value;
+    if constexpr (has_slot<S, s>) {
+      constexpr int q = pair_q<S>(s), o = S::opp(q);
+      const R fi1 = (k * R(S::w(q))) * (slot_quadratic_form<s, R>(pi) - cs2_trace);
+      f[q] = (Sp[s] + Dp[s]) + fi1;
+      f[o] = (Sp[s] - Dp[s]) + fi1;
+    }
+  });
+}
+
+// ---------------------------------------------------------------------------------------
+// Smagorinsky LES with the BGK operator (smagorinsky_collision.py:19-36):
+//   S_shear = shear_tensor(f - feq) / (2 rho cs^2);  tau_eff = tau;  nu = (tau - 0.5) / 3;
+//   twice:  S = S_shear / tau_eff;  nu_t = C^2 sum_ab S_ab S_ab;  tau_eff = 3 (nu + nu_t) + 0.5;
+//   f - (f - feq) / tau_eff.
+// ---------------------------------------------------------------------------------------
+template <class S, typename R>
+__host__ __device__ __forceinline__ void smagorinsky_relax(R (&f)[S::Q], R feq0, R rho, const R (&a)[N_SLOTS],
+                                                           const R (&Sp)[N_SLOTS], const R (&Dp)[N_SLOTS], R tau,
+                                                           R nu, R c2) {
+  const EvenMoments<R> pi = nonequilibrium_shear<S, R>(a, Sp);
+  const R inv = div_(R(1), R(2.0 * LB_CS2) * rho);
+  // sum_ab (Pi_ab / (2 rho cs^2))^2 over the full d x d tensor: diagonal once, off-diagonal twice
+  const R yy = pi.yy * inv, zz = pi.zz * inv, yz = pi.yz * inv;
+  R diag = fma_(yy, yy, zz * zz), off = yz * yz;
+  if constexpr (S::D == 3) {
+    const R xx = pi.xx * inv, xy = pi.xy * inv, xz = pi.xz * inv;
+    diag = fma_(xx, xx, diag);
+    off = fma_(xy, xy, fma_(xz, xz, off));
+  }
+  const R p2 = fma_(R(2), off, diag);
+  R tau_eff = tau;
+#pragma unroll
+  for (int it = 0; it < 2; ++it) {   // self.iterations = 2 (:17)
+    const R ss = div_(p2, tau_eff * tau_eff);
+    tau_eff = fma_(fma_(c2, ss, nu), R(3), R(0.5));
+  }
+  const R om = div_(R(1), tau_eff);
+  f[0] = fma_(om, feq0 - f[0], f[0]);
+  static_for<N_SLOTS>([&](auto sc) {
+    constexpr int s = decltype(sc)::value;
+    if constexpr (has_slot<S, s>) {
+      constexpr int q = pair_q<S>(s), o = S::opp(q);
+      f[q] = fma_(om, (Sp[s] + Dp[s]) - f[q], f[q]);
+      f[o] = fma_(om, (Sp[s] - Dp[s]) - f[o], f[o]);
+    }
+  });
+}
 
 // ---------------------------------------------------------------------------------------
 // KBC (kbc_collision.py:25-160).  The reference builds all raw moments of f and of feq with an
@@ -352,6 +457,10 @@ __host__ __device__ __forceinline__ void collide_node(R (&f)[S::Q], const R (&a)
           f[o] = f[o] - (sp - sm);
         }
       });
+    } else if constexpr (COLL == COLL_REGULARIZED) {
+      regularized_relax<S, R>(f, feq0, a, Sp, Dp, R(cp.reg_c));
+    } else if constexpr (COLL == COLL_SMAGORINSKY) {
+      smagorinsky_relax<S, R>(f, feq0, rho, a, Sp, Dp, R(cp.smag_tau), R(cp.smag_nu), R(cp.smag_c2));
     } else {
       kbc_relax<S, R>(f, feq0, a, Sp, Dp, R(cp.beta), R(cp.inv_beta));
     }

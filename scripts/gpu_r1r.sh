@@ -1,3 +1,4 @@
-mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -q 2>&1 | tail -25
-timeout 600 python scripts/bench_configs.py --only=cfg3 --only="stock" --only="cfg2 TGV3D D3Q19 bgk" | cut -c1-230
+set -x
+timeout 1200 python -m pytest tests/test_gpu_parity.py -x -q 2>&1 | tail -5
+timeout 300 python scripts/bench_configs.py --quick --only=rank3 2>&1 | tail -4
+for v in 2 4; do LB_VEC=$v timeout 300 python scripts/bench_configs.py --quick "--only=rank3 TGV3D D3Q19" 2>&1 | tail -2; done

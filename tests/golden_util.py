@@ -32,6 +32,8 @@ def collision_params(meta):
         return {}
     if c == "trt":
         return dict(tau=meta["tau"], tau_minus=meta["tau_minus"])
+    if c == "smagorinsky":   # make_golden_rank3.py stores the Smagorinsky constant in the tau_minus slot
+        return dict(tau=meta["tau"], smagorinsky_constant=meta["tau_minus"])
     return dict(tau=meta["tau"])
 
 

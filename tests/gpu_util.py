@@ -96,6 +96,13 @@ def make_collision(meta):
         k.tau = meta["tau"]
         k.beta = 1. / (2 * meta["tau"])      # the golden meta stores the tau the reference used
         return k
+    if c == "regularized":
+        r = lt.RegularizedCollision()
+        r.tau = meta["tau"]                  # as above: the tau the reference read from its units
+        r._bound = True
+        return r
+    if c == "smagorinsky":
+        return lt.SmagorinskyCollision(tau=meta["tau"], smagorinsky_constant=meta["tau_minus"])
     raise ValueError(c)
 
 

@@ -14,6 +14,7 @@ template <class S, typename T, typename R, int COLL>
 static void run(T* f, long n, const double* cpd) {
   CollisionParams<T> cp;
   cp.omega = T(cpd[0]); cp.inv_2tau_p = T(cpd[1]); cp.inv_2tau_m = T(cpd[2]); cp.beta = T(cpd[3]); cp.inv_beta = T(cpd[4]);
+  cp.reg_c = T(cpd[5]); cp.smag_tau = T(cpd[6]); cp.smag_nu = T(cpd[7]); cp.smag_c2 = T(cpd[8]);
   constexpr int L = ValueTraits<R>::lanes;
   long i = 0;
   for (; i + L <= n; i += L) {
@@ -44,6 +45,8 @@ static int by_coll(int coll, T* f, long n, const double* cp) {
     case COLL_KBC:
       if constexpr (S::ID != 1) { run<S, T, R, COLL_KBC>(f, n, cp); return 0; }
       return 1;
+    case COLL_REGULARIZED: run<S, T, R, COLL_REGULARIZED>(f, n, cp); return 0;
+    case COLL_SMAGORINSKY: run<S, T, R, COLL_SMAGORINSKY>(f, n, cp); return 0;
   }
   return 1;
 }

@@ -13,7 +13,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 STENCIL_ID = {"D2Q9": 0, "D3Q19": 1, "D3Q27": 2}
-COLL_ID = {"none": 0, "bgk": 1, "trt": 2, "kbc": 3}
+COLL_ID = {"none": 0, "bgk": 1, "trt": 2, "kbc": 3, "regularized": 4, "smagorinsky": 5}
 
 
 class HostEmul:
@@ -30,8 +30,9 @@ class HostEmul:
 
     @staticmethod
     def params(collision, tau=None, tau_minus=1.0):
-        """the five scalars of lb::CollisionParams, as lettuce_b200/_native.py derives them"""
-        cp = (C.c_double * 5)()
+        """the scalars of lb::CollisionParams, as lb_capi.cu make_cp derives them (for 'smagorinsky'
+        tau_minus carries the Smagorinsky constant, as in lb_desc)"""
+        cp = (C.c_double * 9)()
         if collision == "none":
             return cp
         cp[0] = 1.0 / tau
@@ -40,6 +41,10 @@ class HostEmul:
         beta = 1.0 / (2.0 * tau)
         cp[3] = beta
         cp[4] = 1.0 / beta
+        cp[5] = 1.0 - 1.0 / tau
+        cp[6] = tau
+        cp[7] = (tau - 0.5) / 3.0
+        cp[8] = tau_minus * tau_minus
         return cp
 
     def collide(self, stencil, f, collision, cp, packed=False):

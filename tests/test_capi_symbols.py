@@ -55,6 +55,32 @@ def test_descriptor_validation_needs_no_gpu():
     assert L.lb_step(neg, fl, 1, None) == -1
     with pytest.raises(nat.NativeError):
         nat.make_desc("D3Q15", torch.float32, [8, 8, 8])
+    # rank-3 collisions: ids 4 and 5 are known, 6 is not; the Smagorinsky constant rides in tau_minus
+    for cid in (nat.LB_COLL_REGULARIZED, nat.LB_COLL_SMAGORINSKY):
+        assert L.lb_step(nat.make_desc("D3Q19", torch.float32, [8, 8, 8], cid, 0.6, 0.17), fl, 1, None) == -1
+        assert b"null population buffer" in L.lb_last_error()
+    assert L.lb_step(nat.make_desc("D3Q19", torch.float32, [8, 8, 8], 6, 0.6), fl, 1, None) == -1
+    assert b"unknown collision" in L.lb_last_error()
+    assert L.lb_step(nat.make_desc("D3Q19", torch.float32, [8, 8, 8], nat.LB_COLL_SMAGORINSKY, 0.6, -0.1), fl, 1, None) == -1
+    assert b"Smagorinsky" in L.lb_last_error()
+
+
+def test_rank3_collision_descriptors():
+    """host mirror of RegularizedCollision / SmagorinskyCollision (regularized_collision.py:14-19,
+    smagorinsky_collision.py:13-18): constructor signatures and what reaches the kernel"""
+    import torch
+    import lettuce_b200 as lt
+    from lettuce_b200 import _native as nat
+    ctx = lt.Context(device="cpu", dtype=torch.float64, use_native=False)
+    flow = lt.TaylorGreenVortex(ctx, resolution=16, reynolds_number=10, mach_number=0.05, stencil=lt.D2Q9)
+    reg = lt.RegularizedCollision(tau=99.0)                    # ignored, as in the reference
+    d = reg.native_descriptor(flow)
+    assert d == dict(collision=nat.LB_COLL_REGULARIZED, tau=float(flow.units.relaxation_parameter_lu))
+    smag = lt.SmagorinskyCollision(0.6)
+    assert smag.constant == 0.17 and smag.iterations == 2
+    assert smag.native_descriptor(flow) == dict(collision=nat.LB_COLL_SMAGORINSKY, tau=0.6, tau_minus=0.17)
+    with pytest.raises(NotImplementedError):
+        lt.SmagorinskyCollision(0.6, force=object())
 
 
 def test_no_cpu_fallback():

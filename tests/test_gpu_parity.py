@@ -158,8 +158,9 @@ def _build_pair(stencil, dtype, res, collision, params, seed, masks=False, amp=0
         obnds = [orc.OracleBoundary("bounce_back", solid),
                  orc.OracleBoundary("equilibrium", eqm, rho=rho_b, u=u_b)]
         ncm, nsm = orc.build_masks(lat, res, obnds, [smask])
+    second = params.get("tau_minus", params.get("smagorinsky_constant", 1.0))   # the lb_desc.tau_minus slot
     sim = lt.Simulation(flow, gu.make_collision(dict(collision=collision, tau=params.get("tau"),
-                                                     tau_minus=params.get("tau_minus", 1.0))), [])
+                                                     tau_minus=second)), [])
     return sim, lat, f0, ncm, nsm, obnds
 
 
@@ -264,6 +265,46 @@ def test_collisions_vs_oracle(stencil, collision, dtype, masks):
         err = rel_err(out, ref)
         print(f"rel_err {stencil} {collision} {dtype} {res} masks={masks}: {err:.3e}")
         assert err <= TOL[dtype], f"{stencil} {collision} {dtype} {res}"
+
+
+@pytest.mark.parametrize("stencil", list(SHAPES))
+@pytest.mark.parametrize("collision", ["regularized", "smagorinsky"])
+@pytest.mark.parametrize("dtype", ["f32", "f64"])
+@pytest.mark.parametrize("masks", [False, "nsm"])
+def test_rank3_collisions_vs_oracle(stencil, collision, dtype, masks):
+    """RegularizedCollision / SmagorinskyCollision on seeded fields, all vector widths"""
+    params = dict(tau=0.62)
+    if collision == "smagorinsky":
+        params["smagorinsky_constant"] = 0.3
+    for k, res in enumerate(SHAPES[stencil][:3]):
+        out, ref = _run_pair(stencil, dtype, res, collision, params, 10, seed=300 + k, masks=masks, amp=0.02)
+        err = rel_err(out, ref)
+        print(f"rel_err {stencil} {collision} {dtype} {res} masks={masks}: {err:.3e}")
+        assert err <= TOL[dtype], f"{stencil} {collision} {dtype} {res}"
+
+
+def test_smagorinsky_reduces_to_bgk_without_constant():
+    """C = 0: tau_eff == tau, the update is BGK's (same formula, one division more)"""
+    out, ref = _run_pair("D3Q19", "f64", [4, 6, 32], "smagorinsky", dict(tau=0.7, smagorinsky_constant=0.0), 5,
+                         seed=11, amp=0.05)
+    bgk, _ = _run_pair("D3Q19", "f64", [4, 6, 32], "bgk", dict(tau=0.7), 5, seed=11, amp=0.05)
+    assert rel_err(out, ref) <= TOL["f64"] and rel_err(out, bgk) <= 1e-13
+
+
+def test_rank3_collisions_conserve_mass_and_momentum():
+    """the reference's conservation fixture (tests/collision, fix_conserving_collision): collision
+    operators called on their own leave rho and j unchanged"""
+    gu, lt = _gpu()
+    ctx = lt.Context(device="cuda", dtype=torch.float64, use_native=True)
+    for st in (lt.D2Q9, lt.D3Q19, lt.D3Q27):
+        flow = lt.TaylorGreenVortex(ctx, resolution=16, reynolds_number=100, mach_number=0.05, stencil=st)
+        g = torch.Generator(device="cuda").manual_seed(3)
+        flow.f = flow.f * (1.0 + 0.05 * torch.rand(flow.f.shape, device="cuda", dtype=torch.float64, generator=g))
+        for coll in (lt.RegularizedCollision(), lt.SmagorinskyCollision(tau=0.6, smagorinsky_constant=0.2)):
+            rho0, j0 = flow.rho().clone(), flow.j().clone()
+            flow.f = coll(flow)
+            assert torch.allclose(flow.rho(), rho0, rtol=0, atol=1e-13)
+            assert torch.allclose(flow.j(), j0, rtol=0, atol=1e-13)
 
 
 # ------------------------------------------------------------------------------------------

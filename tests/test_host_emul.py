@@ -38,13 +38,13 @@ def test_device_arithmetic_vs_golden(em, name):
     meta = case["meta"]
     e = orc.STENCILS[meta["stencil"]]["e"]
     p = collision_params(meta)
-    out = em.run(meta["stencil"], e, case["f0"], meta["n_steps"], meta["collision"], p.get("tau"),
-                 p.get("tau_minus", 1.0))
+    second = p.get("tau_minus", p.get("smagorinsky_constant", 1.0))   # lb_desc.tau_minus slot
+    out = em.run(meta["stencil"], e, case["f0"], meta["n_steps"], meta["collision"], p.get("tau"), second)
     assert rel_err(out, case["f_out"]) <= TOL[meta["dtype"]]
     if meta["dtype"] == "f32":
         # two nodes per packed F2 value: same bits as one node per float
         packed = em.run(meta["stencil"], e, case["f0"], meta["n_steps"], meta["collision"], p.get("tau"),
-                        p.get("tau_minus", 1.0), packed=True)
+                        second, packed=True)
         assert np.array_equal(packed, out)
 
 
