@@ -48,6 +48,7 @@ extern "C" {
 
 enum { LB_D2Q9 = 0, LB_D3Q19 = 1, LB_D3Q27 = 2 };                     /* lb_desc.stencil   */
 enum { LB_F32 = 0, LB_F64 = 1 };                                      /* lb_desc.dtype     */
+enum { LB_FORCE_NONE = 0, LB_FORCE_GUO = 1, LB_FORCE_SHAN_CHEN = 2 };  /* lb_desc.force     */
 enum { LB_COLL_NONE = 0, LB_COLL_BGK = 1, LB_COLL_TRT = 2, LB_COLL_KBC = 3,
        LB_COLL_REGULARIZED = 4, /* regularized_collision.py:17-44; tau as the reference reads it from the units */
        LB_COLL_SMAGORINSKY = 5  /* smagorinsky_collision.py:19-36; lb_desc.tau_minus carries the Smagorinsky
@@ -81,6 +82,16 @@ typedef struct lb_desc {
   int64_t dims[3];     /* resolution, dims[ndim-1] is the contiguous axis */
   double tau;          /* BGK: tau; TRT: tau_plus; KBC: tau (beta = 1/(2 tau)) */
   double tau_minus;    /* TRT: tau_minus (trt_collision.py:12-14); Smagorinsky: the constant (:13) */
+  /* Forcing scheme of BGKCollision(tau, force) (bgk_collision.py:17-22), LB_COLL_BGK only:
+   *   u = j / rho + scale * acceleration / rho,   f - (f - feq(rho, u)) / tau + S
+   *   LB_FORCE_GUO       scale = 1/2,       S_q = (1 - 1/(2 force_tau)) w_q ((e_q - u)/cs^2 + (e_q.u) e_q/cs^4) . a
+   *                                         (ext/_force/guo.py:16-37)
+   *   LB_FORCE_SHAN_CHEN scale = force_tau, S = 0                   (ext/_force/shan_chen.py:13-23)
+   * acceleration: constant vector in lattice units, lattice axes; force_tau: the tau given to the Force. */
+  double acceleration[3];
+  double force_tau;
+  int32_t force;       /* LB_FORCE_NONE | LB_FORCE_GUO | LB_FORCE_SHAN_CHEN */
+  int32_t reserved;
 } lb_desc;
 
 /* One entry per boundary object, in the order lettuce sorted them

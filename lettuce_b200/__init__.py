@@ -11,6 +11,7 @@ from ._unit import *
 from ._flow import *
 from ._equilibrium import *
 from ._collision import *
+from ._force import *
 from ._boundary import *
 from ._flows import *
 from ._reporter import *

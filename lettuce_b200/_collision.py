@@ -40,7 +40,8 @@ class Collision(ABC):
             raise nat.NativeError("lettuce_b200 collisions run on CUDA tensors only (no CPU fallback)")
         d = self.native_descriptor(flow)
         desc = nat.make_desc(type(flow.stencil).__name__, f.dtype, flow.resolution, d['collision'],
-                             d.get('tau', 1.0), d.get('tau_minus', 1.0))
+                             d.get('tau', 1.0), d.get('tau_minus', 1.0), d.get('force', nat.LB_FORCE_NONE),
+                             d.get('acceleration', ()), d.get('force_tau', 1.0))
         f = f.contiguous()
         out = torch.empty_like(f)
         with torch.cuda.device(f.device):
@@ -59,17 +60,21 @@ class NoCollision(Collision):
 
 class BGKCollision(Collision):
     def __init__(self, tau, force=None):
-        if force is not None:
-            raise NotImplementedError("forcing schemes are outside the hot-path scope (SURVEY.md "
-                                      "section 2 row 7); the reference's native path has none either")
+        if force is not None and not hasattr(force, 'native_descriptor'):
+            raise NotImplementedError(f"{type(force).__name__} has no native kernel (Guo and ShanChen do)")
         self.tau = tau
         self.force = force
 
     def name(self):
+        if self.force is not None:
+            return f"{self.__class__.__name__}_{self.force.__class__.__name__}"
         return self.__class__.__name__
 
     def native_descriptor(self, flow):
-        return dict(collision=nat.LB_COLL_BGK, tau=float(self.tau))
+        d = dict(collision=nat.LB_COLL_BGK, tau=float(self.tau))
+        if self.force is not None:
+            d.update(self.force.native_descriptor())
+        return d
 
 
 class TRTCollision(Collision):

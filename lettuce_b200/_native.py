@@ -18,6 +18,7 @@ LB_D2Q9, LB_D3Q19, LB_D3Q27 = 0, 1, 2
 LB_F32, LB_F64 = 0, 1
 LB_COLL_NONE, LB_COLL_BGK, LB_COLL_TRT, LB_COLL_KBC = 0, 1, 2, 3
 LB_COLL_REGULARIZED, LB_COLL_SMAGORINSKY = 4, 5
+LB_FORCE_NONE, LB_FORCE_GUO, LB_FORCE_SHAN_CHEN = 0, 1, 2
 LB_BND_BOUNCE_BACK, LB_BND_EQUILIBRIUM, LB_BND_ABB_OUTLET, LB_BND_EQ_OUTLET_P = 1, 2, 3, 4
 LB_OBS_ENERGY, LB_OBS_MAXU2, LB_OBS_MASS, LB_OBS_ENSTROPHY, LB_OBS_COUNT = 0, 1, 2, 3, 4
 LB_MAX_BOUNDARIES = 8
@@ -47,7 +48,8 @@ class NativeError(RuntimeError):
 class LbDesc(C.Structure):
     _fields_ = [("stencil", C.c_int32), ("dtype", C.c_int32), ("collision", C.c_int32),
                 ("ndim", C.c_int32), ("dims", C.c_int64 * 3), ("tau", C.c_double),
-                ("tau_minus", C.c_double)]
+                ("tau_minus", C.c_double), ("acceleration", C.c_double * 3), ("force_tau", C.c_double),
+                ("force", C.c_int32), ("reserved", C.c_int32)]
 
 
 class LbBoundary(C.Structure):
@@ -133,7 +135,8 @@ def check(rc: int):
 
 
 def make_desc(stencil_name: str, dtype: torch.dtype, resolution: Sequence[int], collision: int = LB_COLL_NONE,
-              tau: float = 1.0, tau_minus: float = 1.0) -> LbDesc:
+              tau: float = 1.0, tau_minus: float = 1.0, force: int = LB_FORCE_NONE,
+              acceleration: Sequence[float] = (), force_tau: float = 1.0) -> LbDesc:
     if stencil_name not in STENCIL_IDS:
         raise NativeError(f"stencil {stencil_name} has no native kernel (D2Q9, D3Q19, D3Q27 only)")
     if dtype not in DTYPE_IDS:
@@ -144,6 +147,11 @@ def make_desc(stencil_name: str, dtype: torch.dtype, resolution: Sequence[int], 
     for i in range(3):
         d.dims[i] = int(resolution[i]) if i < len(resolution) else 1
     d.tau, d.tau_minus = float(tau), float(tau_minus)
+    d.force, d.force_tau = int(force), float(force_tau)
+    if force != LB_FORCE_NONE and len(acceleration) != len(resolution):
+        raise NativeError(f"acceleration has {len(acceleration)} components on a {len(resolution)}-D lattice")
+    for i, a in enumerate(acceleration):
+        d.acceleration[i] = float(a)
     return d
 
 

@@ -63,6 +63,12 @@ int check_desc(const lb_desc* d, Geometry* g) {
   if (d->collision == LB_COLL_TRT && !(d->tau_minus > 0.0)) return fail(LB_EINVAL, "tau_minus must be > 0");
   if (d->collision == LB_COLL_SMAGORINSKY && !(d->tau_minus >= 0.0))
     return fail(LB_EINVAL, "the Smagorinsky constant (tau_minus) must be >= 0");
+  if (d->force < LB_FORCE_NONE || d->force > LB_FORCE_SHAN_CHEN) return fail(LB_EINVAL, "unknown force id %d", d->force);
+  if (d->force != LB_FORCE_NONE) {
+    if (d->collision != LB_COLL_BGK)
+      return fail(LB_EUNSUPPORTED, "forcing schemes are implemented for BGKCollision only (collision id %d)", d->collision);
+    if (!(d->force_tau > 0.0)) return fail(LB_EINVAL, "force_tau must be > 0");
+  }
   g->q = q;
   g->d = dim;
   if (dim == 2) { g->nx = 1; g->ny = (unsigned)d->dims[0]; g->nz = (unsigned)d->dims[1]; }
@@ -85,6 +91,19 @@ lb::CollisionParams<T> make_cp(const lb_desc* d) {
   cp.smag_tau = T(d->tau);
   cp.smag_nu = T((d->tau - 0.5) / 3.0);
   cp.smag_c2 = T(d->tau_minus * d->tau_minus);   // LB_COLL_SMAGORINSKY: tau_minus = the Smagorinsky constant
+  if (d->force != LB_FORCE_NONE) {
+    // ueq_scaling_factor (guo.py:35-37: 0.5; shan_chen.py:21-23: tau * 1) times the acceleration, and the
+    // prefactor of the source term (guo.py:29: 1 - 1 / (2 tau); shan_chen.py:13-14: no source);
+    // lattice axes -> kernel axes (2-D runs as X = 1)
+    const double scale = d->force == LB_FORCE_GUO ? 0.5 : d->force_tau * 1;
+    const int dim = stencil_d(d->stencil);
+    for (int a = 0; a < dim; ++a) {
+      const int ka = (dim == 2) ? a + 1 : a;
+      cp.force_a[ka] = T(d->acceleration[a]);
+      cp.force_ueq[ka] = T(scale * d->acceleration[a]);
+    }
+    cp.force_src = d->force == LB_FORCE_GUO ? T(1 - 1 / (2 * d->force_tau)) : T(0);
+  }
   return cp;
 }
 
@@ -113,6 +132,7 @@ int vector_width(const lb_desc* d, const Geometry& g, const void* a, const void*
   // HBM roofline against 0.82 / 0.91 with four nodes), fp64 KBC one node per thread
   if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_KBC) cap = (sizeof(T) == 4) ? 2 : 1;
   if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_TRT && sizeof(T) == 4) cap = 2;
+  if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_SMAGORINSKY && sizeof(T) == 4) cap = 2;   // measured 0.96 vs 0.91
   static const char* env = getenv("LB_VEC");
   if (env && atoi(env) >= 1) cap = atoi(env) < widest ? atoi(env) : widest;
   for (int v = cap; v > 1; v >>= 1)
@@ -223,7 +243,7 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   if (p.sbits && !p.ncm) return fail(LB_EINVAL, "streaming_bits requires no_collision_mask (lettuce creates both, _simulation.py:71-75)");
 
   lb::StepConfig c{};
-  c.collision = d->collision;
+  c.collision = (d->collision == LB_COLL_BGK && d->force != LB_FORCE_NONE) ? int(lb::COLL_BGK_FORCE) : d->collision;
   c.mode = p.sbits ? lb::MODE_NCM_SBITS : (p.ncm ? lb::MODE_NCM : lb::MODE_PLAIN);
   c.stream = do_stream;
   c.halo = fl->halo != nullptr;

@@ -1,0 +1,5 @@
+// explicit instantiation of the step kernels for D2Q9 f32, collision BGK with a forcing scheme
+#include "lb_kernels.cuh"
+namespace lb {
+LB_INSTANTIATE_COLL(D2Q9, float, 6)
+}

@@ -910,6 +910,7 @@ cudaError_t launch_step(StepConfig& c, const StepParams<T>& p, cudaStream_t st) 
       else return cudaErrorNotSupported;
     case COLL_REGULARIZED: return launch_step_coll<S, T, COLL_REGULARIZED>(c, p, st);
     case COLL_SMAGORINSKY: return launch_step_coll<S, T, COLL_SMAGORINSKY>(c, p, st);
+    case COLL_BGK_FORCE: return launch_step_coll<S, T, COLL_BGK_FORCE>(c, p, st);
   }
   return cudaErrorInvalidValue;
 }

@@ -36,6 +36,9 @@ struct CollisionParams {
   T smag_tau;     // Smagorinsky: tau, nu = (tau - 0.5) / 3.0, constant ** 2  (smagorinsky_collision.py:27-33)
   T smag_nu;
   T smag_c2;
+  T force_a[3];   // BGK + force: acceleration (kernel axes), scale * acceleration of u_eq, source prefactor
+  T force_ueq[3];
+  T force_src;
 };
 
 // ---------------------------------------------------------------------------------------
@@ -221,7 +224,8 @@ __host__ __device__ __forceinline__ void equilibrium(R rho, const R (&u)[3], R (
   });
 }
 
-enum { COLL_NONE = 0, COLL_BGK = 1, COLL_TRT = 2, COLL_KBC = 3, COLL_REGULARIZED = 4, COLL_SMAGORINSKY = 5 };
+enum { COLL_NONE = 0, COLL_BGK = 1, COLL_TRT = 2, COLL_KBC = 3, COLL_REGULARIZED = 4, COLL_SMAGORINSKY = 5,
+       COLL_BGK_FORCE = 6 };   // internal: LB_COLL_BGK with lb_desc.force set
 
 // Second moments of the non-equilibrium part, Pi_AB = sum_q e_A e_B (f_q - feq_q)  (Flow.shear_tensor of
 // f - feq, _flow.py:202-208): population 0 does not contribute and an opposite pair contributes through
@@ -421,12 +425,52 @@ __host__ __device__ __forceinline__ void kbc_relax(R (&f)[S::Q], R feq0, const R
   });
 }
 
+// ---------------------------------------------------------------------------------------
+// BGK with a forcing scheme (bgk_collision.py:17-22; ext/_force/guo.py:16-37, shan_chen.py:13-23):
+//   u = j / rho + scale a / rho;   f - (f - feq(rho, u)) / tau + S,
+//   Guo:  S_q = c w_q ((e_q - u) / cs^2 + (e_q.u) e_q / cs^4) . a,  c = 1 - 1/(2 tau_force);  Shan-Chen: S = 0.
+// Even / odd in e:  S_q = c (E_p + O_p),  S_o = c (E_p - O_p)  with  E_p = w ((e.U)(e.A) - u.A),
+// O_p = w (e.A),  U = u / cs^2,  A = a / cs^2;  S_0 = -c w_0 (u.A).
+// ---------------------------------------------------------------------------------------
+template <class S, typename R, typename T>
+__host__ __device__ __forceinline__ void bgk_force_relax(R (&f)[S::Q], R rho, const R (&u)[3],
+                                                         const CollisionParams<T>& cp) {
+  const R inv_cs2 = R(1.0 / LB_CS2);
+  R uf[3], U[3], A[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    uf[c] = (S::D == 3 || c > 0) ? u[c] + div_(R(cp.force_ueq[c]), rho) : R(0);
+    U[c] = uf[c] * inv_cs2;
+    A[c] = R(cp.force_a[c]) * inv_cs2;
+  }
+  R feq0, Sp[N_SLOTS], Dp[N_SLOTS];
+  equilibrium_pairs<S, R>(rho, uf, feq0, Sp, Dp);
+  R ua = fma_(uf[2], A[2], uf[1] * A[1]);
+  if constexpr (S::D == 3) ua = fma_(uf[0], A[0], ua);
+  const R om = R(cp.omega), c = R(cp.force_src);
+  f[0] = fma_(om, feq0 - f[0], f[0]) - c * (R(S::w(0)) * ua);
+  static_for<N_SLOTS>([&](auto sc) {
+    constexpr int s = decltype(sc)::value;
+    if constexpr (has_slot<S, s>) {
+      constexpr int q = pair_q<S>(s), o = S::opp(q);
+      const R w = R(S::w(q));
+      const R ea = slot_dot<s, R>(A);
+      const R even = w * fma_(slot_dot<s, R>(U), ea, -ua);
+      const R odd = w * ea;
+      f[q] = fma_(om, (Sp[s] + Dp[s]) - f[q], f[q]) + c * (even + odd);
+      f[o] = fma_(om, (Sp[s] - Dp[s]) - f[o], f[o]) + c * (even - odd);
+    }
+  });
+}
+
 // f <- collision(f), given the pair sums / differences and the moments of the incoming f
 template <class S, typename R, int COLL, typename T>
 __host__ __device__ __forceinline__ void collide_node(R (&f)[S::Q], const R (&a)[N_SLOTS], const R (&b)[N_SLOTS],
                                                       R rho, const R (&u)[3], const CollisionParams<T>& cp) {
   if constexpr (COLL == COLL_NONE) {
     return;  // no_collision.py:9-11
+  } else if constexpr (COLL == COLL_BGK_FORCE) {
+    bgk_force_relax<S, R, T>(f, rho, u, cp);
   } else {
     R feq0, Sp[N_SLOTS], Dp[N_SLOTS];
     equilibrium_pairs<S, R>(rho, u, feq0, Sp, Dp);

@@ -67,7 +67,8 @@ def tgv(res, stencil, dtype, collision, re=1600, ma=0.1, reporters=None, steps=1
     tau = flow.units.relaxation_parameter_lu
     coll = {"bgk": lambda: lt.BGKCollision(tau), "trt": lambda: lt.TRTCollision(tau), "kbc": lambda: lt.KBCCollision(),
             "none": lambda: lt.NoCollision(), "regularized": lambda: lt.RegularizedCollision(),
-            "smagorinsky": lambda: lt.SmagorinskyCollision(tau)}[collision]()
+            "smagorinsky": lambda: lt.SmagorinskyCollision(tau),
+            "bgk_guo": lambda: lt.BGKCollision(tau, force=lt.Guo(flow, tau, [1e-6] * flow.stencil.d))}[collision]()
     reps = reporters(flow) if reporters else []
     sim = lt.Simulation(flow, coll, reps)
     return flow, sim, timed(sim, steps)
@@ -97,6 +98,8 @@ def main():
     for coll in ("regularized", "smagorinsky"):
         tgv_case(f"rank3 TGV3D D3Q19 {coll} f32 256^3", 256, lt.D3Q19, torch.float32, coll, S)
     tgv_case("rank3 TGV3D D3Q27 smagorinsky f32 256^3", 256, lt.D3Q27, torch.float32, "smagorinsky", S)
+    tgv_case("rank3 TGV3D D3Q27 regularized f32 256^3", 256, lt.D3Q27, torch.float32, "regularized", S)
+    tgv_case("rank3 TGV3D D3Q19 bgk+guo f32 256^3", 256, lt.D3Q19, torch.float32, "bgk_guo", S)
     tgv_case("TGV3D D3Q19 bgk f64 256^3", 256, lt.D3Q19, torch.float64, "bgk", S)
     for coll in ("bgk", "trt", "kbc"):
         tgv_case(f"TGV3D D3Q27 {coll} f32 256^3", 256, lt.D3Q27, torch.float32, coll, S)

@@ -34,6 +34,8 @@ def collision_params(meta):
         return dict(tau=meta["tau"], tau_minus=meta["tau_minus"])
     if c == "smagorinsky":   # make_golden_rank3.py stores the Smagorinsky constant in the tau_minus slot
         return dict(tau=meta["tau"], smagorinsky_constant=meta["tau_minus"])
+    if c == "bgk" and meta.get("force"):   # BGKCollision(tau, force=Guo | ShanChen(flow, tau, acceleration))
+        return dict(tau=meta["tau"], force=meta["force"])
     return dict(tau=meta["tau"])
 
 

@@ -83,12 +83,16 @@ class TaggedEqOutletP(lt.EquilibriumOutletP):
         return f"boundary_{self._tag:03d}"
 
 
-def make_collision(meta):
+def make_collision(meta, flow=None):
     c = meta["collision"]
     if c == "none":
         return lt.NoCollision()
     if c == "bgk":
-        return lt.BGKCollision(tau=meta["tau"])
+        force = None
+        if meta.get("force"):
+            fo = meta["force"]
+            force = (lt.Guo if fo["kind"] == "guo" else lt.ShanChen)(flow, fo["tau"], fo["acceleration"])
+        return lt.BGKCollision(tau=meta["tau"], force=force)
     if c == "trt":
         return lt.TRTCollision(tau=meta["tau"], tau_minus=meta["tau_minus"])
     if c == "kbc":
@@ -133,5 +137,5 @@ def simulation_from_case(case, reporters=(), device="cuda"):
                     mask = torch.from_numpy(case[f"b{i}_mask"])
                     this_nsm = None
                 flow.boundaries.append(TaggedBounceBack(mask, nsm=this_nsm, tag=i))
-    sim = lt.Simulation(flow, make_collision(meta), list(reporters))
+    sim = lt.Simulation(flow, make_collision(meta, flow), list(reporters))
     return sim

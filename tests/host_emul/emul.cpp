@@ -15,6 +15,8 @@ static void run(T* f, long n, const double* cpd) {
   CollisionParams<T> cp;
   cp.omega = T(cpd[0]); cp.inv_2tau_p = T(cpd[1]); cp.inv_2tau_m = T(cpd[2]); cp.beta = T(cpd[3]); cp.inv_beta = T(cpd[4]);
   cp.reg_c = T(cpd[5]); cp.smag_tau = T(cpd[6]); cp.smag_nu = T(cpd[7]); cp.smag_c2 = T(cpd[8]);
+  for (int c = 0; c < 3; ++c) { cp.force_a[c] = T(cpd[9 + c]); cp.force_ueq[c] = T(cpd[12 + c]); }
+  cp.force_src = T(cpd[15]);
   constexpr int L = ValueTraits<R>::lanes;
   long i = 0;
   for (; i + L <= n; i += L) {
@@ -47,6 +49,7 @@ static int by_coll(int coll, T* f, long n, const double* cp) {
       return 1;
     case COLL_REGULARIZED: run<S, T, R, COLL_REGULARIZED>(f, n, cp); return 0;
     case COLL_SMAGORINSKY: run<S, T, R, COLL_SMAGORINSKY>(f, n, cp); return 0;
+    case COLL_BGK_FORCE: run<S, T, R, COLL_BGK_FORCE>(f, n, cp); return 0;
   }
   return 1;
 }

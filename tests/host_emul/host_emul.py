@@ -13,7 +13,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 STENCIL_ID = {"D2Q9": 0, "D3Q19": 1, "D3Q27": 2}
-COLL_ID = {"none": 0, "bgk": 1, "trt": 2, "kbc": 3, "regularized": 4, "smagorinsky": 5}
+COLL_ID = {"none": 0, "bgk": 1, "trt": 2, "kbc": 3, "regularized": 4, "smagorinsky": 5, "bgk_force": 6}
 
 
 class HostEmul:
@@ -29,10 +29,10 @@ class HostEmul:
         self.lib.emul_moments.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p]
 
     @staticmethod
-    def params(collision, tau=None, tau_minus=1.0):
+    def params(collision, tau=None, tau_minus=1.0, force=None):
         """the scalars of lb::CollisionParams, as lb_capi.cu make_cp derives them (for 'smagorinsky'
         tau_minus carries the Smagorinsky constant, as in lb_desc)"""
-        cp = (C.c_double * 9)()
+        cp = (C.c_double * 16)()
         if collision == "none":
             return cp
         cp[0] = 1.0 / tau
@@ -45,6 +45,14 @@ class HostEmul:
         cp[6] = tau
         cp[7] = (tau - 0.5) / 3.0
         cp[8] = tau_minus * tau_minus
+        if force is not None:   # dict(kind='guo'|'shan_chen', tau=..., acceleration=[...]) in LATTICE axes
+            acc = [float(a) for a in force["acceleration"]]
+            acc = [0.0] + acc if len(acc) == 2 else acc          # kernel axes: a 2-D lattice runs as X = 1
+            scale = 0.5 if force["kind"] == "guo" else force["tau"] * 1
+            for c in range(3):
+                cp[9 + c] = acc[c]
+                cp[12 + c] = scale * acc[c]
+            cp[15] = 1 - 1 / (2 * force["tau"]) if force["kind"] == "guo" else 0.0
         return cp
 
     def collide(self, stencil, f, collision, cp, packed=False):
@@ -58,8 +66,11 @@ class HostEmul:
         assert rc == 0
         return out
 
-    def run(self, stencil, e, f0, n_steps, collision, tau=None, tau_minus=1.0, packed=False):
-        cp = self.params(collision, tau, tau_minus)
+    def run(self, stencil, e, f0, n_steps, collision, tau=None, tau_minus=1.0, packed=False, force=None):
+        cp = self.params(collision, tau, tau_minus, force)
+        if force is not None:
+            assert collision == "bgk"
+            collision = "bgk_force"
         f = np.ascontiguousarray(f0).copy()
         axes = tuple(range(f.ndim - 1))
         for _ in range(n_steps):

@@ -81,6 +81,28 @@ def test_rank3_collision_descriptors():
     assert smag.native_descriptor(flow) == dict(collision=nat.LB_COLL_SMAGORINSKY, tau=0.6, tau_minus=0.17)
     with pytest.raises(NotImplementedError):
         lt.SmagorinskyCollision(0.6, force=object())
+    # forcing schemes (ext/_force/guo.py, shan_chen.py): constructor (flow, tau, acceleration)
+    guo = lt.Guo(flow, 0.7, [1e-4, 0.0])
+    sc = lt.ShanChen(flow, 0.7, [1e-4, 0.0])
+    assert guo.ueq_scaling_factor == 0.5 and sc.ueq_scaling_factor == 0.7
+    bgk = lt.BGKCollision(0.6, force=guo)
+    assert bgk.name() == "BGKCollision_Guo"
+    assert bgk.native_descriptor(flow) == dict(collision=nat.LB_COLL_BGK, tau=0.6, force=nat.LB_FORCE_GUO,
+                                               force_tau=0.7, acceleration=[1e-4, 0.0])
+    assert lt.BGKCollision(0.6, force=sc).native_descriptor(flow)["force"] == nat.LB_FORCE_SHAN_CHEN
+    with pytest.raises(NotImplementedError):
+        lt.Guo(flow, 0.7, [1e-4, 0.0, 0.0])                    # wrong number of components
+    with pytest.raises(NotImplementedError):
+        lt.BGKCollision(0.6, force=object())
+    # the C ABI refuses a force on any other collision, and bad force ids
+    L = nat.lib()
+    fl = nat.LbFields()
+    d = nat.make_desc("D2Q9", torch.float64, [16, 16], nat.LB_COLL_TRT, 0.6, 1.0, nat.LB_FORCE_GUO, [1e-4, 0.0], 0.7)
+    assert L.lb_step(d, fl, 1, None) == -3 and b"BGKCollision only" in L.lb_last_error()
+    d = nat.make_desc("D2Q9", torch.float64, [16, 16], nat.LB_COLL_BGK, 0.6, 1.0, 7, [1e-4, 0.0], 0.7)
+    assert L.lb_step(d, fl, 1, None) == -1 and b"unknown force" in L.lb_last_error()
+    with pytest.raises(nat.NativeError):
+        nat.make_desc("D2Q9", torch.float64, [16, 16], nat.LB_COLL_BGK, 0.6, 1.0, nat.LB_FORCE_GUO, [1e-4], 0.7)
 
 
 def test_no_cpu_fallback():

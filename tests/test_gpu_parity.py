@@ -160,7 +160,7 @@ def _build_pair(stencil, dtype, res, collision, params, seed, masks=False, amp=0
         ncm, nsm = orc.build_masks(lat, res, obnds, [smask])
     second = params.get("tau_minus", params.get("smagorinsky_constant", 1.0))   # the lb_desc.tau_minus slot
     sim = lt.Simulation(flow, gu.make_collision(dict(collision=collision, tau=params.get("tau"),
-                                                     tau_minus=second)), [])
+                                                     tau_minus=second, force=params.get("force")), flow), [])
     return sim, lat, f0, ncm, nsm, obnds
 
 
@@ -281,6 +281,38 @@ def test_rank3_collisions_vs_oracle(stencil, collision, dtype, masks):
         err = rel_err(out, ref)
         print(f"rel_err {stencil} {collision} {dtype} {res} masks={masks}: {err:.3e}")
         assert err <= TOL[dtype], f"{stencil} {collision} {dtype} {res}"
+
+
+@pytest.mark.parametrize("stencil", list(SHAPES))
+@pytest.mark.parametrize("kind", ["guo", "shan_chen"])
+@pytest.mark.parametrize("dtype", ["f32", "f64"])
+def test_bgk_with_force_vs_oracle(stencil, kind, dtype):
+    """BGKCollision(tau, force=Guo | ShanChen) on seeded fields with boundaries and streaming masks"""
+    d = 2 if stencil == "D2Q9" else 3
+    force = dict(kind=kind, tau=0.8, acceleration=[1e-3, -2e-3, 5e-4][:d])
+    for k, res in enumerate(SHAPES[stencil][:3]):
+        out, ref = _run_pair(stencil, dtype, res, "bgk", dict(tau=0.62, force=force), 10, seed=400 + k,
+                             masks="nsm" if k == 0 else False, amp=0.02)
+        err = rel_err(out, ref)
+        print(f"rel_err {stencil} bgk+{kind} {dtype} {res}: {err:.3e}")
+        assert err <= TOL[dtype], f"{stencil} {kind} {dtype} {res}"
+
+
+def test_force_adds_momentum():
+    """one BGK + Guo step changes the total momentum by N * rho * a (to round-off) and conserves mass"""
+    gu, lt = _gpu()
+    ctx = lt.Context(device="cuda", dtype=torch.float64, use_native=True)
+    flow = lt.TaylorGreenVortex(ctx, resolution=[32, 32, 32], reynolds_number=100, mach_number=0.05, stencil=lt.D3Q19)
+    a = [1e-4, -2e-4, 3e-4]
+    tau = flow.units.relaxation_parameter_lu
+    sim = lt.Simulation(flow, lt.BGKCollision(tau, force=lt.Guo(flow, tau, a)), [])
+    m0, j0 = flow.rho().sum().item(), flow.j().sum(dim=(1, 2, 3))
+    sim(1)
+    m1, j1 = flow.rho().sum().item(), flow.j().sum(dim=(1, 2, 3))
+    assert abs(m1 - m0) <= 1e-9 * m0
+    # sum_q e_q (f_post - f) = a / (2 tau) [shifted equilibrium] + (1 - 1/(2 tau)) a [source] = a per node
+    want = torch.tensor(a, device="cuda", dtype=torch.float64) * 32 ** 3
+    assert torch.allclose(j1 - j0, want, rtol=1e-6, atol=1e-10)
 
 
 def test_smagorinsky_reduces_to_bgk_without_constant():

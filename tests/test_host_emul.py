@@ -39,12 +39,13 @@ def test_device_arithmetic_vs_golden(em, name):
     e = orc.STENCILS[meta["stencil"]]["e"]
     p = collision_params(meta)
     second = p.get("tau_minus", p.get("smagorinsky_constant", 1.0))   # lb_desc.tau_minus slot
-    out = em.run(meta["stencil"], e, case["f0"], meta["n_steps"], meta["collision"], p.get("tau"), second)
+    out = em.run(meta["stencil"], e, case["f0"], meta["n_steps"], meta["collision"], p.get("tau"), second,
+                 force=p.get("force"))
     assert rel_err(out, case["f_out"]) <= TOL[meta["dtype"]]
     if meta["dtype"] == "f32":
         # two nodes per packed F2 value: same bits as one node per float
         packed = em.run(meta["stencil"], e, case["f0"], meta["n_steps"], meta["collision"], p.get("tau"),
-                        second, packed=True)
+                        second, packed=True, force=p.get("force"))
         assert np.array_equal(packed, out)
 
 
