@@ -266,8 +266,7 @@ LB_API int lb_ipc_close(void* dptr);
 /* Introspection for tests / roofline arithmetic */
 LB_API int lb_stencil_q(int stencil);
 LB_API size_t lb_bytes_per_update(const lb_desc* desc); /* 2 * Q * sizeof(dtype) */
-LB_API int lb_vector_width(const lb_desc* desc, int has_streaming_bits); /* nodes per thread chosen for aligned
-                                                                           fields (the flag no longer matters) */
+LB_API int lb_vector_width(const lb_desc* desc, int has_streaming_bits); /* nodes per thread chosen for aligned fields */
 
 #ifdef __cplusplus
 }

@@ -123,7 +123,7 @@ int obs_prepare(const Geometry& g, void* scratch, lb::ObsScratch* out, cudaStrea
 // line and matches the buffers' alignment.  LB_VEC=<n> overrides the choice (tuning experiments).
 template <typename T>
 int vector_width(const lb_desc* d, const Geometry& g, const void* a, const void* b, const void* ncm, const void* sbits,
-                 bool scalar_only) {
+                 bool scalar_only, bool masked_streaming) {
   if (scalar_only) return 1;
   const int widest = 16 / int(sizeof(T));
   int cap = widest;
@@ -133,6 +133,9 @@ int vector_width(const lb_desc* d, const Geometry& g, const void* a, const void*
   if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_KBC) cap = (sizeof(T) == 4) ? 2 : 1;
   if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_TRT && sizeof(T) == 4) cap = 2;
   if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_SMAGORINSKY && sizeof(T) == 4) cap = 2;   // measured 0.96 vs 0.91
+  // D3Q27 with masked streaming: 212 registers (2 blocks per SM) with four nodes, 161 (3 blocks) with two;
+  // measured 0.89 vs 0.92 on the stock obstacle
+  if (d->stencil == LB_D3Q27 && masked_streaming && sizeof(T) == 4 && cap > 2) cap = 2;
   static const char* env = getenv("LB_VEC");
   if (env && atoi(env) >= 1) cap = atoi(env) < widest ? atoi(env) : widest;
   for (int v = cap; v > 1; v >>= 1)
@@ -247,7 +250,8 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   c.mode = p.sbits ? lb::MODE_NCM_SBITS : (p.ncm ? lb::MODE_NCM : lb::MODE_PLAIN);
   c.stream = do_stream;
   c.halo = fl->halo != nullptr;
-  c.vec = do_stream ? vector_width<T>(d, g, fl->f, fl->f_next, p.ncm, p.sbits, p.has_outlet && p.sbits == nullptr) : 1;
+  c.vec = do_stream ? vector_width<T>(d, g, fl->f, fl->f_next, p.ncm, p.sbits, p.has_outlet && p.sbits == nullptr,
+                                         p.sbits != nullptr) : 1;
   p.nzv = g.nz / c.vec;
   p.n_threads = g.nx * g.ny * p.nzv;
   // an outlet on the far side of the slowest axis: its plane is the last tiles of the grid -> run them first
@@ -525,9 +529,9 @@ int lb_vector_width(const lb_desc* d, int has_streaming_bits) {
   Geometry g;
   if (check_desc(d, &g)) return -1;
   static char dummy[16] __attribute__((aligned(16)));
-  (void)has_streaming_bits;   // masked streaming runs at the same width since ABI 4
-  return d->dtype == LB_F64 ? vector_width<double>(d, g, dummy, dummy, nullptr, nullptr, false)
-                            : vector_width<float>(d, g, dummy, dummy, nullptr, nullptr, false);
+  const bool ms = has_streaming_bits != 0;
+  return d->dtype == LB_F64 ? vector_width<double>(d, g, dummy, dummy, nullptr, nullptr, false, ms)
+                            : vector_width<float>(d, g, dummy, dummy, nullptr, nullptr, false, ms);
 }
 
 int lb_step(const lb_desc* desc, const lb_fields* fields, int n_steps, void* stream) {
