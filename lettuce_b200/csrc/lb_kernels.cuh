@@ -16,10 +16,11 @@
 // exactly 2*Q*sizeof(T) bytes per node through HBM: the roofline figure of BASELINE.md.
 // The state stays in the reference's canonical form (post-streaming f_t) after every launch.
 //
-// With a packed streaming mask (MODE 2) the kernel runs one node per thread and checks the
-// destination's mask bit before each store; the destination node itself writes its kept
-// value, so every (q, node) of the output is written exactly once (no race, unlike the
-// reference's generated kernel, SURVEY section 3.3 "semantic trap").
+// With a packed streaming mask (MODE 2) a store is suppressed where the destination's mask bit is
+// set and the destination node itself writes its kept value, so every (q, node) of the output is
+// written exactly once (no race, unlike the reference's generated kernel, SURVEY section 3.3
+// "semantic trap").  The kernel keeps its vector width: a hint bit in the packed mask tells a warp
+// whether any of its nodes is near a kept population at all; only those warps run the masked stores.
 #pragma once
 #include <cooperative_groups.h>
 #include <cuda_runtime.h>
@@ -309,8 +310,8 @@ __device__ __forceinline__ void outlet_node(T (&g)[S::Q], const BoundaryDev<T>& 
 }
 
 // One node: moments -> (fused observables) -> collision where ncm == 0, boundary i where ncm == i
-// OUTLETS: compile the in-order boundary loop that outlet planes need (one-node-per-thread kernels
-// only: outlets always come with a streaming mask, which runs one node per thread)
+// OUTLETS: compile the in-order boundary loop that outlet planes need (the masked-streaming kernels --
+// outlets always come with a streaming mask -- and the one-node-per-thread kernels)
 template <class S, typename T, int COLL, int MODE, bool OBS, bool OUTLETS>
 __device__ __forceinline__ void node_update(T (&g)[S::Q], unsigned m, const StepParams<T>& p,
                                             const T* __restrict__ f_in, T* u_out, unsigned x,

@@ -344,7 +344,8 @@ class SlabSimulation(Simulation):
 
     def _run_segment(self, n, fused):
         if any(r.native_slot == nat.LB_OBS_ENSTROPHY for r in fused) and self.world > 1:
-            raise NotImplementedError("Enstrophy across slabs needs a 3-plane velocity halo (not built yet)")
+            raise NotImplementedError("Enstrophy across slabs needs a 3-plane velocity halo, which the slab "
+                                      "transports do not carry")
         if self.transport == 'host':
             self._advance(n)
             self.flow.i += n
