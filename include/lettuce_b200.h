@@ -208,7 +208,8 @@ LB_API int lb_collide(const lb_desc* desc, const void* f_in, void* f_out,
                const uint8_t* no_collision_mask, const lb_boundary* boundaries,
                int n_boundaries, void* stream);
 
-/* Pure streaming with optional destination mask (_simulation.py:160-175). */
+/* Pure streaming (_simulation.py:160-175), f_out != f_in.  streaming_bits must be NULL: destination-masked
+ * streaming goes through lb_step with LB_COLL_NONE, which takes the masks (LB_EINVAL otherwise). */
 LB_API int lb_stream(const lb_desc* desc, const void* f_in, void* f_out,
               const uint32_t* streaming_bits, void* stream);
 
