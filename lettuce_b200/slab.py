@@ -37,6 +37,16 @@ from ._simulation import Simulation
 
 AUTO_PACKED_MIN_LINES = 512 * 512   # faces (lines per z plane) from which 'auto' picks 'p2p-packed'
 
+
+def auto_transport(resolution) -> str:
+    """'p2p' (direct peer stores) for small z faces, 'p2p-packed' for large ones.  Measured (DESIGN.md
+    section 6): 256^2 faces 95.6 % ('p2p') vs 93.8 % ('p2p-packed') of the single-GPU rate at 8 GPUs;
+    1024^2 faces 83 % vs 98.5 %."""
+    lines = 1
+    for n in resolution[:-1]:
+        lines *= int(n)
+    return 'p2p' if lines < AUTO_PACKED_MIN_LINES else 'p2p-packed'
+
 __all__ = ['slab_range', 'zface_populations', 'SlabTaylorGreenVortex', 'SlabSimulation']
 
 
@@ -158,12 +168,7 @@ class SlabSimulation(Simulation):
         if transport is None:
             transport = 'host' if local_stepper is not None else 'auto'
         if transport == 'auto':
-            # measured: 256^2 faces 95.6 % ('p2p') vs 93.8 % ('p2p-packed') of the
-            # single-GPU rate at 8 GPUs; 1024^2 faces 83 % vs 98.5 %
-            lines = 1
-            for n in flow.resolution[:-1]:
-                lines *= n
-            transport = 'p2p' if lines < AUTO_PACKED_MIN_LINES else 'p2p-packed'
+            transport = auto_transport(flow.resolution)
         if transport not in ('p2p-push', 'p2p-packed', 'p2p', 'nccl', 'host'):
             raise ValueError(transport)
         self.transport = transport

@@ -83,6 +83,14 @@ def test_slab_exchange_matches_undivided_oracle(world, stencil, res, collision):
     assert err == 0.0 if collision == "none" else err < 1e-14
 
 
+def test_auto_transport_by_face_size():
+    from lettuce_b200.slab import auto_transport
+    assert auto_transport([256, 256, 256]) == 'p2p'            # bench.py --gpus N: 256^3 per GPU
+    assert auto_transport([1024, 1024, 128]) == 'p2p-packed'   # config 5
+    assert auto_transport([512, 512, 64]) == 'p2p-packed'
+    assert auto_transport([2048, 64]) == 'p2p'                 # 2-D: y-slabs, faces are lines
+
+
 def test_slab_helpers():
     import lettuce_b200 as lt
     from lettuce_b200.slab import slab_range, zface_populations
