@@ -15,6 +15,7 @@ from ._force import *
 from ._boundary import *
 from ._flows import *
 from ._reporter import *
+from ._output import *
 from ._simulation import *
 from .util import *
 from . import _native as native

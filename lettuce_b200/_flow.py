@@ -13,9 +13,10 @@ import torch
 
 from . import _native as nat
 from ._stencil import TorchStencil
-from .util import torch_gradient
+from .util import torch_gradient, torch_jacobi
 
-__all__ = ['Equilibrium', 'Flow', 'Boundary', 'initialize_f_neq']
+__all__ = ['Equilibrium', 'Flow', 'Boundary', 'initialize_f_neq', 'pressure_poisson',
+           'initialize_pressure_poisson']
 
 
 class Equilibrium(ABC):
@@ -91,8 +92,7 @@ class Flow(ABC):
             self.units.convert_pressure_pu_to_density_lu(initial_p))
         initial_u = self.context.convert_to_tensor(self.units.convert_velocity_to_lu(initial_u))
         if self.initialize_pressure:
-            raise NotImplementedError("pressure-Poisson initialisation is outside the hot-path "
-                                      "scope (SURVEY.md section 2, row 2)")
+            initial_rho = pressure_poisson(self.units, initial_u, initial_rho)
         if self._native_initialize_ok(initial_rho, initial_u):
             self.f = self._native_initialize(initial_rho, initial_u, ghost=0)
             return
@@ -251,3 +251,27 @@ def initialize_f_neq(flow: 'Flow'):
     Pi_1_Q = flow.einsum('ab,iab->i', [Pi_1, Q])
     fneq = flow.einsum('i,i->i', [flow.torch_stencil.w, Pi_1_Q])
     return flow.equilibrium(flow, rho, u) - fneq
+
+
+def pressure_poisson(units: 'UnitConversion', u, rho0, tol_abs=1e-10, max_num_steps=100000):
+    """Density whose pressure solves lap(p) = -d_i d_j (u_i u_j), by Jacobi iteration from rho0
+    (_flow.py:239-287).  Like the reference it always iterates over the first TWO axes
+    (`dim=2` is hard-coded at :280; the 3-D case is marked as not working there).  Set-up only."""
+    dx = units.convert_length_to_pu(1.0)
+    u = units.convert_velocity_to_pu(u)
+    p = units.convert_density_lu_to_pressure_pu(rho0)
+    with torch.no_grad():
+        u_mod = torch.zeros_like(u[0])
+        dim = u.shape[0]
+        for i in range(dim):
+            for j in range(dim):
+                u_mod -= torch_gradient(torch_gradient(u[i] * u[j], dx)[i], dx)[j]
+    p_mod = torch_jacobi(u_mod, p[0], dx, dim=2, tol_abs=tol_abs, max_num_steps=max_num_steps)[None, ...]
+    return units.convert_pressure_pu_to_density_lu(p_mod)
+
+
+def initialize_pressure_poisson(flow: 'Flow', max_num_steps=100000, tol_pressure=1e-6):
+    """equilibrium populations of (rho from pressure_poisson, current u) (_flow.py:290-305)"""
+    u = flow.u()
+    rho = pressure_poisson(flow.units, u, flow.rho(), tol_abs=tol_pressure, max_num_steps=max_num_steps)
+    return flow.equilibrium(flow=flow, rho=rho, u=u)

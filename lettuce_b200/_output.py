@@ -1,0 +1,334 @@
+"""The output side of the path: VTKReporter / write_vtk
+(reference/lettuce/ext/_reporter/vtk_reporter.py:11-64), ErrorReporter (error_reporter.py:9-44),
+EnergySpectrum (observable_reporter.py:71-137) and HDF5Reporter / LettuceDataset
+(util/datautils.py:16-160).
+
+What changes against the reference: the reporters never pull the populations to the host.  On a
+CUDA flow `flow.u_pu` / `flow.p_pu` come from the engine's moments kernel (lb_moments, 1 + d
+values per node instead of q), the fields are put into the file's point order ON THE DEVICE and
+cross PCIe once, into one pinned staging buffer; the bytes go to disk with a single write per
+array.  The `.vtr` container is written here (the reference delegates to pyevtk 1.6
+`gridToVTK`, absent from this image): VTK XML RectilinearGrid, version 1.0, little endian,
+UInt64 block headers, raw appended data, coordinates first and then the point data in dict
+order, every array in x-fastest (Fortran) point order -- pyevtk's published layout.  Parity of
+the container is UNPINNED (no pyevtk here to diff against); `read_vtr` below reads the files
+back and the tests pin the payload.
+
+HDF5Reporter / LettuceDataset need h5py, which this image lacks: constructing them raises
+ImportError naming the dependency ("unavailable in this image"); with h5py present they work as
+in the reference."""
+import io
+import os
+import pickle
+import re
+import sys
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from ._reporter import Observable, Reporter
+
+__all__ = ['VTKReporter', 'write_vtk', 'read_vtr', 'ErrorReporter', 'EnergySpectrum',
+           'HDF5Reporter', 'LettuceDataset', 'write_image']
+
+_VTK_TYPE = {'float32': 'Float32', 'float64': 'Float64', 'int8': 'Int8', 'uint8': 'UInt8',
+             'int16': 'Int16', 'uint16': 'UInt16', 'int32': 'Int32', 'uint32': 'UInt32',
+             'int64': 'Int64', 'uint64': 'UInt64'}
+_NP_TYPE = {v: k for k, v in _VTK_TYPE.items()}
+
+
+def _point_order(a) -> np.ndarray:
+    """[nx, ny, nz] array -> flat little-endian array in VTK point order (x fastest)"""
+    a = np.asarray(a)
+    if a.dtype.name not in _VTK_TYPE:
+        raise TypeError(f"VTK cannot hold arrays of dtype {a.dtype}")
+    flat = a.reshape(-1, order='F') if a.ndim > 1 else a
+    return np.ascontiguousarray(flat, dtype=a.dtype.newbyteorder('<'))
+
+
+def grid_to_vtr(path, x, y, z, point_data: Dict[str, np.ndarray], _preordered: bool = False) -> str:
+    """Write `path + '.vtr'`: a rectilinear grid with 1-D coordinate arrays x, y, z and scalar point
+    arrays of shape [len(x), len(y), len(z)] (what pyevtk.hl.gridToVTK(path, x, y, z, pointData=...)
+    writes for 1-D coordinates).  `_preordered`: the arrays are already flat in point order."""
+    x, y, z = (np.asarray(c) for c in (x, y, z))
+    n = (x.size, y.size, z.size)
+    ext = f"0 {n[0] - 1} 0 {n[1] - 1} 0 {n[2] - 1}"
+    blocks, offset = [], 0
+
+    def add(name, arr, flat):
+        nonlocal offset
+        data = arr if flat else _point_order(arr)
+        line = (f'<DataArray Name="{name}" NumberOfComponents="1" type="{_VTK_TYPE[data.dtype.name]}" '
+                f'format="appended" offset="{offset}"/>\n')
+        blocks.append(data)
+        offset += 8 + data.nbytes
+        return line
+
+    head = ['<?xml version="1.0"?>\n',
+            '<VTKFile type="RectilinearGrid" version="1.0" byte_order="LittleEndian" header_type="UInt64">\n',
+            f'<RectilinearGrid WholeExtent="{ext}">\n', f'<Piece Extent="{ext}">\n', '<Coordinates>\n']
+    for name, c in (("x_coordinates", x), ("y_coordinates", y), ("z_coordinates", z)):
+        head.append(add(name, c, False))
+    head.append('</Coordinates>\n')
+    first = next(iter(point_data), None)
+    head.append(f'<PointData scalars="{first}">\n' if first is not None else '<PointData>\n')
+    npoints = n[0] * n[1] * n[2]
+    for name, arr in point_data.items():
+        arr = np.asarray(arr)
+        if arr.size != npoints or (not _preordered and tuple(arr.shape) != n):
+            raise ValueError(f"point array '{name}' of shape {arr.shape} does not match the grid {n}")
+        head.append(add(name, arr, _preordered))
+    head += ['</PointData>\n', '</Piece>\n', '</RectilinearGrid>\n', '<AppendedData encoding="raw">\n_']
+    filename = str(path) + ".vtr"
+    with open(filename, "wb") as fh:
+        fh.write("".join(head).encode("ascii"))
+        for data in blocks:
+            fh.write(np.uint64(data.nbytes).tobytes())
+            fh.write(memoryview(data).cast('B'))
+        fh.write(b'\n</AppendedData>\n</VTKFile>\n')
+    return filename
+
+
+def read_vtr(filename):
+    """Read a file written by grid_to_vtr (or pyevtk's gridToVTK with 1-D coordinates) back:
+    returns (x, y, z, {name: array [nx, ny, nz]})."""
+    with open(filename, "rb") as fh:
+        raw = fh.read()
+    marker = raw.index(b'<AppendedData encoding="raw">')
+    start = raw.index(b'_', marker) + 1
+    header = raw[:marker].decode("ascii")
+    arrays = {}
+    for m in re.finditer(r'<DataArray Name="([^"]+)" NumberOfComponents="1" type="(\w+)" '
+                         r'format="appended" offset="(\d+)"\s*/>', header):
+        name, vtype, off = m.group(1), m.group(2), int(m.group(3))
+        nbytes = int(np.frombuffer(raw, dtype='<u8', count=1, offset=start + off)[0])
+        dt = np.dtype(_NP_TYPE[vtype]).newbyteorder('<')
+        arrays[name] = np.frombuffer(raw, dtype=dt, count=nbytes // dt.itemsize, offset=start + off + 8)
+    x, y, z = (arrays.pop(k) for k in ("x_coordinates", "y_coordinates", "z_coordinates"))
+    shape = (x.size, y.size, z.size)
+    return x, y, z, {k: v.reshape(shape, order='F') for k, v in arrays.items()}
+
+
+def write_vtk(point_dict, id=0, filename_base="./data/output"):
+    """vtk_reporter.py:11-16: integer node coordinates, one file per `id`"""
+    shape = np.asarray(point_dict["p"]).shape
+    return grid_to_vtr(f"{filename_base}_{id:08d}", np.arange(0, shape[0]), np.arange(0, shape[1]),
+                       np.arange(0, shape[2]), point_dict)
+
+
+class VTKReporter(Reporter):
+    """Pressure and velocity in physical units as `<filename_base>_<step:08d>.vtr` every `interval`
+    steps (vtk_reporter.py:19-64).  `point_dict` holds the arrays of the last file, [nx, ny, nz]
+    views (nz = 1 in 2-D) like the reference's."""
+
+    def __init__(self, interval=50, filename_base="./data/output"):
+        super().__init__(interval)
+        self.filename_base = filename_base
+        directory = os.path.dirname(filename_base)
+        if directory and not os.path.isdir(directory):
+            os.mkdir(directory)
+        self.point_dict = dict()
+        self._stage = None     # pinned host staging buffer [1 + d, nodes]
+
+    def _staging(self, rows, nodes, dtype, pinned):
+        st = self._stage
+        if st is None or tuple(st.shape) != (rows, nodes) or st.dtype != dtype or st.is_pinned() != pinned:
+            self._stage = st = torch.empty([rows, nodes], dtype=dtype, pin_memory=pinned)
+        return st
+
+    def __call__(self, simulation: 'Simulation'):
+        flow = simulation.flow
+        if flow.i % self.interval != 0:
+            return
+        d = flow.stencil.d
+        fields = torch.cat([flow.p_pu, flow.u_pu])               # [1 + d, *res], on the flow's device
+        # file order = x fastest: reverse the node axes on the device, then one copy to the host
+        ordered = fields.permute(0, *range(d, 0, -1)).reshape(1 + d, -1)
+        stage = self._staging(1 + d, ordered.shape[1], ordered.dtype, ordered.is_cuda)
+        stage.copy_(ordered)                                     # synchronous for a pinned destination
+        flat = stage.numpy()
+        shape3 = tuple(flow.resolution) + (1,) * (3 - d)
+        names = ["p"] + [f"u{'xyz'[c]}" for c in range(d)]
+        self.point_dict = {name: flat[k].reshape(shape3, order='F') for k, name in enumerate(names)}
+        grid_to_vtr(f"{self.filename_base}_{flow.i:08d}", *(np.arange(0, n) for n in shape3),
+                    {name: flat[k] for k, name in enumerate(names)}, _preordered=True)
+
+    def output_mask(self, simulation: 'Simulation'):
+        """no_collision_mask as `<filename_base>_mask.vtr` (vtk_reporter.py:49-64)"""
+        flow = simulation.flow
+        mask = flow.context.convert_to_ndarray(simulation.no_collision_mask).astype(int)
+        if flow.stencil.d == 2:
+            mask = mask[..., None]
+        grid_to_vtr(str(self.filename_base) + "_mask", *(np.arange(0, n) for n in mask.shape), {"mask": mask})
+
+
+class ErrorReporter(Reporter):
+    """L2 errors of u and p (physical units) against `analytical_solution(t=...)`, normalised by
+    resolution^(d/2) (error_reporter.py:9-44).  u and p come from the moments kernel; the norms are
+    two device reductions."""
+
+    def __init__(self, analytical_solution, interval=1, out=sys.stdout):
+        Reporter.__init__(self, interval)
+        self.analytical_solution = analytical_solution
+        self.out = [] if out is None else out
+        if not isinstance(self.out, list):
+            print("#error_u         error_p", file=self.out)
+
+    def __call__(self, simulation: 'Simulation'):
+        flow = simulation.flow
+        i = flow.i
+        if i % self.interval != 0:
+            return
+        t = simulation.units.convert_time_to_pu(i)
+        pref, uref = self.analytical_solution(t=t)
+        pref = flow.context.convert_to_tensor(pref)
+        uref = flow.context.convert_to_tensor(uref)
+        p, u = flow.p_pu, flow.u_pu
+        resolution = torch.pow(torch.prod(flow.context.convert_to_tensor(p.size())), 1 / flow.stencil.d)
+        err_u = torch.norm(u - uref) / resolution ** (flow.stencil.d / 2)
+        err_p = torch.norm(p - pref) / resolution ** (flow.stencil.d / 2)
+        if isinstance(self.out, list):
+            self.out.append([err_u.item(), err_p.item()])
+        else:
+            print(err_u.item(), err_p.item(), file=self.out)
+
+
+class EnergySpectrum(Observable):
+    """Kinetic energy per integer wavenumber shell (observable_reporter.py:71-137): u from the
+    moments kernel, one FFT per component (cuFFT through torch.fft on a CUDA flow), and the shell
+    sums as ONE matrix product with the [nodes, shells] membership mask (the reference multiplies
+    the spectrum into a [*res, shells] temporary and sums it)."""
+
+    def __init__(self, flow: 'Flow'):
+        super().__init__(flow)
+        self.dx = self.flow.units.convert_length_to_pu(1.0)
+        self.dimensions = self.flow.resolution
+        frequencies = [self.context.convert_to_tensor(np.fft.fftfreq(dim, d=1 / dim))
+                       for dim in self.dimensions]
+        wavenumbers = torch.stack(torch.meshgrid(*frequencies, indexing='ij'))
+        wavenorms = torch.norm(wavenumbers, dim=0)
+        if self.flow.stencil.d == 3:
+            self.norm = self.dimensions[0] * np.sqrt(2 * np.pi) / self.dx ** 2
+        else:
+            self.norm = self.dimensions[0] / self.dx
+        self.wavenumbers = torch.arange(int(torch.max(wavenorms)))
+        k = self.wavenumbers.to(dtype=self.context.dtype, device=self.context.device)
+        self.wavemask = (wavenorms[..., None] > k - 0.5) & (wavenorms[..., None] <= k + 0.5)
+        self._shells = self.wavemask.reshape(-1, self.wavemask.shape[-1]).to(dtype=self.context.dtype)
+
+    def __call__(self, f: Optional[torch.Tensor] = None):
+        return self.spectrum_from_u(self.flow.u())
+
+    def spectrum_from_u(self, u):
+        u = self.flow.units.convert_velocity_to_pu(u)
+        return self._ekin_spectrum(u).reshape(-1) @ self._shells
+
+    def _ekin_spectrum(self, u):
+        d = self.flow.stencil.d
+        uh = torch.fft.fftn(u, dim=tuple(range(1, d + 1))) / self.norm
+        return torch.sum(0.5 * (uh.imag ** 2 + uh.real ** 2), dim=0)
+
+
+def _need_h5py():
+    try:
+        import h5py
+    except ImportError as e:
+        raise ImportError("HDF5Reporter / LettuceDataset need h5py, which is unavailable in this "
+                          "image; use Flow.dump / Flow.load or VTKReporter") from e
+    return h5py
+
+
+class HDF5Reporter(Reporter):
+    """Appends the populations to `<filebase>.h5` every `interval` steps, with the pickled flow and
+    collision as attributes (datautils.py:16-83)."""
+
+    def __init__(self, flow, collision, interval, filebase='./output', metadata=None):
+        h5py = _need_h5py()
+        from . import __version__
+        super().__init__(interval)
+        self.context = flow.context
+        self.filebase = filebase
+        with h5py.File(self.filebase + '.h5', 'w') as fs:
+            fs.attrs['lettuce_version'] = __version__
+            fs.attrs["flow"] = self._pickle_to_h5(flow)
+            fs.attrs['_collision'] = self._pickle_to_h5(collision)
+            for attr in (metadata or {}):
+                fs.attrs[attr] = metadata[attr]
+            self.shape = (flow.stencil.q, *flow.resolution)
+            fs.create_dataset(name="f", shape=(0, *self.shape), maxshape=(None, *self.shape))
+
+    def __call__(self, simulation: 'Simulation'):
+        if simulation.flow.i % self.interval == 0:
+            h5py = _need_h5py()
+            with h5py.File(self.filebase + '.h5', 'r+') as fs:
+                fs["f"].resize(fs["f"].shape[0] + 1, axis=0)
+                fs["f"][-1, ...] = self.context.convert_to_ndarray(simulation.flow.f)
+                fs.attrs['data'] = str(fs["f"].shape[0])
+                fs.attrs['steps'] = str(simulation.flow.i)
+
+    @staticmethod
+    def _pickle_to_h5(instance):
+        bytes_io = io.BytesIO()
+        pickle.dump(instance, bytes_io)
+        bytes_io.seek(0)
+        return np.void(bytes_io.getvalue())
+
+
+class LettuceDataset(torch.utils.data.Dataset):
+    """torch Dataset over the `f` snapshots of an HDF5Reporter file (datautils.py:86-160)."""
+
+    def __init__(self, filebase, transform=None, target=False, skip_idx_to_target=1):
+        h5py = _need_h5py()
+        super().__init__()
+        self.filebase = filebase
+        self.transform = transform
+        self.target = target
+        self.skip_idx_to_target = skip_idx_to_target
+        self.fs = h5py.File(self.filebase, "r")
+        self.shape = self.fs["f"].shape
+        self.keys = list(self.fs.keys())
+        self.context = self._unpickle_from_h5(self.fs.attrs["flow"]).context
+
+    def __len__(self):
+        return self.shape[0] - self.skip_idx_to_target if self.target else self.shape[0]
+
+    def __getitem__(self, idx):
+        f = self.get_data(idx)
+        target = self.get_data(idx + self.skip_idx_to_target) if self.target else []
+        if self.transform:
+            f = self.transform(f)
+            if self.target:
+                target = self.transform(target)
+        return (f, target, idx) if self.target else (f, idx)
+
+    def __del__(self):
+        fs = getattr(self, 'fs', None)
+        if fs is not None:
+            fs.close()
+
+    def get_data(self, idx):
+        return self.context.convert_to_tensor(self.fs["f"][idx])
+
+    def get_attr(self, attr):
+        return self.fs.attrs[attr]
+
+    @staticmethod
+    def _unpickle_from_h5(byte_str):
+        return pickle.load(io.BytesIO(byte_str))
+
+
+def write_image(filename, array2d):
+    """write_image.py:8-19 draws with matplotlib, which is unavailable in this image."""
+    try:
+        import matplotlib.pyplot as plt
+    except ImportError as e:
+        raise ImportError("write_image needs matplotlib, which is unavailable in this image") from e
+    fig, ax = plt.subplots()
+    plt.tight_layout()
+    ax.imshow(array2d)
+    ax.set_xlabel('')
+    ax.set_ylabel('')
+    ax.get_xaxis().set_visible(False)
+    ax.get_yaxis().set_visible(False)
+    plt.savefig(filename)

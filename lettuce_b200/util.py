@@ -1,9 +1,18 @@
 """Small host-side helpers with the reference's names (reference/lettuce/util/utility.py).
 Used at set-up time only (initial conditions); nothing here is on the per-step path."""
+import inspect
+
 import torch
 
-__all__ = ['LettuceException', 'LettuceWarning', 'InefficientCodeWarning', 'ExperimentalWarning',
-           'torch_gradient', 'append_axes']
+__all__ = ['get_subclasses', 'LettuceException', 'LettuceWarning', 'InefficientCodeWarning',
+           'ExperimentalWarning', 'torch_gradient', 'grid_fine_to_coarse', 'torch_jacobi', 'append_axes']
+
+
+def get_subclasses(cls, module):
+    """direct subclasses of `cls` among the members of `module` (utility.py:15-18)"""
+    for _, obj in inspect.getmembers(module):
+        if hasattr(obj, "__bases__") and cls in obj.__bases__:
+            yield obj
 
 
 class LettuceException(Exception):
@@ -51,3 +60,37 @@ def torch_gradient(f: torch.Tensor, dx=1, order=2) -> torch.Tensor:
 def append_axes(array, n):
     """array[..., None * n] (utility.py append_axes)"""
     return array[(Ellipsis,) + (None,) * n]
+
+
+def grid_fine_to_coarse(flow: 'Flow', f_fine, tau_fine, tau_coarse):
+    """Every second node of a fine-grid field with the non-equilibrium part rescaled by
+    2 tau_coarse / tau_fine (utility.py:102-118).  Set-up helper (restart on a coarser grid)."""
+    if f_fine.dim() not in (3, 4):
+        raise LettuceException("Invalid dimension!")
+    sub = f_fine[(slice(None),) + (slice(None, None, 2),) * (f_fine.dim() - 1)]
+    f_eq = flow.equilibrium(flow, rho=flow.rho(sub), u=flow.u(sub))
+    return f_eq + 2 * tau_coarse / tau_fine * (sub - f_eq)
+
+
+def torch_jacobi(f, p, dx, dim, tol_abs=1e-10, max_num_steps=100000):
+    """Jacobi iteration for the periodic Poisson equation lap(p) = f with second-order
+    differences; stops when mean(residuum^2) <= tol_abs (utility.py:121-166).  The residuum is
+    taken with the updated p, as the reference does."""
+    axes = range(dim)
+    error, it = 1, 0
+    while error > tol_abs and it < max_num_steps:
+        it += 1
+        nb = None
+        for s in (1, -1):
+            for a in axes:
+                r = p.roll(shifts=s, dims=a)
+                nb = r if nb is None else nb + r
+        p = (f * (dx ** 2) - nb) * -1 / (2 * dim)
+        nb = None
+        for s in (1, -1):
+            for a in axes:
+                r = p.roll(shifts=s, dims=a)
+                nb = r if nb is None else nb + r
+        residuum = f - (nb - 2 * dim * p) / (dx ** 2)
+        error = torch.mean(residuum ** 2)
+    return p
