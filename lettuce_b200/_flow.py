@@ -105,7 +105,7 @@ class Flow(ABC):
         ext = list(self.resolution[:-1]) + [self.resolution[-1] + 2 * ghost]
         return (rho.is_cuda and u.is_cuda and rho.dtype in nat.DTYPE_IDS and u.dtype == rho.dtype
                 and type(self.stencil).__name__ in nat.STENCIL_IDS
-                and type(self.equilibrium) is QuadraticEquilibrium
+                and isinstance(self.equilibrium, QuadraticEquilibrium)
                 and list(rho.shape) == [1, *ext] and list(u.shape) == [self.stencil.d, *ext]
                 and (not self.initialize_fneq or min(self.resolution) >= 3))
 
