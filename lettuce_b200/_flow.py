@@ -149,6 +149,15 @@ class Flow(ABC):
                                            nat.current_stream_ptr(f.device)))
         return rho, u
 
+    def rho_u(self, f: Optional[torch.Tensor] = None):
+        """(rho, u) in lattice units from ONE pass over the populations (the output-side reporters
+        need both; the reference computes them separately, _flow.py:136-172)"""
+        f = self.f if f is None else f
+        if self._native_moments_ok(f):
+            return self._native_moments(f, True, True)
+        rho = self.rho(f)
+        return rho, self.u(f, rho=rho)
+
     def rho(self, f: Optional[torch.Tensor] = None) -> torch.Tensor:
         """density, shape [1, *res] (_flow.py:136-138)"""
         f = self.f if f is None else f

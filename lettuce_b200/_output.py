@@ -142,7 +142,9 @@ class VTKReporter(Reporter):
         if flow.i % self.interval != 0:
             return
         d = flow.stencil.d
-        fields = torch.cat([flow.p_pu, flow.u_pu])               # [1 + d, *res], on the flow's device
+        rho, u = flow.rho_u()                                    # one pass over f (lb_moments)
+        fields = torch.cat([flow.units.convert_density_lu_to_pressure_pu(rho),
+                            flow.units.convert_velocity_to_pu(u)])   # [1 + d, *res], on the flow's device
         # file order = x fastest: reverse the node axes on the device, then one copy to the host
         ordered = fields.permute(0, *range(d, 0, -1)).reshape(1 + d, -1)
         stage = self._staging(1 + d, ordered.shape[1], ordered.dtype, ordered.is_cuda)
@@ -184,7 +186,9 @@ class ErrorReporter(Reporter):
         pref, uref = self.analytical_solution(t=t)
         pref = flow.context.convert_to_tensor(pref)
         uref = flow.context.convert_to_tensor(uref)
-        p, u = flow.p_pu, flow.u_pu
+        rho, u = flow.rho_u()                                    # one pass over f (lb_moments)
+        p = flow.units.convert_density_lu_to_pressure_pu(rho)
+        u = flow.units.convert_velocity_to_pu(u)
         resolution = torch.pow(torch.prod(flow.context.convert_to_tensor(p.size())), 1 / flow.stencil.d)
         err_u = torch.norm(u - uref) / resolution ** (flow.stencil.d / 2)
         err_p = torch.norm(p - pref) / resolution ** (flow.stencil.d / 2)
