@@ -117,3 +117,65 @@ def test_slab_tgv_initial_state_equals_global_slice():
             assert s.resolution == [12, 10, 16 // world]
             assert s.units.relaxation_parameter_lu == g.units.relaxation_parameter_lu
             assert torch.allclose(s.f, g.f[..., s.z0:s.z1], rtol=0, atol=1e-15)
+
+
+def _reduce_worker(rank, world, port, q):
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import lettuce_b200 as lt
+        from lettuce_b200 import _native as nat
+        from lettuce_b200.slab import SlabSimulation
+        from oracle import lbm_oracle as orc
+        torch.set_num_threads(1)
+        S = lt.D2Q9()
+        lat = orc.OracleLattice("D2Q9", torch.float64)
+        torch.manual_seed(7)
+        w = torch.tensor(S.w, dtype=torch.float64).reshape(9, 1, 1)
+        f_global = w * (1.0 + 0.1 * torch.rand([9, 6, 4 * world], dtype=torch.float64))
+
+        class LocalFlow:
+            pass
+        flow = LocalFlow()
+        flow.context = lt.Context(device="cpu", dtype=torch.float64, use_native=False)
+        flow.stencil, flow.resolution, flow.i = S, [6, 4], 0
+        flow.f = f_global[..., 4 * rank:4 * rank + 4].contiguous()
+        sim = SlabSimulation(flow, None, [], transport="host", local_stepper=lambda f: f)
+        # per-rank partial observables of two report steps, as the step kernel delivers them
+        obs = torch.zeros([2, nat.LB_OBS_COUNT], dtype=torch.float64)
+        for row, f in enumerate((flow.f, 2 * flow.f)):
+            obs[row, nat.LB_OBS_ENERGY] = orc.energy_lu(lat, f)
+            obs[row, nat.LB_OBS_MAXU2] = orc.max_velocity_lu(lat, f) ** 2
+            obs[row, nat.LB_OBS_MASS] = f.sum()
+        keep = obs.clone()
+        out = sim._finalize_obs(obs)
+        assert torch.equal(obs, keep)                       # the partials are not modified in place
+        assert flow._obs_allreduce is not None              # stand-alone observables use the same hook
+        if rank == 0:
+            e = float(orc.energy_lu(lat, f_global))
+            m = float(orc.max_velocity_lu(lat, f_global)) ** 2
+            q.put([abs(float(out[0, nat.LB_OBS_ENERGY]) - e) / e, abs(float(out[0, nat.LB_OBS_MAXU2]) - m) / m,
+                   abs(float(out[0, nat.LB_OBS_MASS]) - float(f_global.sum())),
+                   abs(float(out[1, nat.LB_OBS_MASS]) - 2 * float(f_global.sum()))])
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_slab_observables_reduce_globally(world):
+    """fused-reporter partials: energy / mass are summed over ranks, max |u|^2 is the maximum"""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_reduce_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    errs = q.get(timeout=10)
+    assert max(errs) <= 1e-12
