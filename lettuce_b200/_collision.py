@@ -16,7 +16,7 @@ import torch
 from . import _native as nat
 
 __all__ = ['Collision', 'BGKCollision', 'TRTCollision', 'KBCCollision', 'KBCCollision2D',
-           'KBCCollision3D', 'NoCollision', 'RegularizedCollision', 'SmagorinskyCollision']
+           'KBCCollision3D', 'NoCollision', 'RegularizedCollision', 'SmagorinskyCollision', 'MRTCollision']
 
 
 class Collision(ABC):
@@ -155,3 +155,26 @@ class SmagorinskyCollision(Collision):
     def native_descriptor(self, flow):
         # lb_desc.tau_minus carries the Smagorinsky constant (include/lettuce_b200.h)
         return dict(collision=nat.LB_COLL_SMAGORINSKY, tau=float(self.tau), tau_minus=float(self.constant))
+
+
+class MRTCollision(Collision):
+    """Multiple-relaxation-time operator over a user-supplied moment transform
+    (reference/lettuce/ext/_collision/mrt_collision.py:6-36).  The reference has no native kernel for it
+    (`native_available() == False`, :32-36) and neither has this engine: `Simulation` refuses it.  The
+    operator itself stays callable on a flow (torch expressions on the flow's device) for analysis."""
+
+    def __init__(self, transform: 'Transform', relaxation_parameters: list, context: 'Context'):
+        self.transform = transform
+        self.relaxation_parameters = context.convert_to_tensor(relaxation_parameters)
+
+    def __call__(self, flow: 'Flow'):
+        m = self.transform.transform(flow.f)
+        meq = self.transform.equilibrium(m, flow)
+        m = m - flow.einsum("q,q->q", [1 / self.relaxation_parameters, m - meq])
+        return self.transform.inverse_transform(m)
+
+    def native_available(self) -> bool:
+        return False
+
+    def native_descriptor(self, flow):
+        raise NotImplementedError("MRTCollision has no native kernel")
