@@ -70,6 +70,9 @@ class Simulation:
         self.no_collision_mask, self.no_streaming_mask = build_masks(flow, self.boundaries, self.context)
 
         # ---- native descriptors -----------------------------------------------------------------
+        if type(flow.stencil).__name__ not in nat.STENCIL_IDS:
+            raise NotImplementedError(f"stencil '{type(flow.stencil).__name__}' has no native kernel "
+                                      f"({', '.join(nat.STENCIL_IDS)} have)")
         if not isinstance(collision, Collision) or not collision.native_available():
             raise NotImplementedError(f"collision '{type(collision).__name__}' has no native kernel")
         if flow.equilibrium is not None and not flow.equilibrium.native_available():
