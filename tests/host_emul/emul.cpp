@@ -90,3 +90,43 @@ extern "C" int emul_moments(int stencil, int dtype, const void* fv, long n, void
   };
   return dtype == 1 ? st(double{}) : st(float{});
 }
+
+// equilibrium of (rho, u) on every node: rho [n], u [3][n] (kernel axes) -> f [Q][n]; the function the step
+// kernel calls for LB_BND_EQUILIBRIUM nodes (lb_kernels.cuh node_update)
+extern "C" int emul_equilibrium(int stencil, int dtype, long n, const void* rho_v, const void* u_v, void* f_v) {
+  auto go = [&](auto s, auto t) {
+    using S = decltype(s); using T = decltype(t);
+    const T* rho = static_cast<const T*>(rho_v); const T* u = static_cast<const T*>(u_v);
+    T* f = static_cast<T*>(f_v);
+    for (long i = 0; i < n; ++i) {
+      T g[S::Q];
+      const T uu[3] = {u[i], u[n + i], u[2 * n + i]};
+      equilibrium<S, T>(rho[i], uu, g);
+      for (int q = 0; q < S::Q; ++q) f[q * n + i] = g[q];
+    }
+  };
+  auto st = [&](auto t) {
+    switch (stencil) { case 0: go(D2Q9{}, t); return 0; case 1: go(D3Q19{}, t); return 0; case 2: go(D3Q27{}, t); return 0; }
+    return 1;
+  };
+  return dtype == 1 ? st(double{}) : st(float{});
+}
+
+// bounce-back of every node in place, f [Q][n] (lb_physics.cuh bounce_back_node)
+extern "C" int emul_bounce_back(int stencil, int dtype, long n, void* f_v) {
+  auto go = [&](auto s, auto t) {
+    using S = decltype(s); using T = decltype(t);
+    T* f = static_cast<T*>(f_v);
+    for (long i = 0; i < n; ++i) {
+      T g[S::Q];
+      for (int q = 0; q < S::Q; ++q) g[q] = f[q * n + i];
+      bounce_back_node<S, T>(g);
+      for (int q = 0; q < S::Q; ++q) f[q * n + i] = g[q];
+    }
+  };
+  auto st = [&](auto t) {
+    switch (stencil) { case 0: go(D2Q9{}, t); return 0; case 1: go(D3Q19{}, t); return 0; case 2: go(D3Q27{}, t); return 0; }
+    return 1;
+  };
+  return dtype == 1 ? st(double{}) : st(float{});
+}

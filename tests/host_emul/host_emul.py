@@ -27,6 +27,8 @@ class HostEmul:
         self.lib.emul_collide.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_long,
                                           C.POINTER(C.c_double)]
         self.lib.emul_moments.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_long, C.c_void_p, C.c_void_p]
+        self.lib.emul_equilibrium.argtypes = [C.c_int, C.c_int, C.c_long, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.lib.emul_bounce_back.argtypes = [C.c_int, C.c_int, C.c_long, C.c_void_p]
 
     @staticmethod
     def params(collision, tau=None, tau_minus=1.0, force=None):
@@ -77,4 +79,58 @@ class HostEmul:
             f = self.collide(stencil, f, collision, cp, packed)
             for q in range(1, f.shape[0]):
                 f[q] = np.roll(f[q], shift=tuple(e[q]), axis=axes)
+        return f
+
+    def equilibrium(self, stencil, rho, u, res, dtype):
+        """rho / u: arrays in lattice units that broadcast against [1, *res] / [d, *res] (the shapes an
+        EquilibriumBoundaryPU accepts) -> feq [Q, *res] from the device header's equilibrium()"""
+        d = len(res)
+        n = int(np.prod(res))
+        rho = np.asarray(rho, dtype=dtype)
+        u = np.asarray(u, dtype=dtype)
+        rho_f = np.ascontiguousarray(np.broadcast_to(rho.reshape((1,) * (d - rho.ndim) + rho.shape if rho.ndim <= d
+                                                                 else rho.shape[-d:]), res)).reshape(n)
+        u = u.reshape([u.shape[0]] + [1] * (d + 1 - u.ndim) + list(u.shape[1:]))
+        u_l = np.broadcast_to(u, [d, *res]).reshape(d, n)
+        u_k = np.zeros([3, n], dtype=dtype)          # kernel axes: a 2-D lattice runs as X = 1
+        u_k[3 - d:] = u_l
+        q = {"D2Q9": 9, "D3Q19": 19, "D3Q27": 27}[stencil]
+        out = np.empty([q, n], dtype=dtype)
+        rc = self.lib.emul_equilibrium(STENCIL_ID[stencil], 1 if dtype == np.float64 else 0, n,
+                                       rho_f.ctypes.data, np.ascontiguousarray(u_k).ctypes.data, out.ctypes.data)
+        assert rc == 0
+        return out.reshape([q, *res])
+
+    def bounce_back(self, stencil, f):
+        out = np.ascontiguousarray(f).copy()
+        n = int(np.prod(f.shape[1:]))
+        assert self.lib.emul_bounce_back(STENCIL_ID[stencil], 1 if f.dtype == np.float64 else 0, n,
+                                         out.ctypes.data) == 0
+        return out
+
+    def run_masked(self, stencil, e, f0, n_steps, collision, ncm, nsm, boundaries, tau=None, tau_minus=1.0,
+                   force=None):
+        """collide where ncm == 0, boundary i where ncm == i (bounce-back or equilibrium, device arithmetic),
+        destination-masked streaming (reference/lettuce/_simulation.py:160-189); boundaries: list of
+        dict(kind='bounce_back') | dict(kind='equilibrium', rho=..., u=...) in index order"""
+        cp = self.params(collision, tau, tau_minus, force)
+        if force is not None:
+            collision = "bgk_force"
+        f = np.ascontiguousarray(f0).copy()
+        res = list(f.shape[1:])
+        axes = tuple(range(f.ndim - 1))
+        feq = {i: self.equilibrium(stencil, b["rho"], b["u"], res, f.dtype.type)
+               for i, b in enumerate(boundaries, start=1) if b["kind"] == "equilibrium"}
+        for _ in range(n_steps):
+            new = np.where(ncm[None] == 0, self.collide(stencil, f, collision, cp), f)
+            bb = None
+            for i, b in enumerate(boundaries, start=1):
+                if b["kind"] == "equilibrium":
+                    new = np.where(ncm[None] == i, feq[i], new)
+                else:
+                    bb = self.bounce_back(stencil, f) if bb is None else bb
+                    new = np.where(ncm[None] == i, bb, new)
+            f = new
+            for q in range(1, f.shape[0]):
+                f[q] = np.where(nsm[q] == 1, f[q], np.roll(f[q], shift=tuple(e[q]), axis=axes))
         return f

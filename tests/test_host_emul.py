@@ -88,3 +88,35 @@ def test_kbc_f32_stepwise_criterion_on_host(em):
         n_special += n
         f = torch.from_numpy(out)
     assert 0 < n_special <= 0.01 * 4 * f.numel()
+
+
+def _boundary_cases():
+    out = []
+    for name in golden_names():
+        meta = load_case(name)["meta"]
+        if meta["boundaries"] and all(b["kind"] in ("bounce_back", "equilibrium") for b in meta["boundaries"]) \
+                and name not in ILL_CONDITIONED_FIRST_STEP:
+            out.append(name)
+    return out
+
+
+@pytest.mark.parametrize("name", _boundary_cases())
+def test_device_boundary_arithmetic_vs_golden(em, name):
+    """bounce-back and equilibrium boundary nodes with the device headers' bounce_back_node() / equilibrium(),
+    masks and destination-masked streaming in numpy, against the reference's runs with boundaries"""
+    case = load_case(name)
+    meta = case["meta"]
+    e = orc.STENCILS[meta["stencil"]]["e"]
+    p = collision_params(meta)
+    second = p.get("tau_minus", p.get("smagorinsky_constant", 1.0))
+    bnds = []
+    for b in meta["boundaries"]:
+        i = b["index"]
+        bnds.append(dict(kind="equilibrium", rho=case[f"b{i}_rho"], u=case[f"b{i}_u"])
+                    if b["kind"] == "equilibrium" else dict(kind="bounce_back"))
+    out = em.run_masked(meta["stencil"], e, case["f0"], meta["n_steps"], meta["collision"], case["ncm"], case["nsm"],
+                        bnds, tau=p.get("tau"), tau_minus=second, force=p.get("force"))
+    if meta["collision"] == "none" and not any(b["kind"] == "equilibrium" for b in bnds):
+        assert np.array_equal(out, case["f_out"])
+    else:
+        assert rel_err(out, case["f_out"]) <= TOL[meta["dtype"]]
