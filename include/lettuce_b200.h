@@ -18,6 +18,8 @@
  *       (bounce_back_boundary.py:17-18, equilibrium_boundary_pu.py:27-32)
  *                                                          -> lb_collide()
  *   - `Flow.rho/j/u` (lettuce/_flow.py:136-172)            -> lb_moments()
+ *   - the field extraction of `VTKReporter.__call__` (ext/_reporter/vtk_reporter.py:29-47)
+ *                                                          -> lb_output_fields()
  *   - the reporter reductions IncompressibleKineticEnergy / MaximumVelocity / Enstrophy
  *       (lettuce/ext/_reporter/observable_reporter.py:27-68, util/utility.py:37-99)
  *                                                          -> lb_observables(), and the
@@ -221,6 +223,16 @@ LB_API int lb_pack_streaming_mask(const lb_desc* desc, const uint8_t* nsm, uint3
 
 /* rho_out [*res] and/or u_out [d][*res] (either may be NULL) */
 LB_API int lb_moments(const lb_desc* desc, const void* f, void* rho_out, void* u_out, void* stream);
+
+/* The fields an output reporter writes, in ONE pass over f: out [1 + d][*reversed(res)] =
+ *   out[0] = (rho - rho0) * p_scale     pressure in physical units   (lettuce/_flow.py:183-186, _unit.py:82-83)
+ *   out[1 + c] = u_c * u_scale          velocity in physical units   (lettuce/_flow.py:188-190, _unit.py:52-53)
+ * stored in the point order of a VTK file, lattice x FASTEST (pyevtk packs every array in Fortran order),
+ * i.e. out[k][z][y][x] for a 3-D lattice f[q][x][y][z].  Replaces the field extraction of
+ * `VTKReporter.__call__` (lettuce/ext/_reporter/vtk_reporter.py:29-47): flow.u_pu, flow.p_pu, the numpy
+ * conversions and the reordering.  p_scale = cs^2 * p_char_pu / p_char_lu, u_scale = u_char_pu / u_char_lu. */
+LB_API int lb_output_fields(const lb_desc* desc, const void* f, double rho0, double p_scale, double u_scale,
+                     void* out, void* stream);
 
 /* Initial populations from (rho, u) in lattice units -- replaces `Flow.initialize`
  * (lettuce/_flow.py:106-122: f = equilibrium(rho, u)) and, with `with_fneq` != 0, its first-order

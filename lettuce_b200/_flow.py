@@ -149,6 +149,27 @@ class Flow(ABC):
                                            nat.current_stream_ptr(f.device)))
         return rho, u
 
+    def output_fields_pu(self, f: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """[1 + d, nodes]: p_pu then u_pu, each FLAT IN FILE ORDER (lattice x fastest), what a field-writing
+        reporter needs (vtk_reporter.py:29-47).  On a CUDA flow one `lb_output_fields` launch: the
+        populations are read once and the fields leave the kernel already converted and reordered."""
+        f = self.f if f is None else f
+        d = self.stencil.d
+        if self._native_moments_ok(f):
+            units = self.units
+            desc = nat.make_desc(type(self.stencil).__name__, f.dtype, self.resolution)
+            out = torch.empty([1 + d, f[0].numel()], dtype=f.dtype, device=f.device)
+            p_scale = float(units.cs ** 2 / units.characteristic_pressure_lu * units.characteristic_pressure_pu)
+            u_scale = float(units.characteristic_velocity_pu / units.characteristic_velocity_lu)
+            with torch.cuda.device(f.device):
+                nat.check(nat.lib().lb_output_fields(desc, f.data_ptr(), float(units.characteristic_density_lu),
+                                                     p_scale, u_scale, out.data_ptr(),
+                                                     nat.current_stream_ptr(f.device)))
+            return out
+        rho, u = self.rho_u(f)               # host tensors (set-up, tests): the reference's expressions
+        fields = torch.cat([self.units.convert_density_lu_to_pressure_pu(rho), self.units.convert_velocity_to_pu(u)])
+        return fields.permute(0, *range(d, 0, -1)).reshape(1 + d, -1)
+
     def rho_u(self, f: Optional[torch.Tensor] = None):
         """(rho, u) in lattice units from ONE pass over the populations (the output-side reporters
         need both; the reference computes them separately, _flow.py:136-172)"""

@@ -33,7 +33,7 @@ EXPORTED_SYMBOLS = (
     "lb_pack_streaming_mask", "lb_moments", "lb_initialize", "lb_obs_scratch_bytes", "lb_observables",
     "lb_enstrophy", "lb_run_host", "lb_stencil_q", "lb_bytes_per_update", "lb_vector_width",
     "lb_unpack_halo", "lb_zface_count", "lb_ipc_alloc", "lb_ipc_free", "lb_ipc_export",
-    "lb_ipc_open", "lb_ipc_close",
+    "lb_ipc_open", "lb_ipc_close", "lb_output_fields",
 )
 
 
@@ -98,6 +98,9 @@ def lib() -> C.CDLL:
     L.lb_stream.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.lb_pack_streaming_mask.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p]
     L.lb_moments.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.lb_output_fields.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_double, C.c_double, C.c_double,
+                                   C.c_void_p, C.c_void_p]
+    L.lb_output_fields.restype = C.c_int
     L.lb_initialize.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p,
                                 C.c_void_p]
     L.lb_obs_scratch_bytes.argtypes = [C.POINTER(LbDesc)]

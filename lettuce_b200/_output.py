@@ -4,10 +4,10 @@ EnergySpectrum (observable_reporter.py:71-137) and HDF5Reporter / LettuceDataset
 (util/datautils.py:16-160).
 
 What changes against the reference: the reporters never pull the populations to the host.  On a
-CUDA flow `flow.u_pu` / `flow.p_pu` come from the engine's moments kernel (lb_moments, 1 + d
-values per node instead of q), the fields are put into the file's point order ON THE DEVICE and
-cross PCIe once, into one pinned staging buffer; the bytes go to disk with a single write per
-array.  The `.vtr` container is written here (the reference delegates to pyevtk 1.6
+CUDA flow ONE kernel (lb_output_fields) reads the populations once and writes p and u in physical
+units, already in the file's point order (x fastest; tiles transposed through shared memory); the
+1 + d fields cross PCIe once, into one pinned staging buffer; the bytes go to disk with a single
+write per array.  The `.vtr` container is written here (the reference delegates to pyevtk 1.6
 `gridToVTK`, absent from this image): VTK XML RectilinearGrid, version 1.0, little endian,
 UInt64 block headers, raw appended data, coordinates first and then the point data in dict
 order, every array in x-fastest (Fortran) point order -- pyevtk's published layout.  Parity of
@@ -142,11 +142,7 @@ class VTKReporter(Reporter):
         if flow.i % self.interval != 0:
             return
         d = flow.stencil.d
-        rho, u = flow.rho_u()                                    # one pass over f (lb_moments)
-        fields = torch.cat([flow.units.convert_density_lu_to_pressure_pu(rho),
-                            flow.units.convert_velocity_to_pu(u)])   # [1 + d, *res], on the flow's device
-        # file order = x fastest: reverse the node axes on the device, then one copy to the host
-        ordered = fields.permute(0, *range(d, 0, -1)).reshape(1 + d, -1)
+        ordered = flow.output_fields_pu()      # [1 + d, nodes] in file order; one kernel on a CUDA flow
         stage = self._staging(1 + d, ordered.shape[1], ordered.dtype, ordered.is_cuda)
         stage.copy_(ordered)                                     # synchronous for a pinned destination
         flat = stage.numpy()

@@ -13,6 +13,7 @@
 #include "../../include/lettuce_b200.h"
 #include "lb_kernels.cuh"
 #include "lb_halo.cuh"
+#include "lb_output.cuh"
 
 namespace {
 
@@ -758,6 +759,37 @@ int lb_initialize(const lb_desc* desc, const void* rho, const void* u, int ghost
 
 }  // extern "C"
 
+namespace {
+template <class S, typename T>
+int output_typed(const Geometry& g, const void* f, double rho0, double p_scale, double u_scale, void* out,
+                 cudaStream_t st) {
+  lb::OutputParams<T> p{};
+  p.f = static_cast<const T*>(f);
+  p.out = static_cast<T*>(out);
+  p.nz = g.nz;
+  if (g.d == 2) { p.na = g.ny; p.nm = 1; }          // 2-D runs as X = 1: lattice x = kernel Y
+  else { p.na = g.nx; p.nm = g.ny; }
+  p.n_nodes = g.n_nodes;
+  p.rho0 = T(rho0);
+  p.p_scale = T(p_scale);
+  p.u_scale = T(u_scale);
+  cudaError_t e = lb::launch_output_fields<S, T>(p, st);
+  if (e != cudaSuccess) return fail(LB_ECUDA, "output kernel launch failed: %s", cudaGetErrorString(e));
+  return LB_OK;
+}
+
+template <typename T>
+int output_stencil(const lb_desc* d, const Geometry& g, const void* f, double rho0, double ps, double us, void* out,
+                   cudaStream_t st) {
+  switch (d->stencil) {
+    case LB_D2Q9: return output_typed<lb::D2Q9, T>(g, f, rho0, ps, us, out, st);
+    case LB_D3Q19: return output_typed<lb::D3Q19, T>(g, f, rho0, ps, us, out, st);
+    case LB_D3Q27: return output_typed<lb::D3Q27, T>(g, f, rho0, ps, us, out, st);
+  }
+  return fail(LB_EINVAL, "bad stencil");
+}
+}  // namespace
+
 extern "C" {
 
 int lb_moments(const lb_desc* desc, const void* f, void* rho_out, void* u_out, void* stream) {
@@ -768,6 +800,17 @@ int lb_moments(const lb_desc* desc, const void* f, void* rho_out, void* u_out, v
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   return desc->dtype == LB_F32 ? moments_stencil<float>(desc, g, f, rho_out, u_out, nullptr, nullptr, st)
                                : moments_stencil<double>(desc, g, f, rho_out, u_out, nullptr, nullptr, st);
+}
+
+int lb_output_fields(const lb_desc* desc, const void* f, double rho0, double p_scale, double u_scale, void* out,
+                     void* stream) {
+  Geometry g;
+  int rc = check_desc(desc, &g);
+  if (rc) return rc;
+  if (!f || !out) return fail(LB_EINVAL, "null pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return desc->dtype == LB_F32 ? output_stencil<float>(desc, g, f, rho0, p_scale, u_scale, out, st)
+                               : output_stencil<double>(desc, g, f, rho0, p_scale, u_scale, out, st);
 }
 
 int lb_observables(const lb_desc* desc, const void* f, int want_enstrophy, void* u_scratch,
