@@ -1,7 +1,8 @@
 """Cost of one VTK report on the GPU box: python scripts/bench_output.py [res] [reports]
 
 Times, for a D3Q19 fp32 Taylor-Green lattice of res^3 nodes (default 256),
-  device  : lb_moments (one pass over f) + PU conversion + reordering into file point order (CUDA events)
+  device  : lb_output_fields -- one pass over f: moments, PU conversion, reordering into file point order
+            (CUDA events); torch_route = the lb_moments + torch passes it replaced
   d2h     : the (1 + d) fields into the pinned staging buffer
   report  : a whole VTKReporter call (device + d2h + file write to a tmp directory)
   full_f  : what the reference's reporter path moves instead -- the populations to the host
@@ -28,6 +29,11 @@ d = 3
 
 
 def device_part():
+    return flow.output_fields_pu()            # lb_output_fields: one kernel
+
+
+def torch_route():
+    """what the kernel replaced: lb_moments + PU conversion + reordering with torch"""
     rho, u = flow.rho_u()
     fields = torch.cat([flow.units.convert_density_lu_to_pressure_pu(rho), flow.units.convert_velocity_to_pu(u)])
     return fields.permute(0, *range(d, 0, -1)).reshape(1 + d, -1)
@@ -46,6 +52,7 @@ def cuda_ms(fn, n):
 
 
 dev_ms, ordered = cuda_ms(device_part, 5)
+torch_ms, _ = cuda_ms(torch_route, 5)
 stage = torch.empty(ordered.shape, dtype=ordered.dtype, pin_memory=True)
 d2h_ms, _ = cuda_ms(lambda: stage.copy_(ordered, non_blocking=True), 5)
 host_f = torch.empty(flow.f.shape, dtype=flow.f.dtype, pin_memory=True)
@@ -64,7 +71,7 @@ with tempfile.TemporaryDirectory() as tmp:
 
 n = res ** 3
 print(json.dumps({"what": "one VTK report, D3Q19 fp32", "res": res, "nodes": n,
-                  "device_ms": round(dev_ms, 3), "d2h_ms": round(d2h_ms, 3), "report_ms": round(report_ms, 2),
+                  "device_ms": round(dev_ms, 3), "torch_route_ms": round(torch_ms, 3), "d2h_ms": round(d2h_ms, 3), "report_ms": round(report_ms, 2),
                   "file_bytes": size, "fields_bytes": int(stage.numel() * 4),
                   "full_f_d2h_ms": round(full_ms, 2), "full_f_bytes": int(flow.f.numel() * 4),
-                  "device_gbs": round((19 + 2 * 4 * 3) * 4 * n / dev_ms / 1e6, 1)}))
+                  "device_gbs": round((19 + 1 + d) * 4 * n / dev_ms / 1e6, 1)}))
