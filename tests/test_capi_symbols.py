@@ -65,6 +65,20 @@ def test_descriptor_validation_needs_no_gpu():
     assert b"Smagorinsky" in L.lb_last_error()
 
 
+def test_output_fields_validation_needs_no_gpu():
+    """lb_output_fields rejects bad descriptors / null buffers before any CUDA call"""
+    from lettuce_b200 import _native as nat
+    import torch
+    L = nat.lib()
+    d = nat.make_desc("D3Q19", torch.float32, [8, 8, 8])
+    assert L.lb_output_fields(d, None, 1.0, 1.0, 1.0, None, None) == -1
+    assert b"null pointer" in L.lb_last_error()
+    bad = nat.make_desc("D3Q19", torch.float32, [8, 8, 8])
+    bad.ndim = 2
+    assert L.lb_output_fields(bad, 1, 1.0, 1.0, 1.0, 1, None) == -1
+    assert b"ndim" in L.lb_last_error()
+
+
 def test_rank3_collision_descriptors():
     """host mirror of RegularizedCollision / SmagorinskyCollision (regularized_collision.py:14-19,
     smagorinsky_collision.py:13-18): constructor signatures and what reaches the kernel"""
