@@ -127,7 +127,7 @@ class VTKReporter(Reporter):
         self.filename_base = filename_base
         directory = os.path.dirname(filename_base)
         if directory and not os.path.isdir(directory):
-            os.mkdir(directory)
+            os.makedirs(directory, exist_ok=True)     # the reference's os.mkdir (:25-26), nested paths included
         self.point_dict = dict()
         self._stage = None     # pinned host staging buffer [1 + d, nodes]
 
