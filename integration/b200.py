@@ -184,6 +184,7 @@ def invoke(simulation):
     flow.f and flow.f_next swapped; no device-wide synchronisation (cf. _template.py:366)"""
     flow = simulation.flow
     d, fl, keep = build_call(simulation)
+    simulation._b200_keep = keep        # the boundary tensors stay alive while the launch is in flight
     rc = lib().lb_step(d, fl, 1, torch.cuda.current_stream().cuda_stream)
     if rc:
         raise RuntimeError(lib().lb_last_error().decode())

@@ -126,3 +126,55 @@ def test_outlet_direction_from_plane_index():
     for direction, want in (([1, 0, 0], 1), ([0, -1, 0], -2), ([0, 0, 1], 3), ([-1, 0, 0], -1)):
         b = lt.AntiBounceBackOutlet(direction, flow)
         assert b200._outlet_direction(b) == want == b.native_descriptor(flow)["direction"]
+
+
+def _gpu_case(name):
+    """(flow, collision) on the GPU from lettuce_b200's stock classes (the stub reads lettuce's class names)"""
+    c32 = lt.Context(device="cuda", dtype=torch.float32, use_native=True)
+    c64 = lt.Context(device="cuda", dtype=torch.float64, use_native=True)
+    if name == "obstacle2d_bgk":          # stock list: equilibrium inlet, anti-bounce-back outlet, bounce-back
+        f = lt.Obstacle(c64, [48, 24], reynolds_number=100, mach_number=0.05, domain_length_x=2)
+        m = np.zeros([48, 24], dtype=bool)
+        m[10:14, 9:15] = True
+        f.mask = m
+        return f, lt.BGKCollision(tau=f.units.relaxation_parameter_lu)
+    if name == "obstacle3d_kbc":
+        f = lt.Obstacle(c32, [24, 12, 8], reynolds_number=50, mach_number=0.05, domain_length_x=2, stencil=lt.D3Q27)
+        m = np.zeros([24, 12, 8], dtype=bool)
+        m[6:9, 4:8, 2:6] = True
+        f.mask = m
+        return f, lt.KBCCollision()
+    if name == "cavity_bgk":
+        f = lt.Cavity2D(c32, [24, 20], 100, 0.05)
+        return f, lt.BGKCollision(tau=f.units.relaxation_parameter_lu)
+    if name == "poiseuille_guo":
+        f = lt.PoiseuilleFlow2D(c64, 16, 10, 0.05)
+        tau = f.units.relaxation_parameter_lu
+        return f, lt.BGKCollision(tau=tau, force=lt.Guo(f, tau, f.acceleration))
+    f = lt.TaylorGreenVortex(c32, [16, 12, 20], 400, 0.1, stencil=lt.D3Q19)
+    return f, lt.TRTCollision(tau=f.units.relaxation_parameter_lu, tau_minus=0.8)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["obstacle2d_bgk", "obstacle3d_kbc", "cavity_bgk", "poiseuille_guo", "tgv_trt"])
+def test_stub_invoke_equals_simulation(name):
+    """b200.invoke(simulation), step by step through the stub's OWN ctypes structures, leaves bitwise the state
+    lt.Simulation(n) leaves (same library, same kernels): boundary records, packed streaming masks, outlets,
+    forces, f / f_next swapping over an odd number of steps"""
+    n = 7
+    fa, ca = _gpu_case(name)
+    fb, cb = _gpu_case(name)
+    assert torch.equal(fa.f, fb.f)
+    a = lt.Simulation(fa, ca, [])
+    b = lt.Simulation(fb, cb, [])            # only to borrow the masks / boundary order lettuce would build
+    a(n)
+    b200._lib = None
+    os.environ[b200.LIB_ENV] = nat.LIB_PATH
+    stub_sim = types.SimpleNamespace(flow=fb, collision=cb, boundaries=b.boundaries,
+                                     no_collision_mask=b.no_collision_mask, no_streaming_mask=b.no_streaming_mask)
+    with torch.cuda.device(fb.f.device):
+        for _ in range(n):
+            b200.invoke(stub_sim)
+    torch.cuda.synchronize()
+    assert torch.isfinite(fb.f).all()
+    assert torch.equal(fa.f, fb.f)
