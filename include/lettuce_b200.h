@@ -45,7 +45,7 @@ extern "C" {
 #define LB_API
 #endif
 
-#define LB_ABI_VERSION 5
+#define LB_ABI_VERSION 6
 #define LB_MAX_BOUNDARIES 8
 
 enum { LB_D2Q9 = 0, LB_D3Q19 = 1, LB_D3Q27 = 2 };                     /* lb_desc.stencil   */
@@ -152,6 +152,22 @@ typedef struct lb_boundary {
  *     recv_hi (peer_up_recv_lo / peer_down_recv_hi) and a one-block kernel does the handshake;
  *     received halos are consumed at load time and scattered once at the end of the call.
  *     No send buffers, no isolated remote stores: the transport that scales to 1024^2 faces.
+ * LB_HALO_LL      (default multi-GPU path) as REMOTE, but WITHOUT any handshake: every packed halo element
+ *     travels as a (payload, tag) pair written with one 8-byte store (fp64: two pairs in one 16-byte store),
+ *     tag = epoch + s + 1 for step s of the call -- the global index of the producing time step.  The
+ *     receiving step kernel loads its incoming elements together with its populations and re-polls only the
+ *     ones whose tag is not there yet, so there is no kernel between two steps, no flag, no fence, and no wait
+ *     on the critical path in the steady state.  Receive buffers are TRIPLE-buffered ([g % 3], g = the global
+ *     step index): a block that writes slot g % 3 at step g has seen a tag g-1 from that neighbour, i.e. the
+ *     neighbour has started step g-1 and therefore finished step g-2, the last reader of that slot's previous
+ *     contents.  recv_* / peer_*_recv_* hold LLWord elements: 8 bytes per fp32 value, 16 per fp64 value
+ *     (lb_halo_ll_bytes()).  The buffers must be zero before the first call (tag 0 is never sent), epoch = the
+ *     number of time steps taken so far; the caller advances epoch by n_steps.  wait_slots[2] is the error flag.
+ *
+ * Masked streaming (lb_fields.streaming_bits) works across slabs with every mode except LB_HALO_DIRECT: the
+ * sender always sends the element that crosses a z face, the RECEIVER drops it where its own node keeps the
+ * population (the destination mask of _simulation.py:171-174 is the receiver's), at load time and in
+ * lb_unpack_halo_ex().
  *
  * Handshake (PUSH, DIRECT, REMOTE): the rank stores the step counter into both neighbours' wait slots
  * (signal_up / signal_down, peer-mapped) and spins until both of its own slots reached it, so
@@ -159,24 +175,33 @@ typedef struct lb_boundary {
  * neighbour still reads.  A call performs n_steps + 1 handshakes with the values
  * epoch+1 .. epoch+n_steps+1; the caller advances epoch by n_steps + 1.  A wait that exceeds
  * ~10 s sets wait_slots[2] = 1 and gives up instead of hanging the GPU. */
-enum { LB_HALO_PACKED = 1, LB_HALO_PUSH = 2, LB_HALO_DIRECT = 3, LB_HALO_REMOTE = 4 };
+enum { LB_HALO_PACKED = 1, LB_HALO_PUSH = 2, LB_HALO_DIRECT = 3, LB_HALO_REMOTE = 4, LB_HALO_LL = 5 };
 
 typedef struct lb_halo {
   int32_t mode;
   uint32_t epoch;
   void* send_hi[2];            /* local packed send buffers                                 */
   void* send_lo[2];
-  void* recv_lo[2];            /* local: written by the -z neighbour (its hi face)          */
-  void* recv_hi[2];            /* local: written by the +z neighbour (its lo face)          */
-  void* peer_up_recv_lo[2];    /* peer-mapped: the +z neighbour's recv_lo                   */
-  void* peer_down_recv_hi[2];  /* peer-mapped: the -z neighbour's recv_hi                   */
+  void* recv_lo[3];            /* local: written by the -z neighbour (its hi face); [2] LL only */
+  void* recv_hi[3];            /* local: written by the +z neighbour (its lo face)          */
+  void* peer_up_recv_lo[3];    /* peer-mapped: the +z neighbour's recv_lo                   */
+  void* peer_down_recv_hi[3];  /* peer-mapped: the -z neighbour's recv_hi                   */
   void* peer_up_f[2];          /* DIRECT: +z neighbour's buffers matching f_next [0], f [1] */
   void* peer_down_f[2];
   uint32_t* signal_up;         /* peer-mapped: +z neighbour's wait_slots[0]                 */
   uint32_t* signal_down;       /* peer-mapped: -z neighbour's wait_slots[1]                 */
   uint32_t* wait_slots;        /* local [8]: [0] written by the -z neighbour, [1] by the +z
                                   neighbour, [2] timeout flag, [3] block counter (scratch)  */
+  uint32_t flags;              /* LB_HALO_LL only: LB_HALO_F_* (drivers that interleave the steps of
+                                  several slabs on ONE device, e.g. the single-GPU tests)   */
+  uint32_t _pad;
 } lb_halo;
+enum {
+  LB_HALO_F_NO_UNPACK = 1,     /* do not scatter the last received halo into f at the end of the call
+                                  (the caller does: lb_unpack_halo_ex with ll_tag = epoch + n_steps) */
+  LB_HALO_F_CONSUME_FIRST = 2  /* f is not canonical: the first step of the call consumes the halo of
+                                  tag `epoch` at load time, like every later step             */
+};
 
 typedef struct lb_fields {
   void* f;                          /* populations, state in / (n even) state out        */
@@ -248,7 +273,8 @@ LB_API int lb_initialize(const lb_desc* desc, const void* rho, const void* u, in
                   void* f, void* stream);
 
 /* Standalone reduction of LB_OBS_* over state f into obs_out[LB_OBS_COUNT] (device, double).
- * `want_enstrophy` != 0 additionally needs u_scratch [d][*res] of dtype. */
+ * `want_enstrophy` != 0 additionally needs u_scratch [d][*res] of dtype, which receives the velocity field;
+ * 1 also runs the enstrophy pass over it, 2 leaves that to the caller (lb_enstrophy / lb_enstrophy_slab). */
 LB_API size_t lb_obs_scratch_bytes(const lb_desc* desc);
 LB_API int lb_observables(const lb_desc* desc, const void* f, int want_enstrophy, void* u_scratch,
                    void* obs_scratch, double* obs_out, void* stream);
@@ -256,6 +282,11 @@ LB_API int lb_observables(const lb_desc* desc, const void* f, int want_enstrophy
 /* Enstrophy (lattice units, dx = 1) of a velocity field u [d][*res] (e.g. lb_fields.u_out)
  * into obs_out[LB_OBS_ENSTROPHY]. */
 LB_API int lb_enstrophy(const lb_desc* desc, const void* u, void* obs_scratch, double* obs_out, void* stream);
+/* The same over one z-slab: u is [d][*res_ext] with `ghost` (0 or >= 3) planes of the neighbouring slabs on
+ * both sides of the last axis (res_ext = res with res[d-1] + 2 ghost); the sum runs over the interior nodes.
+ * The slab driver fills the ghost planes (3-plane velocity halo) and adds the ranks' sums. */
+LB_API int lb_enstrophy_slab(const lb_desc* desc, const void* u_ext, int ghost, void* obs_scratch, double* obs_out,
+                      void* stream);
 
 /* Host-buffer convenience entry (end-to-end path): copies f_host -> device, runs n_steps,
  * copies the result back into f_host, synchronises.  masks / boundary arrays are HOST
@@ -268,6 +299,12 @@ LB_API int lb_run_host(const lb_desc* desc, void* f_host, const uint8_t* ncm_hos
 /* scatter packed halos received from the -z neighbour (its hi face -> our z = 0 plane) and the
  * +z neighbour (its lo face -> our z = nz-1 plane) into f; either may be NULL */
 LB_API int lb_unpack_halo(const lb_desc* desc, void* f, const void* from_down, const void* from_up, void* stream);
+/* the same with the receiver's packed no-streaming bits (elements whose population the node keeps are
+ * dropped; NULL = none) and, when ll_tag != 0, LLWord buffers: every element is polled until its tag equals
+ * ll_tag (bounded; *ll_err = 1 on timeout) */
+LB_API int lb_unpack_halo_ex(const lb_desc* desc, void* f, const void* from_down, const void* from_up,
+                      const uint32_t* streaming_bits, uint32_t ll_tag, uint32_t* ll_err, void* stream);
+LB_API size_t lb_halo_ll_bytes(const lb_desc* desc);   /* bytes of ONE LL receive buffer: zface * lines * word */
 LB_API int lb_zface_count(int stencil);  /* directions per z face: 3 / 5 / 9 */
 /* device memory that other processes of the node can map (cudaMalloc + CUDA IPC) */
 LB_API int lb_ipc_alloc(size_t bytes, void** dptr);

@@ -22,7 +22,7 @@ LB_FORCE_NONE, LB_FORCE_GUO, LB_FORCE_SHAN_CHEN = 0, 1, 2
 LB_BND_BOUNCE_BACK, LB_BND_EQUILIBRIUM, LB_BND_ABB_OUTLET, LB_BND_EQ_OUTLET_P = 1, 2, 3, 4
 LB_OBS_ENERGY, LB_OBS_MAXU2, LB_OBS_MASS, LB_OBS_ENSTROPHY, LB_OBS_COUNT = 0, 1, 2, 3, 4
 LB_MAX_BOUNDARIES = 8
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 STENCIL_IDS = {"D2Q9": LB_D2Q9, "D3Q19": LB_D3Q19, "D3Q27": LB_D3Q27}
 DTYPE_IDS = {torch.float32: LB_F32, torch.float64: LB_F64}
@@ -33,7 +33,8 @@ EXPORTED_SYMBOLS = (
     "lb_pack_streaming_mask", "lb_moments", "lb_initialize", "lb_obs_scratch_bytes", "lb_observables",
     "lb_enstrophy", "lb_run_host", "lb_stencil_q", "lb_bytes_per_update", "lb_vector_width",
     "lb_unpack_halo", "lb_zface_count", "lb_ipc_alloc", "lb_ipc_free", "lb_ipc_export",
-    "lb_ipc_open", "lb_ipc_close", "lb_output_fields",
+    "lb_ipc_open", "lb_ipc_close", "lb_output_fields", "lb_unpack_halo_ex", "lb_halo_ll_bytes",
+    "lb_enstrophy_slab",
 )
 
 
@@ -58,16 +59,20 @@ class LbBoundary(C.Structure):
                 ("u_comp_stride", C.c_int64), ("value", C.c_double)]
 
 
-LB_HALO_PACKED, LB_HALO_PUSH, LB_HALO_DIRECT, LB_HALO_REMOTE = 1, 2, 3, 4
+LB_HALO_PACKED, LB_HALO_PUSH, LB_HALO_DIRECT, LB_HALO_REMOTE, LB_HALO_LL = 1, 2, 3, 4, 5
 
 
 class LbHalo(C.Structure):
     _fields_ = [("mode", C.c_int32), ("epoch", C.c_uint32),
                 ("send_hi", C.c_void_p * 2), ("send_lo", C.c_void_p * 2),
-                ("recv_lo", C.c_void_p * 2), ("recv_hi", C.c_void_p * 2),
-                ("peer_up_recv_lo", C.c_void_p * 2), ("peer_down_recv_hi", C.c_void_p * 2),
+                ("recv_lo", C.c_void_p * 3), ("recv_hi", C.c_void_p * 3),
+                ("peer_up_recv_lo", C.c_void_p * 3), ("peer_down_recv_hi", C.c_void_p * 3),
                 ("peer_up_f", C.c_void_p * 2), ("peer_down_f", C.c_void_p * 2),
-                ("signal_up", C.c_void_p), ("signal_down", C.c_void_p), ("wait_slots", C.c_void_p)]
+                ("signal_up", C.c_void_p), ("signal_down", C.c_void_p), ("wait_slots", C.c_void_p),
+                ("flags", C.c_uint32), ("_pad", C.c_uint32)]
+
+
+LB_HALO_F_NO_UNPACK, LB_HALO_F_CONSUME_FIRST = 1, 2
 
 
 class LbFields(C.Structure):
@@ -111,6 +116,11 @@ def lib() -> C.CDLL:
     L.lb_run_host.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p,
                               C.POINTER(LbBoundary), C.c_int, C.c_int, C.c_void_p]
     L.lb_unpack_halo.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.lb_unpack_halo_ex.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32,
+                                    C.c_void_p, C.c_void_p]
+    L.lb_halo_ll_bytes.argtypes = [C.POINTER(LbDesc)]
+    L.lb_halo_ll_bytes.restype = C.c_size_t
+    L.lb_enstrophy_slab.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     L.lb_zface_count.argtypes = [C.c_int]
     L.lb_ipc_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
     L.lb_ipc_free.argtypes = [C.c_void_p]
@@ -123,7 +133,7 @@ def lib() -> C.CDLL:
     L.lb_vector_width.argtypes = [C.POINTER(LbDesc), C.c_int]
     for name in ("lb_step", "lb_collide", "lb_stream", "lb_pack_streaming_mask", "lb_moments", "lb_initialize",
                  "lb_observables", "lb_enstrophy", "lb_run_host", "lb_stencil_q", "lb_vector_width",
-                 "lb_unpack_halo", "lb_zface_count", "lb_ipc_alloc", "lb_ipc_free", "lb_ipc_export",
+                 "lb_unpack_halo", "lb_unpack_halo_ex", "lb_enstrophy_slab", "lb_zface_count", "lb_ipc_alloc", "lb_ipc_free", "lb_ipc_export",
                  "lb_ipc_open", "lb_ipc_close"):
         getattr(L, name).restype = C.c_int
     if L.lb_abi_version() != ABI_VERSION:

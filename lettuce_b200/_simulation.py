@@ -98,6 +98,11 @@ class Simulation:
         crosses the neighbour plane of another outlet: refuse that combination."""
         from ._boundary import AntiBounceBackOutlet
         outlets = [(i, b) for i, b in enumerate(self.boundaries[1:], start=1) if isinstance(b, AntiBounceBackOutlet)]
+        if outlets and getattr(self.collision, 'force', None) is not None:
+            # the reference's outlets read flow.u() AFTER the forced collision (momentum j + a); the kernel takes
+            # the neighbour's velocity from its incoming populations, which is only right without a force
+            raise NotImplementedError("outlet boundaries together with a forcing scheme are not supported by the "
+                                      "native kernel")
         for i, b in outlets:
             if min(self.flow.resolution) < 2:
                 raise ValueError("outlet boundaries need at least 2 nodes along every axis")
@@ -218,11 +223,17 @@ class Simulation:
     def _collide(self):
         desc = self._desc()
         flow = self.flow
+        from ._boundary import AntiBounceBackOutlet
+        # an outlet node reads every population of the node next to it: out of place then (lb_collide refuses aliasing)
+        out_of_place = any(isinstance(b, AntiBounceBackOutlet) for b in self.boundaries[1:])
         with torch.cuda.device(self.context.device):
             fl = self._fields(desc)
-            nat.check(nat.lib().lb_collide(desc, flow.f.data_ptr(), flow.f.data_ptr(),
+            out = flow.f_next if out_of_place else flow.f
+            nat.check(nat.lib().lb_collide(desc, flow.f.data_ptr(), out.data_ptr(),
                                            fl.no_collision_mask, fl.boundaries, fl.n_boundaries,
                                            nat.current_stream_ptr(self.context.device)))
+        if out_of_place:
+            flow.f, flow.f_next = flow.f_next, flow.f
         return flow.f
 
     def _stream(self):
@@ -271,6 +282,16 @@ class Simulation:
             n_nodes *= int(n)
         return num_steps * n_nodes / 1e6 / (end - beg)
 
+    def _enstrophy(self, desc, u_buf, obs_row):
+        """sum |curl u|^2 of the velocity field u_buf [d, *res] (lattice units) into obs_row[LB_OBS_ENSTROPHY];
+        the slab driver overrides this with the 3-plane velocity halo"""
+        dev = self.context.device
+        if min(self.flow.resolution) < 3:
+            raise NotImplementedError("Enstrophy needs at least 3 nodes per axis (6th-order periodic gradient)")
+        with torch.cuda.device(dev):
+            nat.check(nat.lib().lb_enstrophy(desc, u_buf.data_ptr(), self._obs_scratch.data_ptr(),
+                                             obs_row.data_ptr(), nat.current_stream_ptr(dev)))
+
     def _finalize_obs(self, obs: torch.Tensor) -> torch.Tensor:
         """device [n, LB_OBS_COUNT] -> host; the slab driver all-reduces across ranks here"""
         return obs.cpu()
@@ -313,9 +334,7 @@ class Simulation:
                 self._advance(m, obs_out=obs[row[cur]:row[cur] + m],
                               u_out=u_buf if last in need_u else None)
                 if last in need_u:
-                    with torch.cuda.device(dev):
-                        nat.check(L.lb_enstrophy(desc, u_buf.data_ptr(), self._obs_scratch.data_ptr(),
-                                                 obs[row[last]].data_ptr(), nat.current_stream_ptr(dev)))
+                    self._enstrophy(desc, u_buf, obs[row[last]])
                 cur += m
             else:
                 nxt = min([i for i in idx if i > cur] + [i1])
@@ -325,9 +344,12 @@ class Simulation:
             if self._obs_scratch is None:
                 self._obs_scratch = torch.empty(L.lb_obs_scratch_bytes(desc), dtype=torch.uint8, device=dev)
             with torch.cuda.device(dev):
-                nat.check(L.lb_observables(desc, flow.f.data_ptr(), int(i1 in need_u), nat.ptr(u_buf),
+                # want_enstrophy = 2: only fill u_buf; the enstrophy pass itself goes through the hook below
+                nat.check(L.lb_observables(desc, flow.f.data_ptr(), 2 if i1 in need_u else 0, nat.ptr(u_buf),
                                            self._obs_scratch.data_ptr(), obs[len(idx)].data_ptr(),
                                            nat.current_stream_ptr(dev)))
+            if i1 in need_u:
+                self._enstrophy(desc, u_buf, obs[len(idx)])
             row[i1] = len(idx)
         host = self._finalize_obs(obs)   # the one device->host sync of the segment
         flow.i = i1

@@ -120,29 +120,17 @@ int obs_prepare(const Geometry& g, void* scratch, lb::ObsScratch* out, cudaStrea
   return LB_OK;
 }
 
-// nodes per thread along the contiguous axis: the widest of 16 / 8 / 4(8) bytes that divides the
-// line and matches the buffers' alignment.  LB_VEC=<n> overrides the choice (tuning experiments).
-template <typename T>
-int vector_width(const lb_desc* d, const Geometry& g, const void* a, const void* b, const void* ncm, const void* sbits,
-                 bool scalar_only, bool masked_streaming) {
+// nodes per thread along the contiguous axis: the vector width compiled for this (stencil, dtype, collision,
+// mode) -- lb::vector_nodes -- when it divides the line and matches the buffers' alignment, else one.
+template <class S, typename T>
+int vector_width(int coll, int mode, const Geometry& g, const void* a, const void* b, const void* ncm, const void* sbits,
+                 bool scalar_only) {
   if (scalar_only) return 1;
-  const int widest = 16 / int(sizeof(T));
-  int cap = widest;
-  // D3Q27 KBC / TRT hold ~60 values per node in registers beside the populations: fp32 runs two nodes
-  // per thread as packed F2 values (<= 168 registers, three blocks per SM; measured 0.92 / 0.97 of the
-  // HBM roofline against 0.82 / 0.91 with four nodes), fp64 KBC one node per thread
-  if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_KBC) cap = (sizeof(T) == 4) ? 2 : 1;
-  if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_TRT && sizeof(T) == 4) cap = 2;
-  if (d->stencil == LB_D3Q27 && d->collision == LB_COLL_SMAGORINSKY && sizeof(T) == 4) cap = 2;   // measured 0.96 vs 0.91
-  // D3Q27 with masked streaming: 212 registers (2 blocks per SM) with four nodes, 161 (3 blocks) with two;
-  // measured 0.89 vs 0.92 on the stock obstacle
-  if (d->stencil == LB_D3Q27 && masked_streaming && sizeof(T) == 4 && cap > 2) cap = 2;
-  static const char* env = getenv("LB_VEC");
-  if (env && atoi(env) >= 1) cap = atoi(env) < widest ? atoi(env) : widest;
-  for (int v = cap; v > 1; v >>= 1)
-    if (g.nz % unsigned(v) == 0 && aligned_to(a, v * sizeof(T)) && aligned_to(b, v * sizeof(T)) &&
-        aligned_to(ncm, v) && aligned_to(sbits, v * sizeof(uint32_t)))
-      return v;
+  const int v = lb::vector_nodes<S, T>(coll, mode);
+  static const bool force_scalar = getenv("LB_VEC") != nullptr && atoi(getenv("LB_VEC")) == 1;   // A/B timing only
+  if (v > 1 && !force_scalar && g.nz % unsigned(v) == 0 && aligned_to(a, v * sizeof(T)) && aligned_to(b, v * sizeof(T)) &&
+      aligned_to(ncm, v) && aligned_to(sbits, v * sizeof(uint32_t)))
+    return v;
   return 1;
 }
 
@@ -219,6 +207,11 @@ int fill_boundaries(const lb_desc* d, const Geometry& g, const lb_boundary* b, i
       const unsigned n = o.axis == 0 ? g.nx : (o.axis == 1 ? g.ny : g.nz);
       if (n < 2) return fail(LB_EINVAL, "boundary %d: the outlet needs at least 2 planes along its axis", i);
       if (!p->ncm) return fail(LB_EINVAL, "boundary %d: outlet boundaries need no_collision_mask", i);
+      // the kernel takes the velocity next to the plane from the neighbour's INCOMING populations, which is
+      // only right when the collision conserves momentum; a forced collision adds the force's increment
+      // (the reference's outlets read flow.u() after it, anti_bounce_back_outlet.py:71-86)
+      if (d->force != LB_FORCE_NONE)
+        return fail(LB_EUNSUPPORTED, "boundary %d: outlet boundaries are not supported together with a forcing scheme", i);
       p->has_outlet = 1;
     }
     if (o.kind == LB_BND_EQUILIBRIUM && (!o.rho || !o.u))
@@ -245,14 +238,18 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   int rc = fill_boundaries<T>(d, g, fl->boundaries, fl->n_boundaries, &p);
   if (rc) return rc;
   if (p.sbits && !p.ncm) return fail(LB_EINVAL, "streaming_bits requires no_collision_mask (lettuce creates both, _simulation.py:71-75)");
+  // an outlet node reads ALL populations of the node next to it from f_in: in place, other threads would be
+  // overwriting them meanwhile
+  if (p.has_outlet && fl->f == fl->f_next)
+    return fail(LB_EINVAL, "outlet boundaries read neighbouring nodes: f_out must not alias f_in");
 
   lb::StepConfig c{};
   c.collision = (d->collision == LB_COLL_BGK && d->force != LB_FORCE_NONE) ? int(lb::COLL_BGK_FORCE) : d->collision;
   c.mode = p.sbits ? lb::MODE_NCM_SBITS : (p.ncm ? lb::MODE_NCM : lb::MODE_PLAIN);
   c.stream = do_stream;
   c.halo = fl->halo != nullptr;
-  c.vec = do_stream ? vector_width<T>(d, g, fl->f, fl->f_next, p.ncm, p.sbits, p.has_outlet && p.sbits == nullptr,
-                                         p.sbits != nullptr) : 1;
+  c.vec = do_stream ? vector_width<S, T>(c.collision, c.mode, g, fl->f, fl->f_next, p.ncm, p.sbits,
+                                            p.has_outlet && p.sbits == nullptr) : 1;
   p.nzv = g.nz / c.vec;
   p.n_threads = g.nx * g.ny * p.nzv;
   // an outlet on the far side of the slowest axis: its plane is the last tiles of the grid -> run them first
@@ -278,7 +275,9 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   const size_t face_elems = size_t(lb::zface_count<S>()) * g.nx * g.ny;
   if (h) {
     if (!do_stream) return fail(LB_EINVAL, "halo given to a collide-only call");
-    if (p.sbits) return fail(LB_EUNSUPPORTED, "masked streaming (no_streaming_mask) is not supported across slabs");
+    if (p.sbits && h->mode == LB_HALO_DIRECT)
+      return fail(LB_EUNSUPPORTED, "masked streaming (no_streaming_mask) across slabs needs a packed halo transport: "
+                                   "LB_HALO_DIRECT stores into planes whose no-streaming bits the sender does not have");
     static const bool debug_nosync = getenv("LB_DEBUG_HALO_NOSYNC") != nullptr;  // timing experiments only
     switch (h->mode) {
       case LB_HALO_PACKED:
@@ -299,6 +298,14 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
             return fail(LB_EINVAL, "LB_HALO_REMOTE needs both parities of the receive buffers, local and peer-mapped");
         if (!h->wait_slots || !h->signal_up || !h->signal_down) return fail(LB_EINVAL, "LB_HALO_REMOTE needs the handshake slots");
         halo_sync = !debug_nosync;
+        break;
+      case LB_HALO_LL:
+        for (int k = 0; k < 3; ++k)
+          if (!h->recv_lo[k] || !h->recv_hi[k] || !h->peer_up_recv_lo[k] || !h->peer_down_recv_hi[k])
+            return fail(LB_EINVAL, "LB_HALO_LL needs three receive buffers per face, local and peer-mapped");
+        if (!h->wait_slots) return fail(LB_EINVAL, "LB_HALO_LL needs wait_slots (error flag)");
+        p.halo_ll = 1;
+        p.ll_err = h->wait_slots + 2;
         break;
       case LB_HALO_DIRECT:
         if (!h->peer_up_f[0] || !h->peer_down_f[0] || (n_steps > 1 && (!h->peer_up_f[1] || !h->peer_down_f[1])))
@@ -358,7 +365,16 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
         p.halo_hi = static_cast<T*>(h->peer_up_f[k]); p.halo_lo = static_cast<T*>(h->peer_down_f[k]);
       } else {
         const int ks = h->mode == LB_HALO_PACKED ? 0 : k;
-        if (h->mode == LB_HALO_REMOTE) {   // straight into the neighbours' receive buffers
+        if (h->mode == LB_HALO_LL) {   // tagged words, slot = global step index mod 3
+          const uint32_t gs = h->epoch + uint32_t(s) + 1u;
+          p.halo_hi = static_cast<T*>(h->peer_up_recv_lo[gs % 3u]); p.halo_lo = static_cast<T*>(h->peer_down_recv_hi[gs % 3u]);
+          p.ll_tag_out = gs;
+          if (s > 0 || (h->flags & LB_HALO_F_CONSUME_FIRST)) {
+            p.halo_in_lo = static_cast<const T*>(h->recv_lo[(gs - 1u) % 3u]);
+            p.halo_in_hi = static_cast<const T*>(h->recv_hi[(gs - 1u) % 3u]);
+            p.ll_tag_in = gs - 1u;
+          }
+        } else if (h->mode == LB_HALO_REMOTE) {   // straight into the neighbours' receive buffers
           p.halo_hi = static_cast<T*>(h->peer_up_recv_lo[k]); p.halo_lo = static_cast<T*>(h->peer_down_recv_hi[k]);
         } else {
           p.halo_hi = static_cast<T*>(h->send_hi[ks]); p.halo_lo = static_cast<T*>(h->send_lo[ks]);
@@ -383,7 +399,7 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
       e = launch_obs_finish(p.obs, (p.n_threads + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK, p.obs_out, lb::N_OBS_PART, st);
       if (e != cudaSuccess) return fail(LB_ECUDA, "observable reduction launch failed: %s", cudaGetErrorString(e));
     }
-    if (h && h->mode != LB_HALO_PACKED) {
+    if (h && h->mode != LB_HALO_PACKED && h->mode != LB_HALO_LL) {
       const int k = s & 1;
       const bool push = h->mode == LB_HALO_PUSH;
       if (push || halo_sync) {
@@ -400,7 +416,13 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   if (h && (h->mode == LB_HALO_PUSH || h->mode == LB_HALO_REMOTE) && n_steps > 0) {
     // make the population buffer canonical again: scatter the last received halo into it
     const int k = (n_steps - 1) & 1;
-    rc = lb_unpack_halo(d, a, h->recv_lo[k], h->recv_hi[k], st);
+    rc = lb_unpack_halo_ex(d, a, h->recv_lo[k], h->recv_hi[k], p.sbits, 0u, nullptr, st);
+    if (rc) return fail(LB_ECUDA, "halo unpack launch failed");
+  }
+  if (h && h->mode == LB_HALO_LL && n_steps > 0 && !(h->flags & LB_HALO_F_NO_UNPACK)) {
+    // the same for the LL transport: this is the one place that WAITS for the neighbours (their last step)
+    const uint32_t gs = h->epoch + uint32_t(n_steps);
+    rc = lb_unpack_halo_ex(d, a, h->recv_lo[gs % 3u], h->recv_hi[gs % 3u], p.sbits, gs, h->wait_slots + 2, st);
     if (rc) return fail(LB_ECUDA, "halo unpack launch failed");
   }
   return LB_OK;
@@ -464,15 +486,19 @@ __global__ void mark_sbits_neighbourhood_kernel(uint32_t* bits, unsigned nx, uns
 // reference/lettuce/util/utility.py:37-99 (weights [-1/60, 3/20, -3/4, 3/4, -3/20, 1/60] on
 // roll shifts [+3, +2, +1, -1, -2, -3], i.e. on u[x-3] ... u[x+3]) and
 // observable_reporter.py:53-68.  u is [D][n_nodes] in lattice units, dx = 1.
+// `ghost` planes of the neighbouring z-slabs on both sides of the LAST axis make that axis non-periodic
+// (multi-GPU); every periodic axis needs n >= 3 (one wrap per tap), checked by the host.
 template <typename T>
-__device__ __forceinline__ T diff6(const T* __restrict__ u, unsigned base, unsigned i, unsigned n,
-                                   unsigned stride) {
-  // base = node index with the differentiated coordinate set to 0
+__device__ __forceinline__ T diff6(const T* __restrict__ u, size_t base, unsigned i, unsigned n, size_t stride,
+                                   bool periodic) {
+  // base = element index with the differentiated coordinate set to 0
   auto at = [&](int s) {
     int j = int(i) + s;
-    if (j < 0) j += int(n);
-    if (j >= int(n)) j -= int(n);
-    return u[base + unsigned(j) * stride];
+    if (periodic) {
+      if (j < 0) j += int(n);
+      if (j >= int(n)) j -= int(n);
+    }
+    return u[base + size_t(j) * stride];
   };
   return T(-1.0 / 60) * at(-3) + T(3.0 / 20) * at(-2) + T(-3.0 / 4) * at(-1) + T(3.0 / 4) * at(1) +
          T(-3.0 / 20) * at(2) + T(1.0 / 60) * at(3);
@@ -480,31 +506,39 @@ __device__ __forceinline__ T diff6(const T* __restrict__ u, unsigned base, unsig
 
 template <typename T, int D>
 __global__ void __launch_bounds__(lb::STEP_BLOCK)
-enstrophy_kernel(const T* __restrict__ u, unsigned n0, unsigned n1, unsigned n2, unsigned n_nodes,
+enstrophy_kernel(const T* __restrict__ u, unsigned n0, unsigned n1, unsigned n2, unsigned n_nodes, unsigned ghost,
                  lb::ObsScratch scratch, double* out) {
-  // lattice axes: D == 2 -> (n0, n1), D == 3 -> (n0, n1, n2); last is contiguous
+  // lattice axes: D == 2 -> (n0, n1), D == 3 -> (n0, n1, n2); last is contiguous and the only one with ghosts.
+  // One thread per INTERIOR node; u is [D][n_ext], n_ext = nodes of the extended slab.
   const unsigned tid = blockIdx.x * lb::STEP_BLOCK + threadIdx.x;
   double acc = 0.0;
   if (tid < n_nodes) {
-    const T* u0 = u;
-    const T* u1 = u + (size_t)n_nodes;
+    const bool per = ghost == 0;
     if constexpr (D == 2) {
-      const unsigned i0 = tid / n1, i1 = tid - i0 * n1;
-      const T d1u0 = diff6<T>(u0, i0 * n1, i1, n1, 1);        // d u0 / d y
-      const T d0u1 = diff6<T>(u1, i1, i0, n0, n1);            // d u1 / d x
+      const unsigned e1 = n1 + 2 * ghost;
+      const size_t n_ext = size_t(n0) * e1;
+      const T* u0 = u;
+      const T* u1 = u + n_ext;
+      const unsigned i0 = tid / n1, i1 = tid - i0 * n1 + ghost;
+      const T d1u0 = diff6<T>(u0, size_t(i0) * e1, i1, e1, 1, per);          // d u0 / d y
+      const T d0u1 = diff6<T>(u1, i1, i0, n0, e1, true);                     // d u1 / d x
       const T w = d1u0 - d0u1;
       acc = double(w * w);
     } else {
-      const T* u2 = u + 2 * (size_t)n_nodes;
+      const unsigned e2 = n2 + 2 * ghost;
+      const size_t n_ext = size_t(n0) * n1 * e2;
+      const T* u0 = u;
+      const T* u1 = u + n_ext;
+      const T* u2 = u + 2 * n_ext;
       const unsigned i0 = tid / (n1 * n2);
       const unsigned r = tid - i0 * n1 * n2;
-      const unsigned i1 = r / n2, i2 = r - i1 * n2;
-      const unsigned b0 = i1 * n2 + i2, s0 = n1 * n2;          // vary axis 0
-      const unsigned b1 = i0 * n1 * n2 + i2, s1 = n2;          // vary axis 1
-      const unsigned b2 = i0 * n1 * n2 + i1 * n2;              // vary axis 2
-      const T wz = diff6<T>(u0, b1, i1, n1, s1) - diff6<T>(u1, b0, i0, n0, s0);
-      const T wx = diff6<T>(u2, b1, i1, n1, s1) - diff6<T>(u1, b2, i2, n2, 1);
-      const T wy = diff6<T>(u0, b2, i2, n2, 1) - diff6<T>(u2, b0, i0, n0, s0);
+      const unsigned i1 = r / n2, i2 = r - i1 * n2 + ghost;
+      const size_t b0 = size_t(i1) * e2 + i2, s0 = size_t(n1) * e2;        // vary axis 0
+      const size_t b1 = size_t(i0) * n1 * e2 + i2, s1 = e2;                // vary axis 1
+      const size_t b2 = (size_t(i0) * n1 + i1) * e2;                       // vary axis 2
+      const T wz = diff6<T>(u0, b1, i1, n1, s1, true) - diff6<T>(u1, b0, i0, n0, s0, true);
+      const T wx = diff6<T>(u2, b1, i1, n1, s1, true) - diff6<T>(u1, b2, i2, e2, 1, per);
+      const T wy = diff6<T>(u0, b2, i2, e2, 1, per) - diff6<T>(u2, b0, i0, n0, s0, true);
       acc = double(wz * wz) + double(wx * wx + wy * wy);
     }
   }
@@ -530,9 +564,18 @@ int lb_vector_width(const lb_desc* d, int has_streaming_bits) {
   Geometry g;
   if (check_desc(d, &g)) return -1;
   static char dummy[16] __attribute__((aligned(16)));
-  const bool ms = has_streaming_bits != 0;
-  return d->dtype == LB_F64 ? vector_width<double>(d, g, dummy, dummy, nullptr, nullptr, false, ms)
-                            : vector_width<float>(d, g, dummy, dummy, nullptr, nullptr, false, ms);
+  const int coll = (d->collision == LB_COLL_BGK && d->force != LB_FORCE_NONE) ? int(lb::COLL_BGK_FORCE) : d->collision;
+  const int mode = has_streaming_bits ? lb::MODE_NCM_SBITS : lb::MODE_PLAIN;
+  auto w = [&](auto s, auto t) {
+    return vector_width<decltype(s), decltype(t)>(coll, mode, g, dummy, dummy, nullptr, nullptr, false);
+  };
+  const bool f64 = d->dtype == LB_F64;
+  switch (d->stencil) {
+    case LB_D2Q9: return f64 ? w(lb::D2Q9{}, double{}) : w(lb::D2Q9{}, float{});
+    case LB_D3Q19: return f64 ? w(lb::D3Q19{}, double{}) : w(lb::D3Q19{}, float{});
+    case LB_D3Q27: return f64 ? w(lb::D3Q27{}, double{}) : w(lb::D3Q27{}, float{});
+  }
+  return -1;
 }
 
 int lb_step(const lb_desc* desc, const lb_fields* fields, int n_steps, void* stream) {
@@ -614,19 +657,25 @@ int moments_stencil(const lb_desc* d, const Geometry& g, const void* f, void* r,
 }
 
 template <typename T>
-int enstrophy_typed(const lb_desc* d, const Geometry& g, const void* u, void* scratch, double* obs_out,
+int enstrophy_typed(const lb_desc* d, const Geometry& g, const void* u, int ghost, void* scratch, double* obs_out,
                     cudaStream_t st) {
+  // torch.roll wraps any size; the kernel wraps once per tap: every periodic axis needs >= 3 nodes
+  for (int a = 0; a < g.d; ++a)
+    if (d->dims[a] < 3 && !(a == g.d - 1 && ghost > 0))
+      return fail(LB_EUNSUPPORTED, "the 6th-order gradient of the enstrophy needs at least 3 nodes per axis (dims[%d] = %lld)",
+                  a, (long long)d->dims[a]);
+  if (ghost != 0 && ghost < 3) return fail(LB_EINVAL, "ghost = %d: must be 0 (periodic) or >= 3 (stencil radius)", ghost);
   lb::ObsScratch sc;
   const int rc = obs_prepare(g, scratch, &sc, st);
   if (rc) return rc;
   const unsigned grid = (g.n_nodes + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK;
   if (g.d == 2)
     enstrophy_kernel<T, 2><<<grid, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(u), (unsigned)d->dims[0],
-                                                           (unsigned)d->dims[1], 1u, g.n_nodes, sc, obs_out);
+                                                           (unsigned)d->dims[1], 1u, g.n_nodes, unsigned(ghost), sc, obs_out);
   else
     enstrophy_kernel<T, 3><<<grid, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(u), (unsigned)d->dims[0],
                                                            (unsigned)d->dims[1], (unsigned)d->dims[2],
-                                                           g.n_nodes, sc, obs_out);
+                                                           g.n_nodes, unsigned(ghost), sc, obs_out);
   LB_CUDA(cudaGetLastError());
   return LB_OK;
 }
@@ -824,19 +873,23 @@ int lb_observables(const lb_desc* desc, const void* f, int want_enstrophy, void*
   rc = desc->dtype == LB_F32
            ? moments_stencil<float>(desc, g, f, nullptr, want_enstrophy ? u_scratch : nullptr, obs_scratch, obs_out, st)
            : moments_stencil<double>(desc, g, f, nullptr, want_enstrophy ? u_scratch : nullptr, obs_scratch, obs_out, st);
-  if (rc || !want_enstrophy) return rc;
-  return desc->dtype == LB_F32 ? enstrophy_typed<float>(desc, g, u_scratch, obs_scratch, obs_out, st)
-                               : enstrophy_typed<double>(desc, g, u_scratch, obs_scratch, obs_out, st);
+  if (rc || want_enstrophy != 1) return rc;   // 2: the caller only wanted u_scratch filled
+  return desc->dtype == LB_F32 ? enstrophy_typed<float>(desc, g, u_scratch, 0, obs_scratch, obs_out, st)
+                               : enstrophy_typed<double>(desc, g, u_scratch, 0, obs_scratch, obs_out, st);
 }
 
-int lb_enstrophy(const lb_desc* desc, const void* u, void* obs_scratch, double* obs_out, void* stream) {
+int lb_enstrophy_slab(const lb_desc* desc, const void* u, int ghost, void* obs_scratch, double* obs_out, void* stream) {
   Geometry g;
   int rc = check_desc(desc, &g);
   if (rc) return rc;
   if (!u || !obs_scratch || !obs_out) return fail(LB_EINVAL, "null pointer");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  return desc->dtype == LB_F32 ? enstrophy_typed<float>(desc, g, u, obs_scratch, obs_out, st)
-                               : enstrophy_typed<double>(desc, g, u, obs_scratch, obs_out, st);
+  return desc->dtype == LB_F32 ? enstrophy_typed<float>(desc, g, u, ghost, obs_scratch, obs_out, st)
+                               : enstrophy_typed<double>(desc, g, u, ghost, obs_scratch, obs_out, st);
+}
+
+int lb_enstrophy(const lb_desc* desc, const void* u, void* obs_scratch, double* obs_out, void* stream) {
+  return lb_enstrophy_slab(desc, u, 0, obs_scratch, obs_out, stream);
 }
 
 }  // extern "C"

@@ -102,28 +102,47 @@ int launch_halo_push(const void* src_hi, void* dst_hi, const void* src_lo, void*
   return e == cudaSuccess ? 0 : -1;
 }
 
-// packed [zface][lines] -> f[q][line * nz + z_edge]
-template <class S, typename T>
-__global__ void unpack_halo_kernel(T* __restrict__ f, const T* __restrict__ from_down,
-                                   const T* __restrict__ from_up, unsigned lines, unsigned nz,
-                                   size_t n_nodes) {
+// packed [zface][lines] -> f[q][line * nz + z_edge].  sbits: the receiver's packed no-streaming bits -- an element
+// whose population the node keeps is dropped (destination-masked streaming, _simulation.py:171-174).  LL: the
+// buffers hold tagged words; every element is polled until its tag is `tag`.
+template <class S, typename T, bool LL>
+__global__ void unpack_halo_kernel(T* __restrict__ f, const void* __restrict__ from_down,
+                                   const void* __restrict__ from_up, const uint32_t* __restrict__ sbits,
+                                   unsigned lines, unsigned nz, size_t n_nodes, uint32_t tag, uint32_t* err) {
   const unsigned line = blockIdx.x * blockDim.x + threadIdx.x;
   if (line >= lines) return;
+  constexpr int NF = zface_count<S>();
+  T lo[NF], hi[NF];
+  if constexpr (LL) {
+    if (from_down) ll_gather<NF, T>(from_down, line, lines, tag, err, lo);
+    if (from_up) ll_gather<NF, T>(from_up, line, lines, tag, err, hi);
+  } else {
+#pragma unroll
+    for (int k = 0; k < NF; ++k) {
+      if (from_down) lo[k] = static_cast<const T*>(from_down)[size_t(k) * lines + line];
+      if (from_up) hi[k] = static_cast<const T*>(from_up)[size_t(k) * lines + line];
+    }
+  }
+  const uint32_t b_lo = sbits ? sbits[size_t(line) * nz] : 0u;
+  const uint32_t b_hi = sbits ? sbits[size_t(line) * nz + (nz - 1)] : 0u;
   static_for<S::Q>([&](auto qc) {
     constexpr int q = decltype(qc)::value;
     constexpr int ez = S::e(q, 2);
     if constexpr (ez == 1) {
-      if (from_down) f[q * n_nodes + size_t(line) * nz] = from_down[size_t(zface_index<S>(q)) * lines + line];
+      if (from_down && !((b_lo >> q) & 1u)) f[q * n_nodes + size_t(line) * nz] = lo[zface_index<S>(q)];
     } else if constexpr (ez == -1) {
-      if (from_up) f[q * n_nodes + size_t(line) * nz + (nz - 1)] = from_up[size_t(zface_index<S>(q)) * lines + line];
+      if (from_up && !((b_hi >> q) & 1u)) f[q * n_nodes + size_t(line) * nz + (nz - 1)] = hi[zface_index<S>(q)];
     }
   });
 }
 
 template <class S, typename T>
-int unpack_typed(void* f, const void* d, const void* u, unsigned lines, unsigned nz, size_t n, cudaStream_t st) {
-  unpack_halo_kernel<S, T><<<(lines + 255) / 256, 256, 0, st>>>(static_cast<T*>(f), static_cast<const T*>(d),
-                                                               static_cast<const T*>(u), lines, nz, n);
+int unpack_typed(void* f, const void* d, const void* u, const uint32_t* sbits, unsigned lines, unsigned nz, size_t n,
+                 uint32_t tag, uint32_t* err, cudaStream_t st) {
+  if (tag != 0u)
+    unpack_halo_kernel<S, T, true><<<(lines + 127) / 128, 128, 0, st>>>(static_cast<T*>(f), d, u, sbits, lines, nz, n, tag, err);
+  else
+    unpack_halo_kernel<S, T, false><<<(lines + 255) / 256, 256, 0, st>>>(static_cast<T*>(f), d, u, sbits, lines, nz, n, 0u, nullptr);
   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
@@ -140,8 +159,10 @@ int lb_zface_count(int stencil) {
   return -1;
 }
 
-int lb_unpack_halo(const lb_desc* d, void* f, const void* from_down, const void* from_up, void* stream) {
+int lb_unpack_halo_ex(const lb_desc* d, void* f, const void* from_down, const void* from_up, const uint32_t* sbits,
+                      uint32_t ll_tag, uint32_t* ll_err, void* stream) {
   if (!d || !f) return LB_EINVAL;
+  if (ll_tag != 0u && !ll_err) return LB_EINVAL;
   const bool two_d = d->stencil == LB_D2Q9;
   const unsigned nz = unsigned(two_d ? d->dims[1] : d->dims[2]);
   const unsigned lines = unsigned(two_d ? d->dims[0] : d->dims[0] * d->dims[1]);
@@ -149,15 +170,28 @@ int lb_unpack_halo(const lb_desc* d, void* f, const void* from_down, const void*
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   int rc = -1;
   if (d->dtype == LB_F32) {
-    if (d->stencil == LB_D2Q9) rc = lb::unpack_typed<lb::D2Q9, float>(f, from_down, from_up, lines, nz, n, st);
-    if (d->stencil == LB_D3Q19) rc = lb::unpack_typed<lb::D3Q19, float>(f, from_down, from_up, lines, nz, n, st);
-    if (d->stencil == LB_D3Q27) rc = lb::unpack_typed<lb::D3Q27, float>(f, from_down, from_up, lines, nz, n, st);
+    if (d->stencil == LB_D2Q9) rc = lb::unpack_typed<lb::D2Q9, float>(f, from_down, from_up, sbits, lines, nz, n, ll_tag, ll_err, st);
+    if (d->stencil == LB_D3Q19) rc = lb::unpack_typed<lb::D3Q19, float>(f, from_down, from_up, sbits, lines, nz, n, ll_tag, ll_err, st);
+    if (d->stencil == LB_D3Q27) rc = lb::unpack_typed<lb::D3Q27, float>(f, from_down, from_up, sbits, lines, nz, n, ll_tag, ll_err, st);
   } else if (d->dtype == LB_F64) {
-    if (d->stencil == LB_D2Q9) rc = lb::unpack_typed<lb::D2Q9, double>(f, from_down, from_up, lines, nz, n, st);
-    if (d->stencil == LB_D3Q19) rc = lb::unpack_typed<lb::D3Q19, double>(f, from_down, from_up, lines, nz, n, st);
-    if (d->stencil == LB_D3Q27) rc = lb::unpack_typed<lb::D3Q27, double>(f, from_down, from_up, lines, nz, n, st);
+    if (d->stencil == LB_D2Q9) rc = lb::unpack_typed<lb::D2Q9, double>(f, from_down, from_up, sbits, lines, nz, n, ll_tag, ll_err, st);
+    if (d->stencil == LB_D3Q19) rc = lb::unpack_typed<lb::D3Q19, double>(f, from_down, from_up, sbits, lines, nz, n, ll_tag, ll_err, st);
+    if (d->stencil == LB_D3Q27) rc = lb::unpack_typed<lb::D3Q27, double>(f, from_down, from_up, sbits, lines, nz, n, ll_tag, ll_err, st);
   }
   return rc == 0 ? LB_OK : LB_ECUDA;
+}
+
+int lb_unpack_halo(const lb_desc* d, void* f, const void* from_down, const void* from_up, void* stream) {
+  return lb_unpack_halo_ex(d, f, from_down, from_up, nullptr, 0u, nullptr, stream);
+}
+
+size_t lb_halo_ll_bytes(const lb_desc* d) {
+  if (!d) return 0;
+  const int nf = lb_zface_count(d->stencil);
+  if (nf < 0) return 0;
+  const bool two_d = d->stencil == LB_D2Q9;
+  const size_t lines = size_t(two_d ? d->dims[0] : d->dims[0] * d->dims[1]);
+  return size_t(nf) * lines * (d->dtype == LB_F64 ? 16 : 8);
 }
 
 int lb_ipc_alloc(size_t bytes, void** dptr) {

@@ -115,6 +115,14 @@ struct StepParams {
   unsigned halo_hi_off, halo_lo_off;
   int halo_compact;
   int halo_stage_shift;   // see step_body: 0 = isolated stores, else log2(slots per (face, population))
+  // "LL" transport (LB_HALO_LL): every packed halo element travels as (payload, tag) words written with ONE
+  // 8-byte store, tag = the global index of the time step that produced it.  The receiver's loads of the
+  // incoming halo see an element either complete or not at all, so the data is its own flag: no handshake
+  // kernel, no fences, no wait on the critical path (only the first blocks of a step ever re-poll).
+  // halo_in_* / halo_hi / halo_lo then point to LLWord<T> arrays instead of T arrays.
+  int halo_ll;
+  uint32_t ll_tag_in, ll_tag_out;
+  uint32_t* ll_err;       // set to 1 when a poll gives up (neighbour never delivered): state is then invalid
   // Block b of the grid works on tile (b + block_rot) mod grid.  The host rotates the tiles of an outlet
   // plane at the END of the lattice to the front: they run the long boundary path (neighbour loads,
   // masked stores), and as the last blocks of the grid that path was a tail of 6-9 us per step.
@@ -163,6 +171,67 @@ __device__ __forceinline__ uint32_t ld_mask(const uint8_t* p) {
   if constexpr (V == 4) return *reinterpret_cast<const uint32_t*>(p);
   else if constexpr (V == 2) return *reinterpret_cast<const uint16_t*>(p);
   else return *p;
+}
+
+// ---- LL halo words: (payload, tag) pairs with 8-byte single-copy atomicity (the protocol of NCCL's LL
+// algorithm: st/ld.volatile.global.v2/v4.u32 over NVLink peer mappings) ------------------------------
+template <typename T> struct LLWord;
+template <> struct LLWord<float> { using type = uint2; };    // {bits, tag}
+template <> struct LLWord<double> { using type = uint4; };   // {lo, tag, hi, tag}: two atomic halves
+
+__device__ __forceinline__ void ll_store(uint2* p, float v, uint32_t tag) {
+  asm volatile("st.volatile.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(tag) : "memory");
+}
+__device__ __forceinline__ void ll_store(uint4* p, double v, uint32_t tag) {
+  const unsigned long long b = (unsigned long long)__double_as_longlong(v);
+  asm volatile("st.volatile.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(uint32_t(b)), "r"(tag),
+               "r"(uint32_t(b >> 32)), "r"(tag) : "memory");
+}
+__device__ __forceinline__ bool ll_load(const uint2* p, uint32_t tag, float& v) {
+  uint32_t d, t;
+  asm volatile("ld.volatile.global.v2.u32 {%0, %1}, [%2];" : "=r"(d), "=r"(t) : "l"(p) : "memory");
+  v = __uint_as_float(d);
+  return t == tag;
+}
+__device__ __forceinline__ bool ll_load(const uint4* p, uint32_t tag, double& v) {
+  uint32_t d0, t0, d1, t1;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(d0), "=r"(t0), "=r"(d1), "=r"(t1) : "l"(p) : "memory");
+  v = __longlong_as_double((long long)(((unsigned long long)d1 << 32) | d0));
+  return t0 == tag && t1 == tag;
+}
+constexpr long long LL_TIMEOUT_CYCLES = 20000000000ll;   // ~10 s: far beyond any skew between ranks of one node
+
+// slow path of ll_gather, out of line so that it costs the step kernels no registers: poll until all n
+// elements carry `tag` (bounded: sets *err and gives up)
+template <typename W>
+__device__ __noinline__ void ll_wait(const W* src, size_t stride, int n, uint32_t tag, uint32_t* err) {
+  const long long t0 = clock64();
+  for (;;) {
+    bool ok = true;
+    for (int k = 0; k < n; ++k) {
+      typename std::conditional<sizeof(W) == 8, float, double>::type v;
+      ok &= ll_load(src + k * stride, tag, v);
+    }
+    if (ok) return;
+    if (clock64() - t0 > LL_TIMEOUT_CYCLES) { *err = 1u; return; }   // never hang the GPU
+    __nanosleep(100);
+  }
+}
+
+// NF tagged elements src[k * stride], k < NF, all loads in flight together; where a tag is not there yet (only
+// the first blocks of a step ever see that) wait out of line and load again
+template <int NF, typename T>
+__device__ __forceinline__ void ll_gather(const void* base, size_t index, size_t stride, uint32_t tag, uint32_t* err,
+                                          T (&out)[NF]) {
+  using W = typename LLWord<T>::type;
+  const W* src = static_cast<const W*>(base) + index;
+  bool ok = true;
+#pragma unroll
+  for (int k = 0; k < NF; ++k) ok &= ll_load(src + k * stride, tag, out[k]);
+  if (ok) return;
+  ll_wait<W>(src, stride, NF, tag, err);
+#pragma unroll
+  for (int k = 0; k < NF; ++k) ll_load(src + k * stride, tag, out[k]);
 }
 
 // (sum, max, sum) over the block; the result is valid in thread 0.  Fixed order: lanes by a
@@ -440,11 +509,18 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
   T hin[NF];
   const bool in_lo = HALO && (p.halo_in_lo != nullptr) && (zv == 0);
   const bool edge_in = HALO && (in_lo || ((p.halo_in_hi != nullptr) && (zv == nzv - 1)));
-  if (edge_in) {
-    const T* hsrc = (in_lo ? p.halo_in_lo : p.halo_in_hi) + line;
+  const bool edge_in2 = HALO && in_lo && (p.halo_in_hi != nullptr) && (nzv == 1);
+  if constexpr (HALO) {
     const size_t lines = size_t(nx) * ny;
+    if (edge_in) {
+      if (p.halo_ll) {
+        ll_gather<NF, T>(in_lo ? p.halo_in_lo : p.halo_in_hi, line, lines, p.ll_tag_in, p.ll_err, hin);
+      } else {
+        const T* hsrc = (in_lo ? p.halo_in_lo : p.halo_in_hi) + line;
 #pragma unroll
-    for (int k = 0; k < NF; ++k) hin[k] = hsrc[k * lines];
+        for (int k = 0; k < NF; ++k) hin[k] = hsrc[k * lines];
+      }
+    }
   }
 
   // ---- masked streaming (no_streaming_mask packed as one bit per population and node, p.sbits) ----
@@ -452,11 +528,13 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
   // (lb_pack_streaming_mask).  Loaded HERE with the populations; a warp none of whose nodes has it set --
   // almost all of them -- streams with the plain vector stores.
   constexpr bool SB = (MODE == MODE_NCM_SBITS) && STREAM;
-  [[maybe_unused]] uint32_t near_kept = 0;
+  [[maybe_unused]] uint32_t near_kept = 0, own_first = 0, own_last = 0;
   if constexpr (SB) {
     const Vec<uint32_t, V> ow = ld_vec<uint32_t, V>(p.sbits + node);
 #pragma unroll
     for (int k = 0; k < V; ++k) near_kept |= ow.v[k];
+    own_first = ow.v[0];
+    own_last = ow.v[V - 1];
   }
   [[maybe_unused]] auto kept = [](uint32_t bits, int q) { return ((bits >> q) & 1u) != 0u; };
 
@@ -472,18 +550,28 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
   }
   uint32_t mword = 0;
   if constexpr (MODE != MODE_PLAIN) mword = ld_mask<V>(p.ncm + node);
+  // a received element is dropped where the node keeps its own value of that population (the sender does not
+  // know the receiver's no-streaming bits: it always sends, the destination decides -- _simulation.py:171-174)
   if (edge_in) {
     static_for<Q>([&](auto qc) {
       constexpr int q = decltype(qc)::value;
-      if constexpr (S::e(q, 2) == 1) { if (in_lo) f[q][0] = hin[zface_index<S>(q)]; }
-      if constexpr (S::e(q, 2) == -1) { if (!in_lo) f[q][V - 1] = hin[zface_index<S>(q)]; }
+      if constexpr (S::e(q, 2) == 1) { if (in_lo && !(SB && kept(own_first, q))) f[q][0] = hin[zface_index<S>(q)]; }
+      if constexpr (S::e(q, 2) == -1) { if (!in_lo && !(SB && kept(own_last, q))) f[q][V - 1] = hin[zface_index<S>(q)]; }
     });
-    if (p.halo_in_hi != nullptr && in_lo && nzv == 1) {   // one-vector lines: both faces in one thread
-      static_for<Q>([&](auto qc) {
-        constexpr int q = decltype(qc)::value;
-        if constexpr (S::e(q, 2) == -1) f[q][V - 1] = p.halo_in_hi[zface_index<S>(q) * size_t(nx) * ny + line];
-      });
+  }
+  if (edge_in2) {   // one-vector lines (nzv == 1): the thread is on both faces (rare: loaded here, not up front)
+    T hin2[NF];
+    const size_t lines = size_t(nx) * ny;
+    if (p.halo_ll) {
+      ll_gather<NF, T>(p.halo_in_hi, line, lines, p.ll_tag_in, p.ll_err, hin2);
+    } else {
+#pragma unroll
+      for (int k = 0; k < NF; ++k) hin2[k] = p.halo_in_hi[k * lines + line];
     }
+    static_for<Q>([&](auto qc) {
+      constexpr int q = decltype(qc)::value;
+      if constexpr (S::e(q, 2) == -1) { if (!(SB && kept(own_last, q))) f[q][V - 1] = hin2[zface_index<S>(q)]; }
+    });
   }
 
   T acc_e = T(0), acc_mass = T(0), acc_m2 = T(0);   // per-thread partials over V nodes; widened below
@@ -579,6 +667,11 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
     const bool staged = HALO && V > 1 && sshift != 0u;
     const unsigned first_line_blk = (blk * unsigned(STEP_BLOCK)) / nzv;
     [[maybe_unused]] const unsigned lline = line - first_line_blk;
+    // one halo element to the neighbour (or the local send buffer): a plain store, or a tagged LL word
+    [[maybe_unused]] auto halo_store = [&](T* base, long long index, T val) {
+      if (p.halo_ll) ll_store(reinterpret_cast<typename LLWord<T>::type*>(base) + index, val, p.ll_tag_out);
+      else base[index] = val;
+    };
 
     // The masked variant of the loop below (element-by-element stores under the no-streaming bits) is a
     // SECOND copy of the code, entered by whole warps: a warp none of whose lanes saw a set bit -- almost
@@ -628,6 +721,33 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
       [[maybe_unused]] const unsigned idx = dline + z0;  // this thread's vector in the destination line
       T* const bq = f_out + size_t(q) * N;               // uniform
 
+      // The ONE element of this thread that leaves its vector upwards (ez = +1) / downwards (ez = -1): into the
+      // next lane's vector, around the line end (periodic lattice), or -- z-slabs -- through the slab's z face to
+      // the neighbour rank.  `local_ok` = the destination node does not keep its own value (masked streaming).
+      // A z-face element is ALWAYS sent: the receiver drops it where its node keeps the population.
+      [[maybe_unused]] auto push_edge = [&](T val, bool up, bool local_ok) {
+        constexpr int zf = zface_index<S>(q);
+        const bool cross = HALO && (up ? (last_in_line && p.halo_hi != nullptr) : (first_in_line && p.halo_lo != nullptr));
+        if constexpr (HALO) {
+          if (cross) {
+            if (staged) {
+              const unsigned slot = (unsigned((up ? 0 : NF) + zf) << sshift) | lline;
+              stage_val[slot] = val;
+              stage_dst[slot] = dlines;
+            } else {
+              halo_store(up ? p.halo_hi : p.halo_lo,
+                         (long long)(p.halo_compact ? zf : q) * p.halo_qs + (long long)(dlines) * p.halo_ls +
+                             (up ? p.halo_hi_off : p.halo_lo_off), val);
+            }
+          }
+        }
+        // Packed layouts: ALSO store to the local wrap position.  The value there is never read (the
+        // neighbour's element is consumed from the receive buffer at load time and scattered at the end
+        // of the call), but without it the boundary sector of every line stays partially written, and
+        // every partially written sector costs a read-modify-write in HBM (measured: 10 % of a step).
+        if ((!cross || p.halo_compact) && local_ok) bq[idx + (up ? d_up : d_dn)] = val;
+      };
+
       if constexpr (MASKED && q != 0) {
         // own values that streaming must not overwrite (the destination tests below keep every other
         // thread from writing there)
@@ -652,8 +772,7 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
         }
       } else if constexpr (MASKED && q != 0 && V == 1) {
         // one node per thread: its destination is the "edge" element (d_up = 1 or the wrap)
-        if constexpr (ez > 0) { if (active && !kept(edge_m_up, q)) bq[idx + d_up] = f[q][0]; }
-        else { if (active && !kept(edge_m_dn, q)) bq[idx + d_dn] = f[q][0]; }
+        if (active) push_edge(f[q][0], ez > 0, !kept(ez > 0 ? edge_m_up : edge_m_dn, q));
       } else if constexpr (MASKED && q != 0 && ez > 0) {
         const T up = __shfl_up_sync(0xffffffffu, f[q][V - 1], 1);
         Vec<T, V> v;
@@ -667,7 +786,7 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
           for (int k = 0; k < V; ++k)
             if ((k > 0 || has_left) && !kept(dst_m[k], q)) bq[idx + k] = v.v[k];
         }
-        if (edge_up && !kept(edge_m_up, q)) bq[idx + d_up] = f[q][V - 1];
+        if (edge_up) push_edge(f[q][V - 1], true, !kept(edge_m_up, q));
       } else if constexpr (MASKED && q != 0) {
         const T dn = __shfl_down_sync(0xffffffffu, f[q][0], 1);
         Vec<T, V> v;
@@ -681,22 +800,14 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
           for (int k = 0; k < V; ++k)
             if ((k < V - 1 || has_right) && !kept(dst_m[k], q)) bq[idx + k] = v.v[k];
         }
-        if (edge_dn && !kept(edge_m_dn, q)) bq[idx + d_dn] = f[q][0];
+        if (edge_dn) push_edge(f[q][0], false, !kept(edge_m_dn, q));
       } else if constexpr (ez == 0) {
         Vec<T, V> v;
 #pragma unroll
         for (int k = 0; k < V; ++k) v.v[k] = f[q][k];
         if (active) st_vec<T, V>(bq + idx, v);
       } else if constexpr (V == 1) {
-        const bool crosses = (ez > 0) ? (z0 + 1 == nz) : (z0 == 0);
-        const unsigned zd = (ez > 0) ? (crosses ? 0u : z0 + 1) : (crosses ? nz - 1 : z0 - 1);
-        if (active) {
-          T* hp = (ez > 0) ? p.halo_hi : p.halo_lo;
-          if (HALO && crosses && hp != nullptr)
-            hp[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs + (long long)(dlines) * p.halo_ls +
-               ((ez > 0) ? p.halo_hi_off : p.halo_lo_off)] = f[q][0];
-          if (!(HALO && crosses && hp != nullptr) || p.halo_compact) bq[dline + zd] = f[q][0];
-        }
+        if (active) push_edge(f[q][0], ez > 0, true);
       } else if constexpr (ez > 0) {
         // destination z0+k takes the source value of z0+k-1: element 0 comes from the left lane
         const T up = __shfl_up_sync(0xffffffffu, f[q][V - 1], 1);
@@ -708,22 +819,7 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
 #pragma unroll
         for (int k = 1; k < V; ++k)
           if (st_noleft) bq[idx + k] = f[q][k - 1];
-        if (edge_up) {
-          if (HALO && last_in_line && p.halo_hi != nullptr) {
-            if (staged) {
-              stage_val[(unsigned(zface_index<S>(q)) << sshift) | lline] = f[q][V - 1];
-              stage_dst[(unsigned(zface_index<S>(q)) << sshift) | lline] = dlines;
-            } else {
-              p.halo_hi[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs + (long long)(dlines) * p.halo_ls +
-                        p.halo_hi_off] = f[q][V - 1];
-            }
-          }
-          // Packed layouts: ALSO store to the local wrap position.  The value there is never read (the
-          // neighbour's element is consumed from the receive buffer at load time and scattered at the end
-          // of the call), but without it the boundary sector of every line stays partially written, and
-          // every partially written sector costs a read-modify-write in HBM (measured: 10 % of a step).
-          if (!(HALO && last_in_line && p.halo_hi != nullptr) || p.halo_compact) bq[idx + d_up] = f[q][V - 1];
-        }
+        if (edge_up) push_edge(f[q][V - 1], true, true);
       } else {
         // ez < 0: destination z0+k takes the source value of z0+k+1
         const T dn = __shfl_down_sync(0xffffffffu, f[q][0], 1);
@@ -735,18 +831,7 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
 #pragma unroll
         for (int k = 0; k < V - 1; ++k)
           if (st_noright) bq[idx + k] = f[q][k + 1];
-        if (edge_dn) {
-          if (HALO && first_in_line && p.halo_lo != nullptr) {
-            if (staged) {
-              stage_val[(unsigned(NF + zface_index<S>(q)) << sshift) | lline] = f[q][0];
-              stage_dst[(unsigned(NF + zface_index<S>(q)) << sshift) | lline] = dlines;
-            } else {
-              p.halo_lo[(p.halo_compact ? zface_index<S>(q) : q) * p.halo_qs + (long long)(dlines) * p.halo_ls +
-                        p.halo_lo_off] = f[q][0];
-            }
-          }
-          if (!(HALO && first_in_line && p.halo_lo != nullptr) || p.halo_compact) bq[idx + d_dn] = f[q][0];
-        }
+        if (edge_dn) push_edge(f[q][0], false, true);
       }
     });
     };
@@ -769,8 +854,8 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
           const unsigned long long owner = (unsigned long long)(first_line_blk + j) * nzv + (face == 0 ? nzv - 1u : 0u);
           T* const base = (face == 0) ? p.halo_hi : p.halo_lo;
           if (owner >= t0 && owner < t1 && base != nullptr)
-            base[k * p.halo_qs + (long long)(stage_dst[e]) * p.halo_ls +
-                 (face == 0 ? p.halo_hi_off : p.halo_lo_off)] = stage_val[e];
+            halo_store(base, k * p.halo_qs + (long long)(stage_dst[e]) * p.halo_ls +
+                                 (face == 0 ? p.halo_hi_off : p.halo_lo_off), stage_val[e]);
         }
       }
     }
@@ -840,33 +925,49 @@ struct MomentsParams {
   double* obs_out;  // nullptr: no reduction
 };
 
-template <class S, typename T, bool OBS>
+// V consecutive nodes per thread (16-byte loads and stores, like the step kernel): Q * V * sizeof(T) bytes in
+// flight per thread instead of Q scalars
+template <class S, typename T, int V, bool OBS>
 __global__ void __launch_bounds__(STEP_BLOCK)
 moments_kernel(const __grid_constant__ MomentsParams<T> p) {
+  const unsigned n_threads = p.n_nodes / V;
   const unsigned tid = blockIdx.x * STEP_BLOCK + threadIdx.x;
-  const bool active = tid < p.n_nodes;
-  const unsigned node = active ? tid : p.n_nodes - 1u;
+  const bool active = tid < n_threads;
+  const unsigned node = (active ? tid : n_threads - 1u) * V;
   const size_t N = p.n_nodes;
-  T g[S::Q];
+  T g[S::Q][V];
   static_for<S::Q>([&](auto qc) {
     constexpr int q = decltype(qc)::value;
-    g[q] = p.f[q * N + node];
+    const Vec<T, V> v = ld_vec<T, V>(p.f + q * N + node);
+#pragma unroll
+    for (int k = 0; k < V; ++k) g[q][k] = v.v[k];
   });
-  T rho, u[3];
-  moments<S, T>(g, rho, u);
+  Vec<T, V> rho, u[3];
+  T acc_e = T(0), acc_m2 = T(0), acc_mass = T(0);
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    T h[S::Q], r, uu[3];
+    static_for<S::Q>([&](auto qc) { h[decltype(qc)::value] = g[decltype(qc)::value][k]; });
+    moments<S, T>(h, r, uu);
+    rho.v[k] = r;
+    u[0].v[k] = uu[0]; u[1].v[k] = uu[1]; u[2].v[k] = uu[2];
+    if constexpr (OBS) {
+      const T u2 = fma_(uu[0], uu[0], fma_(uu[1], uu[1], uu[2] * uu[2]));
+      acc_e += T(0.5) * u2;
+      acc_m2 = max_(acc_m2, u2);
+      acc_mass += r;
+    }
+  }
   if (active) {
-    if (p.rho_out) p.rho_out[node] = rho;
+    if (p.rho_out) st_vec<T, V>(p.rho_out + node, rho);
     if (p.u_out) {
 #pragma unroll
-      for (int c = 0; c < S::D; ++c) p.u_out[c * N + node] = u[S::axis(c)];
+      for (int c = 0; c < S::D; ++c) st_vec<T, V>(p.u_out + c * N + node, u[S::axis(c)]);
     }
   }
   if constexpr (OBS) {
-    const T u2 = fma_(u[0], u[0], fma_(u[1], u[1], u[2] * u[2]));
-    double e = active ? double(T(0.5) * u2) : 0.0;
-    double m2 = active ? double(u2) : 0.0;
-    double mass = active ? double(rho) : 0.0;
-    reduce_observables<STEP_BLOCK>(e, m2, mass, p.obs, p.obs_out);
+    if (!active) { acc_e = T(0); acc_m2 = T(0); acc_mass = T(0); }
+    reduce_observables<STEP_BLOCK>(double(acc_e), double(acc_m2), double(acc_mass), p.obs, p.obs_out);
   }
 }
 
@@ -875,9 +976,19 @@ cudaError_t launch_moments(const MomentsParams<T>& p, cudaStream_t st);
 
 template <class S, typename T>
 cudaError_t launch_moments_impl(const MomentsParams<T>& p, cudaStream_t st) {
-  const unsigned grid = (p.n_nodes + STEP_BLOCK - 1) / STEP_BLOCK;
-  if (p.obs_out) moments_kernel<S, T, true><<<grid, STEP_BLOCK, 0, st>>>(p);
-  else moments_kernel<S, T, false><<<grid, STEP_BLOCK, 0, st>>>(p);
+  constexpr int VEC = 16 / int(sizeof(T));
+  auto aligned = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
+  const bool vec = p.n_nodes % VEC == 0 && aligned(p.f) && aligned(p.rho_out) && aligned(p.u_out) &&
+                   (size_t(p.n_nodes) * sizeof(T)) % 16 == 0;
+  const unsigned n_threads = vec ? p.n_nodes / VEC : p.n_nodes;
+  const unsigned grid = (n_threads + STEP_BLOCK - 1) / STEP_BLOCK;
+  if (vec) {
+    if (p.obs_out) moments_kernel<S, T, VEC, true><<<grid, STEP_BLOCK, 0, st>>>(p);
+    else moments_kernel<S, T, VEC, false><<<grid, STEP_BLOCK, 0, st>>>(p);
+  } else {
+    if (p.obs_out) moments_kernel<S, T, 1, true><<<grid, STEP_BLOCK, 0, st>>>(p);
+    else moments_kernel<S, T, 1, false><<<grid, STEP_BLOCK, 0, st>>>(p);
+  }
   return cudaGetLastError();
 }
 
@@ -916,6 +1027,24 @@ cudaError_t launch_step(StepConfig& c, const StepParams<T>& p, cudaStream_t st) 
   return cudaErrorInvalidValue;
 }
 
+// Nodes per thread along the contiguous axis that are COMPILED for (stencil, dtype, collision, mode): one
+// node per thread (any shape, any alignment) and one vector width -- 16 bytes, except where the register
+// budget says otherwise (measured):
+//   D3Q27 KBC / TRT / Smagorinsky hold ~60 values per node beside the populations: fp32 runs two nodes per
+//     thread as packed F2 values (<= 168 registers, three blocks per SM; 0.92 / 0.97 / 0.96 of the HBM
+//     roofline against 0.82 / 0.91 / 0.91 with four nodes), fp64 KBC one node per thread;
+//   D3Q27 with masked streaming: 212 registers (2 blocks per SM) with four nodes, 161 (3 blocks) with two;
+//     0.89 vs 0.92 on the stock obstacle.
+// Lines whose length or alignment does not fit the vector run one node per thread.
+template <class S, typename T>
+__host__ __device__ constexpr int vector_nodes(int coll, int mode) {
+  int v = 16 / int(sizeof(T));
+  if (S::Q == 27 && coll == COLL_KBC) v = (sizeof(T) == 4) ? 2 : 1;
+  if (S::Q == 27 && sizeof(T) == 4 && (coll == COLL_TRT || coll == COLL_SMAGORINSKY)) v = 2;
+  if (S::Q == 27 && sizeof(T) == 4 && mode == MODE_NCM_SBITS && v > 2) v = 2;
+  return v;
+}
+
 // blocks of a kernel that fit on the device at once (cached per instantiation)
 template <class K>
 int coresident_blocks(K kernel) {
@@ -939,7 +1068,7 @@ cudaError_t launch_one(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   if (c.loop_steps > 1) {
     // request for ONE launch covering loop_steps steps: honoured if the grid is co-resident, otherwise
     // nothing is launched and the caller (c.looped == false) issues one launch per step
-    if constexpr (STREAM && !HALO) {
+    if constexpr (STREAM && !HALO && V > 1) {
       auto kernel = step_loop_kernel<S, T, V, COLL, MODE, OBS>;
       if (int(grid) <= coresident_blocks(kernel)) {
         int n_loop = c.loop_steps;
@@ -974,44 +1103,47 @@ cudaError_t launch_mode(StepConfig& c, const StepParams<T>& p, cudaStream_t st) 
       return cudaErrorInvalidValue;
   }
   if (c.halo) {
-    if constexpr (MODE != MODE_NCM_SBITS) {
-      if (c.obs) return launch_one<S, T, V, COLL, MODE, true, true, true>(c, p, st);
-      return launch_one<S, T, V, COLL, MODE, false, true, true>(c, p, st);
-    } else {
-      return cudaErrorNotSupported;
-    }
+    if (c.obs) return launch_one<S, T, V, COLL, MODE, true, true, true>(c, p, st);
+    return launch_one<S, T, V, COLL, MODE, false, true, true>(c, p, st);
   }
   if (c.obs) return launch_one<S, T, V, COLL, MODE, true, true, false>(c, p, st);
   return launch_one<S, T, V, COLL, MODE, false, true, false>(c, p, st);
 }
 
-template <class S, typename T, int V, int COLL>
+template <class S, typename T, int COLL, int MODE>
 cudaError_t launch_vec(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
-  switch (c.mode) {
-    case MODE_PLAIN: return launch_mode<S, T, V, COLL, MODE_PLAIN>(c, p, st);
-    case MODE_NCM: return launch_mode<S, T, V, COLL, MODE_NCM>(c, p, st);
-    case MODE_NCM_SBITS: return launch_mode<S, T, V, COLL, MODE_NCM_SBITS>(c, p, st);
+  constexpr int VEC = vector_nodes<S, T>(COLL, MODE);
+  if (c.vec == 1) return launch_mode<S, T, 1, COLL, MODE>(c, p, st);
+  if constexpr (VEC > 1) {
+    if (c.vec == VEC) return launch_mode<S, T, VEC, COLL, MODE>(c, p, st);
   }
   return cudaErrorInvalidValue;
 }
 
 template <class S, typename T, int COLL>
 cudaError_t launch_step_coll_impl(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
-  constexpr int VEC = 16 / sizeof(T);
-  if (c.vec == 1) return launch_vec<S, T, 1, COLL>(c, p, st);
-  if (c.vec == VEC) return launch_vec<S, T, VEC, COLL>(c, p, st);
-  if constexpr (VEC == 4) {
-    if (c.vec == 2) return launch_vec<S, T, 2, COLL>(c, p, st);   // 64-bit accesses: nz % 4 == 2
+  switch (c.mode) {
+    case MODE_PLAIN: return launch_vec<S, T, COLL, MODE_PLAIN>(c, p, st);
+    case MODE_NCM: return launch_vec<S, T, COLL, MODE_NCM>(c, p, st);
+    case MODE_NCM_SBITS: return launch_vec<S, T, COLL, MODE_NCM_SBITS>(c, p, st);
   }
   return cudaErrorInvalidValue;
 }
 
+#if defined(LB_STUB)   // development builds (Makefile, DEV=...): this unit's kernels are left out
+#define LB_INSTANTIATE_COLL(S, T, COLL)                                                   \
+  template <>                                                                             \
+  cudaError_t lb::launch_step_coll<S, T, COLL>(StepConfig&, const StepParams<T>&, cudaStream_t) { \
+    return cudaErrorNotSupported;                                                         \
+  }
+#else
 #define LB_INSTANTIATE_COLL(S, T, COLL)                                                   \
   template <>                                                                             \
   cudaError_t lb::launch_step_coll<S, T, COLL>(StepConfig& c, const StepParams<T>& p,       \
                                                cudaStream_t st) {                         \
     return launch_step_coll_impl<S, T, COLL>(c, p, st);                                   \
   }
+#endif
 
 #define LB_INSTANTIATE_MOMENTS(S, T)                                                      \
   template <>                                                                             \

@@ -17,7 +17,12 @@ Transports behind one class:
           and writes them as contiguous runs straight into the neighbours' receive buffers (peer
           pointers); a one-block handshake kernel follows each step; received halos are consumed at
           load time.  No isolated remote stores: the transport for large faces (1024^2).
-  'auto'  (default on CUDA) 'p2p' for faces below 512 x 512 lines, 'p2p-packed' from there on.
+  'p2p-ll'  (LB_HALO_LL, the default on CUDA) as 'p2p-packed', but every halo element travels as a (payload, tag)
+          pair written with one 8-byte store, tag = the global index of the producing time step, into
+          TRIPLE-buffered receive buffers.  The data is its own flag: the receiving step kernel loads its incoming
+          elements with its populations and re-polls only those whose tag is not there yet.  No handshake kernel,
+          no flags, no fences between steps: simulation(n) is n step kernels back to back on every rank.
+  'auto'  (default on CUDA) = 'p2p-ll'.
   'nccl'  (LB_HALO_PACKED) packed send buffers, torch.distributed send/recv, lb_unpack_halo:
           the baseline design north_star names.
   'host'  same exchange logic over any torch.distributed backend with an injected local stepper;
@@ -31,23 +36,19 @@ import torch
 import torch.distributed as dist
 
 from . import _native as nat
-from ._flows import TaylorGreenVortex
+from ._flows import Obstacle, TaylorGreenVortex
 from ._reporter import ObservableReporter
 from ._simulation import Simulation
 
-AUTO_PACKED_MIN_LINES = 512 * 512   # faces (lines per z plane) from which 'auto' picks 'p2p-packed'
+PEER_TRANSPORTS = ('p2p-ll', 'p2p-packed', 'p2p-push', 'p2p')   # halos move through CUDA-IPC peer pointers
 
 
 def auto_transport(resolution) -> str:
-    """'p2p' (direct peer stores) for small z faces, 'p2p-packed' for large ones.  Measured (DESIGN.md
-    section 6): 256^2 faces 95.6 % ('p2p') vs 93.8 % ('p2p-packed') of the single-GPU rate at 8 GPUs;
-    1024^2 faces 83 % vs 98.5 %."""
-    lines = 1
-    for n in resolution[:-1]:
-        lines *= int(n)
-    return 'p2p' if lines < AUTO_PACKED_MIN_LINES else 'p2p-packed'
+    """The handshake-free 'p2p-ll' transport for every face size (round 1 picked 'p2p' below
+    512 x 512 lines and 'p2p-packed' above, both with a handshake kernel per step)."""
+    return 'p2p-ll'
 
-__all__ = ['slab_range', 'zface_populations', 'SlabTaylorGreenVortex', 'SlabSimulation']
+__all__ = ['slab_range', 'zface_populations', 'SlabTaylorGreenVortex', 'SlabObstacle', 'SlabSimulation']
 
 
 def slab_range(n: int, rank: int, world: int):
@@ -117,6 +118,47 @@ class SlabTaylorGreenVortex(TaylorGreenVortex):
         return torch.meshgrid(*axes, indexing='ij')
 
 
+class SlabObstacle(Obstacle):
+    """The local z-slab of `lt.Obstacle` (obstacle.py:16-125; SURVEY section 8e: "masks are sharded the same
+    way"): same units as the undivided flow (they depend on resolution[0] only), the grid of the slab's own
+    z range, and the stock boundary list -- equilibrium inlet on x = 0, AntiBounceBackOutlet on the +x side,
+    bounce-back on the mask -- built from the LOCAL mask.  All three are node-local or read a neighbour along x,
+    so no boundary needs a halo; the no-streaming mask of the outlet is the destination's own and is applied by
+    the receiving rank (include/lettuce_b200.h).  `mask` accepts the local slab or the whole lattice."""
+
+    def __init__(self, context, global_resolution, reynolds_number, mach_number, domain_length_x,
+                 rank: int, world: int, char_length=1, char_velocity=1, stencil=None, equilibrium=None):
+        self.global_resolution = list(global_resolution)
+        self.rank, self.world = rank, world
+        self.z0, self.z1 = slab_range(self.global_resolution[-1], rank, world)
+        local = self.global_resolution[:-1] + [self.z1 - self.z0]
+        Obstacle.__init__(self, context, local, reynolds_number, mach_number, domain_length_x,
+                          char_length=char_length, char_velocity=char_velocity, stencil=stencil,
+                          equilibrium=equilibrium)
+
+    @property
+    def mask(self):
+        return self._mask
+
+    @mask.setter
+    def mask(self, m):
+        if list(m.shape) == self.global_resolution and self.world > 1:
+            m = m[..., self.z0:self.z1]
+        assert list(m.shape) == list(self.resolution), (m.shape, self.resolution)
+        self._mask = self.context.convert_to_tensor(m, dtype=torch.bool)
+
+    @property
+    def grid(self):
+        """coordinates of the slab's nodes in the global lattice"""
+        ranges = [torch.arange(n) for n in self.resolution[:-1]] + [torch.arange(self.z0, self.z1)]
+        return torch.meshgrid(*(self.units.convert_length_to_pu(r) for r in ranges), indexing='ij')
+
+    @property
+    def global_grid(self):
+        xyz = tuple(self.units.convert_length_to_pu(torch.arange(n)) for n in self.global_resolution)
+        return torch.meshgrid(*xyz, indexing='ij')
+
+
 class _DeviceMemory:
     """cudaMalloc'ed, IPC-exportable memory exposed to torch through __cuda_array_interface__"""
 
@@ -158,18 +200,19 @@ class SlabSimulation(Simulation):
     MLUPS; fused reporters receive globally reduced observables."""
 
     def __init__(self, flow, collision, reporter, transport: Optional[str] = None, group=None,
-                 local_stepper=None):
+                 local_stepper=None, host_no_streaming_mask=None):
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.up = (self.rank + 1) % self.world
         self.down = (self.rank - 1) % self.world
         self.local_stepper = local_stepper
+        self.host_no_streaming_mask = host_no_streaming_mask
         if transport is None:
             transport = 'host' if local_stepper is not None else 'auto'
         if transport == 'auto':
             transport = auto_transport(flow.resolution)
-        if transport not in ('p2p-push', 'p2p-packed', 'p2p', 'nccl', 'host'):
+        if transport not in PEER_TRANSPORTS + ('nccl', 'host'):
             raise ValueError(transport)
         self.transport = transport
         self._epoch = 0
@@ -183,15 +226,20 @@ class SlabSimulation(Simulation):
             self.no_collision_mask = self.no_streaming_mask = None
         else:
             Simulation.__init__(self, flow, collision, reporter)
-            if self.no_streaming_mask is not None and bool(self.no_streaming_mask.any()):
-                raise NotImplementedError("no_streaming_mask is not supported across slabs")
+            if transport == 'p2p' and self.no_streaming_mask is not None and bool((self.no_streaming_mask == 1).any()):
+                raise NotImplementedError("no_streaming_mask across slabs needs a packed transport ('p2p-ll', "
+                                          "'p2p-packed', 'p2p-push', 'nccl'): the direct peer stores of 'p2p' go "
+                                          "into planes whose mask the sender does not have")
+            self._check_slab_outlets()
         flow._obs_allreduce = self._reduce_obs
         self.hi_q, self.lo_q = zface_populations(flow.stencil)
         self.lines = 1
         for n in flow.resolution[:-1]:
             self.lines *= n
         if self.world > 1:
-            if transport in ('p2p-push', 'p2p-packed'):
+            if transport == 'p2p-ll':
+                self._setup_ll()
+            elif transport in ('p2p-push', 'p2p-packed'):
                 self._setup_push()
             elif transport == 'p2p':
                 self._setup_direct()
@@ -239,6 +287,28 @@ class SlabSimulation(Simulation):
             torch.cuda.synchronize(dev)
             self._peer = self._share(self._mem)
 
+    def _setup_ll(self):
+        """three IPC-visible receive buffers per face (tagged words, zero = "nothing sent yet") + the flag word"""
+        flow, dev = self.flow, self.flow.f.device
+        nbytes = nat.lib().lb_halo_ll_bytes(self._desc())
+        with torch.cuda.device(dev):
+            recv = [_DeviceMemory([nbytes], torch.uint8) for _ in range(6)]    # lo0 lo1 lo2 hi0 hi1 hi2
+            flags = _DeviceMemory([8], torch.int32)
+            self._mem = recv + [flags]
+            self._recv = [m.tensor(dev) for m in recv]
+            self._flags = flags.tensor(dev)
+            torch.cuda.synchronize(dev)
+            self._peer = self._share(self._mem)
+
+    def _check_slab_outlets(self):
+        """an outlet plane normal to the slab axis would read the neighbour rank's plane: not supported"""
+        from ._boundary import AntiBounceBackOutlet
+        if self.world > 1:
+            for b in self.boundaries[1:]:
+                if isinstance(b, AntiBounceBackOutlet) and b.direction[-1] != 0:
+                    raise NotImplementedError("outlet boundaries normal to the slab axis (the last lattice axis) are "
+                                              "not supported across slabs")
+
     def _setup_direct(self):
         flow, dev = self.flow, self.flow.f.device
         with torch.cuda.device(dev):
@@ -256,6 +326,15 @@ class SlabSimulation(Simulation):
         flow = self.flow
         h = nat.LbHalo()
         h.epoch = epoch
+        if self.transport == 'p2p-ll':
+            up, down = self._peer[self.up], self._peer[self.down]
+            h.mode = nat.LB_HALO_LL
+            for k in range(3):
+                h.recv_lo[k], h.recv_hi[k] = self._recv[k].data_ptr(), self._recv[3 + k].data_ptr()
+                h.peer_up_recv_lo[k] = up[k]            # our hi face lands in the +z neighbour's recv_lo
+                h.peer_down_recv_hi[k] = down[3 + k]    # our lo face lands in the -z neighbour's recv_hi
+            h.wait_slots = self._flags.data_ptr()
+            return h
         if self.transport in ('p2p-push', 'p2p-packed'):
             up, down = self._peer[self.up], self._peer[self.down]
             h.mode = nat.LB_HALO_PUSH if self.transport == 'p2p-push' else nat.LB_HALO_REMOTE
@@ -268,6 +347,14 @@ class SlabSimulation(Simulation):
         elif self.transport == 'p2p':
             up, down = self._peer[self.up], self._peer[self.down]
             h.mode = nat.LB_HALO_DIRECT
+            # the neighbours store into the two IPC buffers: if flow.f was rebound (Flow.load, a reporter, a
+            # .contiguous() copy) move the state back into them instead of silently losing the halos
+            ptrs = (self._buf[0].data_ptr(), self._buf[1].data_ptr())
+            if flow.f.data_ptr() not in ptrs:
+                self._buf[0].copy_(flow.f)
+                flow.f, flow.f_next = self._buf[0], self._buf[1]
+            elif flow.f_next.data_ptr() not in ptrs or flow.f_next.data_ptr() == flow.f.data_ptr():
+                flow.f_next = self._buf[1] if flow.f.data_ptr() == ptrs[0] else self._buf[0]
             cur = 0 if flow.f.data_ptr() == self._buf[0].data_ptr() else 1
             # step s writes into f_next (s even) / f (s odd): the neighbours' matching buffers
             h.peer_up_f[0], h.peer_up_f[1] = up[1 - cur], up[cur]
@@ -298,6 +385,10 @@ class SlabSimulation(Simulation):
             return
         if self.world == 1:
             return Simulation._advance(self, n, obs_out, u_out)
+        if self.transport == 'p2p-ll':
+            Simulation._advance(self, n, obs_out, u_out)
+            self._epoch += n          # = time steps taken: the tag of the next step is epoch + 1
+            return
         if self.transport in ('p2p-push', 'p2p-packed', 'p2p'):
             Simulation._advance(self, n, obs_out, u_out)
             self._epoch += n + 1
@@ -310,15 +401,25 @@ class SlabSimulation(Simulation):
             self._exchange_packed()
             desc = self._desc()
             with torch.cuda.device(dev):
-                nat.check(nat.lib().lb_unpack_halo(desc, self.flow.f.data_ptr(), self.recv_down.data_ptr(),
-                                                   self.recv_up.data_ptr(), nat.current_stream_ptr(dev)))
+                nat.check(nat.lib().lb_unpack_halo_ex(desc, self.flow.f.data_ptr(), self.recv_down.data_ptr(),
+                                                      self.recv_up.data_ptr(), nat.ptr(self._streaming_bits), 0, None,
+                                                      nat.current_stream_ptr(dev)))
 
     def _host_step(self):
         """local update by the injected stepper, which follows the kernel's contract: it returns
         the locally streamed slab (periodic in z by itself) -- the planes that wrapped around are
-        exactly the populations owed to the neighbours."""
+        exactly the populations owed to the neighbours.  With a no-streaming mask the stepper is a pair
+        (collide, stream-without-mask) and the mask is applied HERE, after the exchange: the sender always
+        sends, the receiving slab keeps its own post-collision value where its bit is set
+        (_simulation.py:171-174), exactly what the kernels do."""
         flow = self.flow
-        f = self.local_stepper(flow.f)
+        fstar = None
+        if isinstance(self.local_stepper, tuple):
+            collide, stream = self.local_stepper
+            fstar = collide(flow.f)
+            f = stream(fstar)
+        else:
+            f = self.local_stepper(flow.f)
         if self.world > 1:
             for k, q in enumerate(self.hi_q):
                 self.send_hi[k] = f[q][..., 0].reshape(-1)       # wrapped to z=0: belongs to `up`
@@ -330,6 +431,8 @@ class SlabSimulation(Simulation):
                 f[q][..., 0] = self.recv_down[k].reshape(plane)
             for k, q in enumerate(self.lo_q):
                 f[q][..., -1] = self.recv_up[k].reshape(plane)
+        if fstar is not None and self.host_no_streaming_mask is not None:
+            f = torch.where(self.host_no_streaming_mask == 1, fstar, f)
         flow.f = f
 
     # ---- reporters: global reductions ------------------------------------------------------------
@@ -347,10 +450,36 @@ class SlabSimulation(Simulation):
     def _finalize_obs(self, obs):
         return self._reduce_obs(obs).cpu()
 
+    GRADIENT_RADIUS = 3   # 6th-order central difference (util.torch_gradient, utility.py:37-99)
+
+    def _exchange_velocity_halo(self, u):
+        """u [d, *res] -> u_ext [d, *res[:-1], nz + 6]: the 3 planes next to each z face come from the neighbours
+        (a real exchange step, on enstrophy-reporting steps only: torch.distributed send / recv)"""
+        g = self.GRADIENT_RADIUS
+        if u.shape[-1] < g:
+            raise NotImplementedError("Enstrophy across slabs needs slabs of at least 3 planes")
+        lo, hi = u[..., :g].contiguous(), u[..., -g:].contiguous()
+        from_down, from_up = torch.empty_like(hi), torch.empty_like(lo)
+        ops = [dist.P2POp(dist.isend, hi, self.up, self.group), dist.P2POp(dist.isend, lo, self.down, self.group),
+               dist.P2POp(dist.irecv, from_down, self.down, self.group),
+               dist.P2POp(dist.irecv, from_up, self.up, self.group)]
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+        return torch.cat([from_down, u, from_up], dim=-1).contiguous()
+
+    def _enstrophy(self, desc, u_buf, obs_row):
+        if self.world == 1:
+            return Simulation._enstrophy(self, desc, u_buf, obs_row)
+        if min(self.flow.resolution[:-1]) < 3:
+            raise NotImplementedError("Enstrophy needs at least 3 nodes per axis (6th-order periodic gradient)")
+        dev = self.context.device
+        u_ext = self._exchange_velocity_halo(u_buf)
+        with torch.cuda.device(dev):
+            nat.check(nat.lib().lb_enstrophy_slab(desc, u_ext.data_ptr(), self.GRADIENT_RADIUS,
+                                                  self._obs_scratch.data_ptr(), obs_row.data_ptr(),
+                                                  nat.current_stream_ptr(dev)))
+
     def _run_segment(self, n, fused):
-        if any(r.native_slot == nat.LB_OBS_ENSTROPHY for r in fused) and self.world > 1:
-            raise NotImplementedError("Enstrophy across slabs needs a 3-plane velocity halo, which the slab "
-                                      "transports do not carry")
         if self.transport == 'host':
             self._advance(n)
             self.flow.i += n
@@ -363,14 +492,18 @@ class SlabSimulation(Simulation):
             self._advance(num_steps)
             self.flow.i += num_steps
             return num_steps * self.flow.f[0].numel() * self.world / 1e6 / (timer() - beg)
+        i_before = self.flow.i
         mlups_local = Simulation.__call__(self, num_steps)
-        if self.world > 1 and self.transport in ('p2p-push', 'p2p-packed', 'p2p'):
+        if self.world > 1 and self.transport in PEER_TRANSPORTS:
             if int(self._flags[2].item()) != 0:
-                raise RuntimeError("halo handshake timed out: a neighbour rank did not reach the same step")
+                self.flow.i = i_before
+                raise RuntimeError("halo exchange timed out: a neighbour rank did not deliver its halo / reach the "
+                                   "same step within ~10 s.  The populations of this call are INVALID (steps after "
+                                   "the timeout ran on stale halos); flow.i was left at its value before the call.")
         return mlups_local * self.world
 
     def close(self):
-        if self.world > 1 and self.transport in ('p2p-push', 'p2p-packed', 'p2p'):
+        if self.world > 1 and self.transport in PEER_TRANSPORTS:
             torch.cuda.synchronize(self.context.device)
             dist.barrier(group=self.group)
             for r, ptrs in self._peer.items():

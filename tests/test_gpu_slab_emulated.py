@@ -3,7 +3,9 @@
 handshake needed, none used: kernels that wait on one another must not share a GPU).  Both halo
 layouts -- direct stores into the neighbour's planes, and packed send buffers + lb_unpack_halo --
 and the push protocol's "consume the received halo at load time, unpack at the end" ("deferred") --
-must reproduce the undivided single-GPU run bit for bit."""
+must reproduce the undivided single-GPU run bit for bit.  So must the handshake-free "ll" transport (tagged
+(payload, tag) words, triple-buffered receive buffers; the serial launch order means no poll ever has to wait),
+and all packed layouts with a per-(q, node) no-streaming mask whose destination bits live on the RECEIVING slab."""
 import ctypes as C
 
 import numpy as np
@@ -15,7 +17,7 @@ from golden_util import DT
 pytestmark = pytest.mark.gpu
 
 
-def _run_slabs(stencil, dtype, res, R, n_steps, collision, mode, with_mask):
+def _run_slabs(stencil, dtype, res, R, n_steps, collision, mode, with_mask, with_nsm=False):
     import gpu_util as gu
     import lettuce_b200 as lt
     nat = lt.native
@@ -26,12 +28,13 @@ def _run_slabs(stencil, dtype, res, R, n_steps, collision, mode, with_mask):
     w = np.asarray(S.w).reshape([S.q] + [1] * len(res))
     f0 = torch.tensor(w * (1.0 + 0.05 * rng.random([S.q, *res])), dtype=tdt, device="cuda")
     solid = torch.tensor(rng.random(res) < 0.1, device="cuda") if with_mask else None
+    nsm = torch.tensor(rng.random([S.q, *res]) < 0.08, device="cuda") if with_nsm else None
 
     # undivided reference run on the GPU
     ctx = lt.Context(device="cuda", dtype=tdt, use_native=True)
     flow = gu.FieldFlow(ctx, res, getattr(lt, stencil), f0)
     if with_mask:
-        flow.boundaries.append(gu.TaggedBounceBack(solid, tag=1))
+        flow.boundaries.append(gu.TaggedBounceBack(solid, nsm=nsm, tag=1))
     coll = {"none": lt.NoCollision(), "bgk": lt.BGKCollision(0.7), "trt": lt.TRTCollision(0.7, 0.9)}[collision]
     sim = lt.Simulation(flow, coll, [])
     sim(n_steps)
@@ -45,6 +48,14 @@ def _run_slabs(stencil, dtype, res, R, n_steps, collision, mode, with_mask):
     A = [f0[..., r * nzl:(r + 1) * nzl].contiguous() for r in range(R)]
     B = [torch.empty_like(a) for a in A]
     ncm = [solid[..., r * nzl:(r + 1) * nzl].to(torch.uint8).contiguous() for r in range(R)] if with_mask else None
+    sbits = None
+    if with_nsm:     # each slab packs ITS part of the mask (the hint bit wraps around the slab: conservative)
+        sbits = []
+        for r in range(R):
+            m = nsm[..., r * nzl:(r + 1) * nzl].to(torch.uint8).contiguous()
+            b = torch.empty(lres, dtype=torch.int32, device="cuda")
+            nat.check(L.lb_pack_streaming_mask(desc, m.data_ptr(), b.data_ptr(), torch.cuda.current_stream().cuda_stream))
+            sbits.append(b)
     bnd = (nat.LbBoundary * 1)()
     bnd[0].kind = nat.LB_BND_BOUNCE_BACK
     lines = int(np.prod(res[:-1]))
@@ -53,6 +64,9 @@ def _run_slabs(stencil, dtype, res, R, n_steps, collision, mode, with_mask):
     send_lo = [torch.zeros([nf, lines], dtype=tdt, device="cuda") for _ in range(R)]
     recv_lo = [torch.zeros_like(t) for t in send_hi]
     recv_hi = [torch.zeros_like(t) for t in send_hi]
+    ll_bytes = L.lb_halo_ll_bytes(desc)
+    ll_lo = [[torch.zeros([ll_bytes], dtype=torch.uint8, device="cuda") for _ in range(3)] for _ in range(R)]
+    ll_hi = [[torch.zeros([ll_bytes], dtype=torch.uint8, device="cuda") for _ in range(3)] for _ in range(R)]
     # wait slots pre-set far ahead so the single-stream emulation never spins
     flags = [torch.full([8], 1 << 30, dtype=torch.int32, device="cuda") for _ in range(R)]
     for fl_ in flags:
@@ -70,6 +84,14 @@ def _run_slabs(stencil, dtype, res, R, n_steps, collision, mode, with_mask):
                 h.signal_up = h.signal_down = flags[r].data_ptr() + 16     # dummy slot nobody waits on
                 h.wait_slots = flags[r].data_ptr()
                 h.epoch = 0
+            elif mode == "ll":
+                h.mode = nat.LB_HALO_LL
+                h.epoch = step
+                h.flags = nat.LB_HALO_F_NO_UNPACK | (nat.LB_HALO_F_CONSUME_FIRST if step > 0 else 0)
+                for k in range(3):
+                    h.recv_lo[k], h.recv_hi[k] = ll_lo[r][k].data_ptr(), ll_hi[r][k].data_ptr()
+                    h.peer_up_recv_lo[k], h.peer_down_recv_hi[k] = ll_lo[up][k].data_ptr(), ll_hi[down][k].data_ptr()
+                h.wait_slots = flags[r].data_ptr()
             else:
                 h.mode = nat.LB_HALO_PACKED
                 h.send_hi[0], h.send_lo[0] = send_hi[r].data_ptr(), send_lo[r].data_ptr()
@@ -81,13 +103,15 @@ def _run_slabs(stencil, dtype, res, R, n_steps, collision, mode, with_mask):
                 fl.no_collision_mask = ncm[r].data_ptr()
                 fl.boundaries = C.cast(bnd, C.POINTER(nat.LbBoundary))
                 fl.n_boundaries = 1
+                if with_nsm:
+                    fl.streaming_bits = sbits[r].data_ptr()
             fl.halo = C.pointer(h)
             nat.check(L.lb_step(desc, fl, 1, st))
         if mode == "packed":
             for r in range(R):
                 up, down = (r + 1) % R, (r - 1) % R
-                nat.check(L.lb_unpack_halo(desc, B[r].data_ptr(), send_hi[down].data_ptr(),
-                                           send_lo[up].data_ptr(), st))
+                nat.check(L.lb_unpack_halo_ex(desc, B[r].data_ptr(), send_hi[down].data_ptr(), send_lo[up].data_ptr(),
+                                              sbits[r].data_ptr() if with_nsm else None, 0, None, st))
         elif mode == "deferred":
             for r in range(R):                       # the "push": neighbours' sends -> our recvs
                 up, down = (r + 1) % R, (r - 1) % R
@@ -95,10 +119,16 @@ def _run_slabs(stencil, dtype, res, R, n_steps, collision, mode, with_mask):
                 recv_hi[r].copy_(send_lo[up])
             if step == n_steps - 1:                  # canonical again at the end of the "call"
                 for r in range(R):
-                    nat.check(L.lb_unpack_halo(desc, B[r].data_ptr(), recv_lo[r].data_ptr(),
-                                               recv_hi[r].data_ptr(), st))
+                    nat.check(L.lb_unpack_halo_ex(desc, B[r].data_ptr(), recv_lo[r].data_ptr(), recv_hi[r].data_ptr(),
+                                                  sbits[r].data_ptr() if with_nsm else None, 0, None, st))
+        elif mode == "ll" and step == n_steps - 1:
+            g = n_steps                              # tag of the last step
+            for r in range(R):
+                nat.check(L.lb_unpack_halo_ex(desc, B[r].data_ptr(), ll_lo[r][g % 3].data_ptr(), ll_hi[r][g % 3].data_ptr(),
+                                              sbits[r].data_ptr() if with_nsm else None, g, flags[r].data_ptr() + 8, st))
         A, B = B, A
     got = torch.cat(A, dim=-1)
+    assert all(int(fl_[2].item()) == 0 for fl_ in flags), "an LL poll timed out"
     return got, want
 
 
@@ -112,15 +142,32 @@ CASES = [
 
 
 @pytest.mark.parametrize("stencil,dtype,res,R", CASES)
-@pytest.mark.parametrize("mode", ["direct", "packed", "deferred"])
+@pytest.mark.parametrize("mode", ["direct", "packed", "deferred", "ll"])
 def test_slab_streaming_equals_undivided(stencil, dtype, res, R, mode):
     got, want = _run_slabs(stencil, dtype, res, R, 4, "none", mode, with_mask=False)
     assert torch.equal(got, want)
 
 
 @pytest.mark.parametrize("stencil,dtype,res,R", CASES[:6])
-@pytest.mark.parametrize("mode", ["direct", "packed", "deferred"])
+@pytest.mark.parametrize("mode", ["direct", "packed", "deferred", "ll"])
 @pytest.mark.parametrize("collision", ["bgk", "trt"])
 def test_slab_collision_with_mask_equals_undivided(stencil, dtype, res, R, mode, collision):
     got, want = _run_slabs(stencil, dtype, res, R, 6, collision, mode, with_mask=True)
     assert torch.equal(got, want)
+
+
+@pytest.mark.parametrize("stencil,dtype,res,R", CASES)
+@pytest.mark.parametrize("mode", ["packed", "deferred", "ll"])
+@pytest.mark.parametrize("collision", ["none", "bgk"])
+def test_slab_masked_streaming_equals_undivided(stencil, dtype, res, R, mode, collision):
+    """destination-masked streaming (_simulation.py:171-174) across slab faces: random per-(q, node) keep bits and
+    bounce-back solids; the sender always sends, the receiving slab drops what its nodes keep"""
+    got, want = _run_slabs(stencil, dtype, res, R, 5, collision, mode, with_mask=True, with_nsm=True)
+    assert torch.equal(got, want)
+
+
+def test_direct_transport_refuses_masked_streaming():
+    import lettuce_b200 as lt
+    nat = lt.native
+    with pytest.raises(nat.NativeError, match="packed halo transport"):
+        _run_slabs("D3Q19", "f32", [4, 4, 16], 2, 1, "none", "direct", with_mask=True, with_nsm=True)

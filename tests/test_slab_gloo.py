@@ -83,12 +83,113 @@ def test_slab_exchange_matches_undivided_oracle(world, stencil, res, collision):
     assert err == 0.0 if collision == "none" else err < 1e-14
 
 
-def test_auto_transport_by_face_size():
+def _masked_worker(rank, world, port, stencil, res, n_steps, q):
+    """bounce-back solids + a random per-(q, node) no-streaming mask, both sharded along the last axis: the
+    destination bits of a population that crosses a slab face live on the RECEIVING rank"""
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import lettuce_b200 as lt
+        from lettuce_b200.slab import SlabSimulation, slab_range
+        from oracle import lbm_oracle as orc
+        torch.set_num_threads(1)
+        torch.manual_seed(4321)
+        S = getattr(lt, stencil)()
+        lat = orc.OracleLattice(stencil, torch.float64)
+        w = torch.tensor(S.w, dtype=torch.float64).reshape([S.q] + [1] * len(res))
+        f_global = w * (1.0 + 0.1 * torch.rand([S.q, *res], dtype=torch.float64))
+        solid = torch.rand(res) < 0.15
+        nsm = (torch.rand([S.q, *res]) < 0.1).to(torch.uint8)
+        ncm = solid.to(torch.uint8)
+        bnd = [orc.OracleBoundary(kind="bounce_back", mask=solid)]
+        z0, z1 = slab_range(res[-1], rank, world)
+
+        class LocalFlow:
+            pass
+        flow = LocalFlow()
+        flow.context = lt.Context(device="cpu", dtype=torch.float64, use_native=False)
+        flow.stencil = S
+        flow.resolution = list(res[:-1]) + [z1 - z0]
+        flow.f = f_global[..., z0:z1].contiguous()
+        flow.i = 0
+        params = dict(tau=0.8)
+        bnd_l = [orc.OracleBoundary(kind="bounce_back", mask=solid[..., z0:z1])]
+        ncm_l, nsm_l = ncm[..., z0:z1].contiguous(), nsm[..., z0:z1].contiguous()
+        sim = SlabSimulation(flow, None, [], transport="host",
+                             local_stepper=(lambda f: orc.collide(lat, f, "bgk", params, ncm=ncm_l, boundaries=bnd_l),
+                                            lambda f: orc.stream(lat, f, None)),
+                             host_no_streaming_mask=nsm_l)
+        sim(n_steps)
+        parts = [torch.empty_like(flow.f) for _ in range(world)]
+        dist.all_gather(parts, flow.f.contiguous())
+        # the 3-plane velocity halo of the enstrophy reporter (SlabSimulation._exchange_velocity_halo)
+        u_global = torch.arange(S.d * f_global[0].numel(), dtype=torch.float64).reshape([S.d, *res])
+        ok_u = True
+        if z1 - z0 >= 3:
+            ext = sim._exchange_velocity_halo(u_global[..., z0:z1].contiguous())
+            idx = torch.arange(z0 - 3, z1 + 3) % res[-1]
+            ok_u = bool(torch.equal(ext, u_global[..., idx]))
+        oks = [None] * world
+        dist.all_gather_object(oks, ok_u)
+        if rank == 0:
+            ref = orc.run(lat, f_global, n_steps, "bgk", params, ncm=ncm, nsm=nsm, boundaries=bnd)
+            got = torch.cat(parts, dim=-1)
+            q.put((float((got - ref).abs().max()), all(oks)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,stencil,res", [(2, "D3Q19", [4, 5, 8]), (3, "D2Q9", [6, 9]), (2, "D3Q27", [3, 4, 2])])
+def test_slab_masked_streaming_and_velocity_halo(world, stencil, res):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_masked_worker, args=(r, world, port, stencil, res, 4, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    err, u_ok = q.get(timeout=10)
+    assert err < 1e-14 and u_ok
+
+
+def test_slab_obstacle_is_the_slice_of_the_undivided_flow():
+    import lettuce_b200 as lt
+    from lettuce_b200._simulation import build_masks
+    from lettuce_b200.slab import SlabObstacle
+    ctx = lt.Context(device="cpu", dtype=torch.float64, use_native=False)
+    res = [16, 8, 12]
+    g = lt.Obstacle(ctx, res, reynolds_number=50, mach_number=0.05, domain_length_x=2, stencil=lt.D3Q19)
+    x, y, z = g.grid
+    solid = ((x - 0.3 * x.max()) ** 2 + (y - 0.5 * y.max()) ** 2 + (z - 0.5 * z.max()) ** 2) < (0.2 * y.max()) ** 2
+    g.mask = solid
+    gb = [None] + sorted(g.boundaries, key=str)
+    ncm_g, nsm_g = build_masks(g, gb, ctx)
+    for world in (2, 3):
+        for rank in range(world):
+            s = SlabObstacle(ctx, res, 50, 0.05, 2, rank=rank, world=world, stencil=lt.D3Q19)
+            s.mask = solid                      # the whole-lattice mask is cut to the slab
+            assert s.resolution == [16, 8, 12 // world]
+            assert s.units.relaxation_parameter_lu == g.units.relaxation_parameter_lu
+            assert torch.equal(s.f, g.f[..., s.z0:s.z1])
+            for a, b in zip(s.grid, g.grid):
+                assert torch.equal(a, b[..., s.z0:s.z1])
+            sb = [None] + sorted(s.boundaries, key=str)
+            assert [type(b).__name__ for b in sb[1:]] == [type(b).__name__ for b in gb[1:]]
+            ncm_s, nsm_s = build_masks(s, sb, ctx)
+            assert torch.equal(ncm_s, ncm_g[..., s.z0:s.z1]) and torch.equal(nsm_s, nsm_g[..., s.z0:s.z1])
+
+
+def test_auto_transport_is_the_handshake_free_one():
     from lettuce_b200.slab import auto_transport
-    assert auto_transport([256, 256, 256]) == 'p2p'            # bench.py --gpus N: 256^3 per GPU
-    assert auto_transport([1024, 1024, 128]) == 'p2p-packed'   # config 5
-    assert auto_transport([512, 512, 64]) == 'p2p-packed'
-    assert auto_transport([2048, 64]) == 'p2p'                 # 2-D: y-slabs, faces are lines
+    assert auto_transport([256, 256, 256]) == 'p2p-ll'            # bench.py --gpus N: 256^3 per GPU
+    assert auto_transport([1024, 1024, 128]) == 'p2p-ll'          # config 5
+    assert auto_transport([2048, 64]) == 'p2p-ll'                 # 2-D: y-slabs, faces are lines
 
 
 def test_slab_helpers():
