@@ -149,16 +149,19 @@ class Flow(ABC):
                                            nat.current_stream_ptr(f.device)))
         return rho, u
 
-    def output_fields_pu(self, f: Optional[torch.Tensor] = None) -> torch.Tensor:
+    def output_fields_pu(self, f: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """[1 + d, nodes]: p_pu then u_pu, each FLAT IN FILE ORDER (lattice x fastest), what a field-writing
         reporter needs (vtk_reporter.py:29-47).  On a CUDA flow one `lb_output_fields` launch: the
-        populations are read once and the fields leave the kernel already converted and reordered."""
+        populations are read once and the fields leave the kernel already converted and reordered.
+        `out`: a [1 + d, nodes] device tensor to write into (reporters reuse theirs)."""
         f = self.f if f is None else f
         d = self.stencil.d
         if self._native_moments_ok(f):
             units = self.units
             desc = nat.make_desc(type(self.stencil).__name__, f.dtype, self.resolution)
-            out = torch.empty([1 + d, f[0].numel()], dtype=f.dtype, device=f.device)
+            if out is None:
+                out = torch.empty([1 + d, f[0].numel()], dtype=f.dtype, device=f.device)
+            assert out.is_contiguous() and tuple(out.shape) == (1 + d, f[0].numel()) and out.dtype == f.dtype
             p_scale = float(units.cs ** 2 / units.characteristic_pressure_lu * units.characteristic_pressure_pu)
             u_scale = float(units.characteristic_velocity_pu / units.characteristic_velocity_lu)
             with torch.cuda.device(f.device):

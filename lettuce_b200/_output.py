@@ -1,7 +1,6 @@
 """The output side of the path: VTKReporter / write_vtk
-(reference/lettuce/ext/_reporter/vtk_reporter.py:11-64), ErrorReporter (error_reporter.py:9-44),
-EnergySpectrum (observable_reporter.py:71-137) and HDF5Reporter / LettuceDataset
-(util/datautils.py:16-160).
+(reference/lettuce/ext/_reporter/vtk_reporter.py:11-64), ErrorReporter (error_reporter.py:9-44) and
+EnergySpectrum (observable_reporter.py:71-137).
 
 What changes against the reference: the reporters never pull the populations to the host.  On a
 CUDA flow ONE kernel (lb_output_fields) reads the populations once and writes p and u in physical
@@ -14,12 +13,8 @@ order, every array in x-fastest (Fortran) point order -- pyevtk's published layo
 the container is UNPINNED (no pyevtk here to diff against); `read_vtr` below reads the files
 back and the tests pin the payload.
 
-HDF5Reporter / LettuceDataset need h5py, which this image lacks: constructing them raises
-ImportError naming the dependency ("unavailable in this image"); with h5py present they work as
-in the reference."""
-import io
+HDF5Reporter / LettuceDataset / write_image are out of scope (SURVEY.md section 2 #12, #9): the names refuse."""
 import os
-import pickle
 import re
 import sys
 from typing import Dict, Optional
@@ -117,19 +112,45 @@ def write_vtk(point_dict, id=0, filename_base="./data/output"):
                        np.arange(0, shape[2]), point_dict)
 
 
+class _ReportSlot:
+    """one report in flight: device fields -> pinned host copy -> file"""
+
+    def __init__(self, rows, nodes, dtype, device):
+        import threading
+        self.dev = torch.empty([rows, nodes], dtype=dtype, device=device)
+        self.host = torch.empty([rows, nodes], dtype=dtype, pin_memory=True)
+        self.fields_ready = torch.cuda.Event()
+        self.copied = torch.cuda.Event()
+        self.done = threading.Event()
+        self.done.set()
+        self.error = None
+
+
 class VTKReporter(Reporter):
     """Pressure and velocity in physical units as `<filename_base>_<step:08d>.vtr` every `interval`
     steps (vtk_reporter.py:19-64).  `point_dict` holds the arrays of the last file, [nx, ny, nz]
-    views (nz = 1 in 2-D) like the reference's."""
+    views (nz = 1 in 2-D) like the reference's.
 
-    def __init__(self, interval=50, filename_base="./data/output"):
+    On a CUDA flow a report costs the time-stepping stream ONE kernel (lb_output_fields into a device buffer
+    of the reporter's own); the device->host copy of the 1 + d fields runs on a second stream into
+    double-buffered pinned staging and the file is written by a background thread, both overlapped with the
+    following time steps (`asynchronous=False`: everything inside the call, as in the reference).
+    `Simulation.__call__` calls `flush()` before it returns, so the files of a call exist when it is over;
+    a report finds its slot busy only when reports arrive faster than PCIe + the disk take them."""
+
+    def __init__(self, interval=50, filename_base="./data/output", asynchronous=True, buffers=2):
         super().__init__(interval)
         self.filename_base = filename_base
         directory = os.path.dirname(filename_base)
         if directory and not os.path.isdir(directory):
             os.makedirs(directory, exist_ok=True)     # the reference's os.mkdir (:25-26), nested paths included
         self.point_dict = dict()
-        self._stage = None     # pinned host staging buffer [1 + d, nodes]
+        self.asynchronous = asynchronous
+        self.buffers = max(1, int(buffers))
+        self._stage = None     # synchronous path: pinned host staging buffer [1 + d, nodes]
+        self._slots, self._next = [], 0
+        self._copy_stream = None
+        self._queue, self._writer = None, None
 
     def _staging(self, rows, nodes, dtype, pinned):
         st = self._stage
@@ -137,20 +158,91 @@ class VTKReporter(Reporter):
             self._stage = st = torch.empty([rows, nodes], dtype=dtype, pin_memory=pinned)
         return st
 
+    @staticmethod
+    def _names_shape(flow):
+        d = flow.stencil.d
+        return ["p"] + [f"u{'xyz'[c]}" for c in range(d)], tuple(flow.resolution) + (1,) * (3 - d)
+
+    def _write(self, flat, names, shape3, step):
+        self.point_dict = {name: flat[k].reshape(shape3, order='F') for k, name in enumerate(names)}
+        grid_to_vtr(f"{self.filename_base}_{step:08d}", *(np.arange(0, n) for n in shape3),
+                    {name: flat[k] for k, name in enumerate(names)}, _preordered=True)
+
+    def _writer_loop(self):
+        while True:
+            item = self._queue.get()
+            if item is None:
+                return
+            slot, names, shape3, step = item
+            try:
+                slot.copied.synchronize()          # the D2H copy of this report has landed
+                self._write(slot.host.numpy(), names, shape3, step)
+            except Exception as e:                 # surfaced by flush()
+                slot.error = e
+            finally:
+                slot.done.set()
+
     def __call__(self, simulation: 'Simulation'):
         flow = simulation.flow
         if flow.i % self.interval != 0:
             return
-        d = flow.stencil.d
-        ordered = flow.output_fields_pu()      # [1 + d, nodes] in file order; one kernel on a CUDA flow
-        stage = self._staging(1 + d, ordered.shape[1], ordered.dtype, ordered.is_cuda)
-        stage.copy_(ordered)                                     # synchronous for a pinned destination
-        flat = stage.numpy()
-        shape3 = tuple(flow.resolution) + (1,) * (3 - d)
-        names = ["p"] + [f"u{'xyz'[c]}" for c in range(d)]
-        self.point_dict = {name: flat[k].reshape(shape3, order='F') for k, name in enumerate(names)}
-        grid_to_vtr(f"{self.filename_base}_{flow.i:08d}", *(np.arange(0, n) for n in shape3),
-                    {name: flat[k] for k, name in enumerate(names)}, _preordered=True)
+        names, shape3 = self._names_shape(flow)
+        rows = len(names)
+        if not (self.asynchronous and flow.f.is_cuda):
+            ordered = flow.output_fields_pu()      # [1 + d, nodes] in file order; one kernel on a CUDA flow
+            stage = self._staging(rows, ordered.shape[1], ordered.dtype, ordered.is_cuda)
+            stage.copy_(ordered)                                     # synchronous for a pinned destination
+            self._write(stage.numpy(), names, shape3, flow.i)
+            return
+        import queue
+        import threading
+        dev = flow.f.device
+        nodes = flow.f[0].numel()
+        if not self._slots or tuple(self._slots[0].dev.shape) != (rows, nodes) or self._slots[0].dev.dtype != flow.f.dtype:
+            self.flush()
+            with torch.cuda.device(dev):
+                self._slots = [_ReportSlot(rows, nodes, flow.f.dtype, dev) for _ in range(self.buffers)]
+                self._copy_stream = torch.cuda.Stream(device=dev)
+        if self._writer is None:
+            self._queue = queue.Queue()
+            self._writer = threading.Thread(target=self._writer_loop, daemon=True)
+            self._writer.start()
+        slot = self._slots[self._next % self.buffers]
+        self._next += 1
+        slot.done.wait()                           # back-pressure: this slot's previous file is on disk
+        if slot.error is not None:
+            err, slot.error = slot.error, None
+            raise err
+        slot.done.clear()
+        with torch.cuda.device(dev):
+            flow.output_fields_pu(out=slot.dev)    # the ONE kernel on the time-stepping stream
+            slot.fields_ready.record(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(self._copy_stream):
+                self._copy_stream.wait_event(slot.fields_ready)
+                slot.host.copy_(slot.dev, non_blocking=True)
+                slot.copied.record(self._copy_stream)
+        self._queue.put((slot, names, shape3, flow.i))
+
+    def flush(self):
+        """wait until every report issued so far is on disk (and re-raise a writer error)"""
+        for slot in self._slots:
+            slot.done.wait()
+            if slot.error is not None:
+                err, slot.error = slot.error, None
+                raise err
+
+    def close(self):
+        self.flush()
+        if self._writer is not None:
+            self._queue.put(None)
+            self._writer.join()
+            self._writer = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
     def output_mask(self, simulation: 'Simulation'):
         """no_collision_mask as `<filename_base>_mask.vtr` (vtk_reporter.py:49-64)"""
@@ -230,105 +322,25 @@ class EnergySpectrum(Observable):
         return torch.sum(0.5 * (uh.imag ** 2 + uh.real ** 2), dim=0)
 
 
-def _need_h5py():
-    try:
-        import h5py
-    except ImportError as e:
-        raise ImportError("HDF5Reporter / LettuceDataset need h5py, which is unavailable in this "
-                          "image; use Flow.dump / Flow.load or VTKReporter") from e
-    return h5py
+class _OutOfScope:
+    """HDF5Reporter / LettuceDataset (util/datautils.py) and write_image (ext/_reporter/write_image.py) are
+    OUT OF SCOPE of this package (HDF5 / image I/O, h5py and matplotlib are not in
+    the image).  The names exist so that `from lettuce import *` code fails with a clear message instead of an
+    AttributeError; use VTKReporter / Flow.dump / Flow.load."""
+    _what = "this reporter"
+
+    def __init__(self, *args, **kwargs):
+        raise NotImplementedError(f"{self._what} is out of scope of lettuce_b200 (HDF5 / image output; "
+                                  f"SURVEY.md section 2): use VTKReporter, Flow.dump / Flow.load")
 
 
-class HDF5Reporter(Reporter):
-    """Appends the populations to `<filebase>.h5` every `interval` steps, with the pickled flow and
-    collision as attributes (datautils.py:16-83)."""
-
-    def __init__(self, flow, collision, interval, filebase='./output', metadata=None):
-        h5py = _need_h5py()
-        from . import __version__
-        super().__init__(interval)
-        self.context = flow.context
-        self.filebase = filebase
-        with h5py.File(self.filebase + '.h5', 'w') as fs:
-            fs.attrs['lettuce_version'] = __version__
-            fs.attrs["flow"] = self._pickle_to_h5(flow)
-            fs.attrs['_collision'] = self._pickle_to_h5(collision)
-            for attr in (metadata or {}):
-                fs.attrs[attr] = metadata[attr]
-            self.shape = (flow.stencil.q, *flow.resolution)
-            fs.create_dataset(name="f", shape=(0, *self.shape), maxshape=(None, *self.shape))
-
-    def __call__(self, simulation: 'Simulation'):
-        if simulation.flow.i % self.interval == 0:
-            h5py = _need_h5py()
-            with h5py.File(self.filebase + '.h5', 'r+') as fs:
-                fs["f"].resize(fs["f"].shape[0] + 1, axis=0)
-                fs["f"][-1, ...] = self.context.convert_to_ndarray(simulation.flow.f)
-                fs.attrs['data'] = str(fs["f"].shape[0])
-                fs.attrs['steps'] = str(simulation.flow.i)
-
-    @staticmethod
-    def _pickle_to_h5(instance):
-        bytes_io = io.BytesIO()
-        pickle.dump(instance, bytes_io)
-        bytes_io.seek(0)
-        return np.void(bytes_io.getvalue())
+class HDF5Reporter(_OutOfScope):
+    _what = "HDF5Reporter"
 
 
-class LettuceDataset(torch.utils.data.Dataset):
-    """torch Dataset over the `f` snapshots of an HDF5Reporter file (datautils.py:86-160)."""
-
-    def __init__(self, filebase, transform=None, target=False, skip_idx_to_target=1):
-        h5py = _need_h5py()
-        super().__init__()
-        self.filebase = filebase
-        self.transform = transform
-        self.target = target
-        self.skip_idx_to_target = skip_idx_to_target
-        self.fs = h5py.File(self.filebase, "r")
-        self.shape = self.fs["f"].shape
-        self.keys = list(self.fs.keys())
-        self.context = self._unpickle_from_h5(self.fs.attrs["flow"]).context
-
-    def __len__(self):
-        return self.shape[0] - self.skip_idx_to_target if self.target else self.shape[0]
-
-    def __getitem__(self, idx):
-        f = self.get_data(idx)
-        target = self.get_data(idx + self.skip_idx_to_target) if self.target else []
-        if self.transform:
-            f = self.transform(f)
-            if self.target:
-                target = self.transform(target)
-        return (f, target, idx) if self.target else (f, idx)
-
-    def __del__(self):
-        fs = getattr(self, 'fs', None)
-        if fs is not None:
-            fs.close()
-
-    def get_data(self, idx):
-        return self.context.convert_to_tensor(self.fs["f"][idx])
-
-    def get_attr(self, attr):
-        return self.fs.attrs[attr]
-
-    @staticmethod
-    def _unpickle_from_h5(byte_str):
-        return pickle.load(io.BytesIO(byte_str))
+class LettuceDataset(_OutOfScope):
+    _what = "LettuceDataset"
 
 
 def write_image(filename, array2d):
-    """write_image.py:8-19 draws with matplotlib, which is unavailable in this image."""
-    try:
-        import matplotlib.pyplot as plt
-    except ImportError as e:
-        raise ImportError("write_image needs matplotlib, which is unavailable in this image") from e
-    fig, ax = plt.subplots()
-    plt.tight_layout()
-    ax.imshow(array2d)
-    ax.set_xlabel('')
-    ax.set_ylabel('')
-    ax.get_xaxis().set_visible(False)
-    ax.get_yaxis().set_visible(False)
-    plt.savefig(filename)
+    raise NotImplementedError("write_image is out of scope of lettuce_b200 (matplotlib output; SURVEY.md section 2)")

@@ -58,10 +58,14 @@ class Observable(ABC):
         out = torch.zeros(nat.LB_OBS_COUNT, dtype=torch.float64, device=f.device)
         u = torch.empty([flow.stencil.d, *flow.resolution], dtype=f.dtype, device=f.device) \
             if want_enstrophy else None
+        # the slab driver replaces the enstrophy pass (3-plane velocity halo from the neighbouring ranks)
+        enstrophy_ = getattr(flow, '_obs_enstrophy', None) if want_enstrophy else None
         with torch.cuda.device(f.device):
-            nat.check(L.lb_observables(desc, f.data_ptr(), int(want_enstrophy), nat.ptr(u),
-                                       scratch.data_ptr(), out.data_ptr(),
+            nat.check(L.lb_observables(desc, f.data_ptr(), (2 if enstrophy_ else 1) if want_enstrophy else 0,
+                                       nat.ptr(u), scratch.data_ptr(), out.data_ptr(),
                                        nat.current_stream_ptr(f.device)))
+        if enstrophy_ is not None:
+            enstrophy_(desc, u, out, scratch)
         reduce_ = getattr(flow, '_obs_allreduce', None)   # set by the slab driver: global reduction
         if reduce_ is not None:
             out = reduce_(out[None, :])[0]

@@ -275,6 +275,10 @@ class Simulation:
             for r in generic:
                 r(self)
 
+        for r in self.reporter:                    # reporters that write files in the background: files of this call
+            flush = getattr(r, 'flush', None)      # exist when the call returns
+            if callable(flush):
+                flush()
         torch.cuda.synchronize(self.context.device)
         end = timer()
         n_nodes = 1

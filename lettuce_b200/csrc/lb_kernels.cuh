@@ -218,6 +218,20 @@ __device__ __noinline__ void ll_wait(const W* src, size_t stride, int n, uint32_
   }
 }
 
+// first attempt: an ordinary load (the compiler schedules it with the population loads; a stale cached copy
+// would carry a stale tag and only send us to the slow path, never to a wrong value: word and tag are one
+// 8-byte unit)
+__device__ __forceinline__ bool ll_peek(const uint2* p, uint32_t tag, float& v) {
+  const uint2 w = *p;
+  v = __uint_as_float(w.x);
+  return w.y == tag;
+}
+__device__ __forceinline__ bool ll_peek(const uint4* p, uint32_t tag, double& v) {
+  const uint4 w = *p;
+  v = __longlong_as_double((long long)(((unsigned long long)w.z << 32) | w.x));
+  return w.y == tag && w.w == tag;
+}
+
 // NF tagged elements src[k * stride], k < NF, all loads in flight together; where a tag is not there yet (only
 // the first blocks of a step ever see that) wait out of line and load again
 template <int NF, typename T>
@@ -227,7 +241,7 @@ __device__ __forceinline__ void ll_gather(const void* base, size_t index, size_t
   const W* src = static_cast<const W*>(base) + index;
   bool ok = true;
 #pragma unroll
-  for (int k = 0; k < NF; ++k) ok &= ll_load(src + k * stride, tag, out[k]);
+  for (int k = 0; k < NF; ++k) ok &= ll_peek(src + k * stride, tag, out[k]);
   if (ok) return;
   ll_wait<W>(src, stride, NF, tag, err);
 #pragma unroll
@@ -503,25 +517,7 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
   const unsigned node = line * nz + z0;
   const size_t N = p.n_nodes;
 
-  // ---- incoming halo (multi-GPU): issued BEFORE the population loads so that both are in
-  // flight together; a thread is on at most one z face unless the line is a single vector
   constexpr int NF = zface_count<S>();
-  T hin[NF];
-  const bool in_lo = HALO && (p.halo_in_lo != nullptr) && (zv == 0);
-  const bool edge_in = HALO && (in_lo || ((p.halo_in_hi != nullptr) && (zv == nzv - 1)));
-  const bool edge_in2 = HALO && in_lo && (p.halo_in_hi != nullptr) && (nzv == 1);
-  if constexpr (HALO) {
-    const size_t lines = size_t(nx) * ny;
-    if (edge_in) {
-      if (p.halo_ll) {
-        ll_gather<NF, T>(in_lo ? p.halo_in_lo : p.halo_in_hi, line, lines, p.ll_tag_in, p.ll_err, hin);
-      } else {
-        const T* hsrc = (in_lo ? p.halo_in_lo : p.halo_in_hi) + line;
-#pragma unroll
-        for (int k = 0; k < NF; ++k) hin[k] = hsrc[k * lines];
-      }
-    }
-  }
 
   // ---- masked streaming (no_streaming_mask packed as one bit per population and node, p.sbits) ----
   // Bit 31 of a node's word says that the node or one of its 26 neighbours keeps a population
@@ -550,9 +546,24 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
   }
   uint32_t mword = 0;
   if constexpr (MODE != MODE_PLAIN) mword = ld_mask<V>(p.ncm + node);
-  // a received element is dropped where the node keeps its own value of that population (the sender does not
+  // ---- incoming halo (multi-GPU): issued right behind the population loads so that both are in flight
+  // together (LL transport: the tag test then waits for these few words only, not in front of the population
+  // loads); a thread is on at most one z face unless the line is a single vector.
+  // A received element is dropped where the node keeps its own value of that population (the sender does not
   // know the receiver's no-streaming bits: it always sends, the destination decides -- _simulation.py:171-174)
+  const bool in_lo = HALO && (p.halo_in_lo != nullptr) && (zv == 0);
+  const bool edge_in = HALO && (in_lo || ((p.halo_in_hi != nullptr) && (zv == nzv - 1)));
+  const bool edge_in2 = HALO && in_lo && (p.halo_in_hi != nullptr) && (nzv == 1);
   if (edge_in) {
+    T hin[NF] = {};
+    const size_t lines = size_t(nx) * ny;
+    if (p.halo_ll) {
+      ll_gather<NF, T>(in_lo ? p.halo_in_lo : p.halo_in_hi, line, lines, p.ll_tag_in, p.ll_err, hin);
+    } else {
+      const T* hsrc = (in_lo ? p.halo_in_lo : p.halo_in_hi) + line;
+#pragma unroll
+      for (int k = 0; k < NF; ++k) hin[k] = hsrc[k * lines];
+    }
     static_for<Q>([&](auto qc) {
       constexpr int q = decltype(qc)::value;
       if constexpr (S::e(q, 2) == 1) { if (in_lo && !(SB && kept(own_first, q))) f[q][0] = hin[zface_index<S>(q)]; }
@@ -560,7 +571,7 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
     });
   }
   if (edge_in2) {   // one-vector lines (nzv == 1): the thread is on both faces (rare: loaded here, not up front)
-    T hin2[NF];
+    T hin2[NF] = {};
     const size_t lines = size_t(nx) * ny;
     if (p.halo_ll) {
       ll_gather<NF, T>(p.halo_in_hi, line, lines, p.ll_tag_in, p.ll_err, hin2);

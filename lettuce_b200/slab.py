@@ -232,6 +232,8 @@ class SlabSimulation(Simulation):
                                           "into planes whose mask the sender does not have")
             self._check_slab_outlets()
         flow._obs_allreduce = self._reduce_obs
+        if self.world > 1 and transport != 'host':
+            flow._obs_enstrophy = self._enstrophy
         self.hi_q, self.lo_q = zface_populations(flow.stencil)
         self.lines = 1
         for n in flow.resolution[:-1]:
@@ -467,16 +469,17 @@ class SlabSimulation(Simulation):
             req.wait()
         return torch.cat([from_down, u, from_up], dim=-1).contiguous()
 
-    def _enstrophy(self, desc, u_buf, obs_row):
+    def _enstrophy(self, desc, u_buf, obs_row, scratch=None):
         if self.world == 1:
             return Simulation._enstrophy(self, desc, u_buf, obs_row)
         if min(self.flow.resolution[:-1]) < 3:
             raise NotImplementedError("Enstrophy needs at least 3 nodes per axis (6th-order periodic gradient)")
         dev = self.context.device
+        scratch = self._obs_scratch if scratch is None else scratch
         u_ext = self._exchange_velocity_halo(u_buf)
         with torch.cuda.device(dev):
             nat.check(nat.lib().lb_enstrophy_slab(desc, u_ext.data_ptr(), self.GRADIENT_RADIUS,
-                                                  self._obs_scratch.data_ptr(), obs_row.data_ptr(),
+                                                  scratch.data_ptr(), obs_row.data_ptr(),
                                                   nat.current_stream_ptr(dev)))
 
     def _run_segment(self, n, fused):
