@@ -93,8 +93,14 @@ typedef struct lb_desc {
   double acceleration[3];
   double force_tau;
   int32_t force;       /* LB_FORCE_NONE | LB_FORCE_GUO | LB_FORCE_SHAN_CHEN */
-  int32_t reserved;
+  int32_t kernel_flags; /* 0 = the library chooses; LB_KF_* select a kernel variant explicitly (tests, A/B timing) */
 } lb_desc;
+/* lb_desc.kernel_flags: every variant produces bit-identical results */
+enum {
+  LB_KF_NO_TMA = 1,    /* never use the persistent TMA-prefetch step kernel                                */
+  LB_KF_FORCE_TMA = 2, /* use it wherever it applies (plain lattices of whole, 16-byte aligned tiles)      */
+  LB_KF_NO_LOOP = 4    /* one launch per time step also where the cooperative multi-step kernel would fit */
+};
 
 /* One entry per boundary object, in the order lettuce sorted them
  * (_simulation.py:57-58): entry i applies where no_collision_mask == i + 1.

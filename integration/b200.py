@@ -20,6 +20,7 @@ import os
 import torch
 
 LIB_ENV = "LETTUCE_B200_LIB"          # path of liblettuce_b200.so (default: next to this file)
+ABI_VERSION = 6                       # LB_ABI_VERSION of the include/lettuce_b200.h these structures mirror
 _lib = None
 
 LB_BND_BOUNCE_BACK, LB_BND_EQUILIBRIUM, LB_BND_ABB_OUTLET, LB_BND_EQ_OUTLET_P = 1, 2, 3, 4
@@ -33,7 +34,7 @@ class Desc(C.Structure):            # lb_desc
     _fields_ = [("stencil", C.c_int32), ("dtype", C.c_int32), ("collision", C.c_int32),
                 ("ndim", C.c_int32), ("dims", C.c_int64 * 3), ("tau", C.c_double), ("tau_minus", C.c_double),
                 ("acceleration", C.c_double * 3), ("force_tau", C.c_double), ("force", C.c_int32),
-                ("reserved", C.c_int32)]
+                ("kernel_flags", C.c_int32)]
 
 
 class Boundary(C.Structure):        # lb_boundary
@@ -58,8 +59,36 @@ def lib():
         L.lb_step.argtypes = [C.POINTER(Desc), C.POINTER(Fields), C.c_int, C.c_void_p]
         L.lb_pack_streaming_mask.argtypes = [C.POINTER(Desc), C.c_void_p, C.c_void_p, C.c_void_p]
         L.lb_last_error.restype = C.c_char_p
+        L.lb_abi_version.restype = C.c_int
+        if L.lb_abi_version() != ABI_VERSION:      # struct drift would corrupt the C structures silently
+            raise RuntimeError(f"liblettuce_b200.so has ABI version {L.lb_abi_version()}, this binding was written "
+                               f"for {ABI_VERSION}")
         _lib = L
     return _lib
+
+
+def check_supported(simulation):
+    """what lettuce_b200.Simulation refuses, refused here as well (instead of a silently different result)"""
+    flow = simulation.flow
+    eq = type(flow.equilibrium).__name__ if getattr(flow, "equilibrium", None) is not None else "QuadraticEquilibrium"
+    if eq not in ("QuadraticEquilibrium", "QuadraticEquilibriumLessMemory"):
+        raise NotImplementedError(f"equilibrium '{eq}' has no native kernel (the kernels evaluate the quadratic one)")
+    if not flow.f.is_contiguous():
+        raise ValueError("flow.f must be contiguous")
+    outlets = [(i, b) for i, b in enumerate(simulation.boundaries[1:], start=1)
+               if type(b).__name__ in ("AntiBounceBackOutlet", "EquilibriumOutletP")]
+    if outlets and getattr(simulation.collision, "force", None) is not None:
+        raise NotImplementedError("outlet boundaries together with a forcing scheme are not supported natively")
+    for i, b in outlets:
+        if min(flow.resolution) < 2:
+            raise ValueError("outlet boundaries need at least 2 nodes along every axis")
+        axis = abs(_outlet_direction(b))
+        for j, other in outlets:
+            # a lower-index outlet on another axis crosses this outlet's neighbour plane: the kernel takes the
+            # neighbour's velocity from its incoming populations and cannot redo that outlet on it
+            if j < i and abs(_outlet_direction(other)) != axis:
+                raise NotImplementedError(f"outlet boundary {i}: the lower-index outlet {j} crosses its neighbour "
+                                          f"plane; this ordering is not supported natively")
 
 
 def make_desc(simulation) -> Desc:
@@ -156,6 +185,7 @@ def build_call(simulation, pack=True):
     """(Desc, Fields, keepalive) for one lb_step call.  `pack=False` leaves a non-zero
     no_streaming_mask unpacked (host-side tests without a GPU)."""
     flow = simulation.flow
+    check_supported(simulation)
     d = make_desc(simulation)
     fl = Fields()
     fl.f, fl.f_next = flow.f.data_ptr(), flow.f_next.data_ptr()
@@ -170,8 +200,9 @@ def build_call(simulation, pack=True):
             bits = getattr(simulation, "_b200_bits", None)       # packed once; rebuild if the mask object changes
             if bits is None or bits[0] != (nsm.data_ptr(), nsm._version):
                 words = torch.empty(list(flow.resolution), dtype=torch.int32, device=nsm.device)
-                rc = lib().lb_pack_streaming_mask(d, nsm.contiguous().data_ptr(), words.data_ptr(),
-                                                  torch.cuda.current_stream().cuda_stream)
+                with torch.cuda.device(nsm.device):
+                    rc = lib().lb_pack_streaming_mask(d, nsm.contiguous().data_ptr(), words.data_ptr(),
+                                                      torch.cuda.current_stream(nsm.device).cuda_stream)
                 if rc:
                     raise RuntimeError(lib().lb_last_error().decode())
                 bits = simulation._b200_bits = ((nsm.data_ptr(), nsm._version), words)
@@ -185,7 +216,8 @@ def invoke(simulation):
     flow = simulation.flow
     d, fl, keep = build_call(simulation)
     simulation._b200_keep = keep        # the boundary tensors stay alive while the launch is in flight
-    rc = lib().lb_step(d, fl, 1, torch.cuda.current_stream().cuda_stream)
+    with torch.cuda.device(flow.f.device):      # the flow's device, whatever the current one is
+        rc = lib().lb_step(d, fl, 1, torch.cuda.current_stream(flow.f.device).cuda_stream)
     if rc:
         raise RuntimeError(lib().lb_last_error().decode())
     flow.f, flow.f_next = flow.f_next, flow.f

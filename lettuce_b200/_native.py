@@ -50,7 +50,10 @@ class LbDesc(C.Structure):
     _fields_ = [("stencil", C.c_int32), ("dtype", C.c_int32), ("collision", C.c_int32),
                 ("ndim", C.c_int32), ("dims", C.c_int64 * 3), ("tau", C.c_double),
                 ("tau_minus", C.c_double), ("acceleration", C.c_double * 3), ("force_tau", C.c_double),
-                ("force", C.c_int32), ("reserved", C.c_int32)]
+                ("force", C.c_int32), ("kernel_flags", C.c_int32)]
+
+
+LB_KF_NO_TMA, LB_KF_FORCE_TMA, LB_KF_NO_LOOP = 1, 2, 4
 
 
 class LbBoundary(C.Structure):
@@ -149,7 +152,7 @@ def check(rc: int):
 
 def make_desc(stencil_name: str, dtype: torch.dtype, resolution: Sequence[int], collision: int = LB_COLL_NONE,
               tau: float = 1.0, tau_minus: float = 1.0, force: int = LB_FORCE_NONE,
-              acceleration: Sequence[float] = (), force_tau: float = 1.0) -> LbDesc:
+              acceleration: Sequence[float] = (), force_tau: float = 1.0, kernel_flags: int = 0) -> LbDesc:
     if stencil_name not in STENCIL_IDS:
         raise NativeError(f"stencil {stencil_name} has no native kernel (D2Q9, D3Q19, D3Q27 only)")
     if dtype not in DTYPE_IDS:
@@ -161,6 +164,7 @@ def make_desc(stencil_name: str, dtype: torch.dtype, resolution: Sequence[int], 
         d.dims[i] = int(resolution[i]) if i < len(resolution) else 1
     d.tau, d.tau_minus = float(tau), float(tau_minus)
     d.force, d.force_tau = int(force), float(force_tau)
+    d.kernel_flags = int(kernel_flags)
     if force != LB_FORCE_NONE and len(acceleration) != len(resolution):
         raise NativeError(f"acceleration has {len(acceleration)} components on a {len(resolution)}-D lattice")
     for i, a in enumerate(acceleration):

@@ -129,7 +129,8 @@ class Simulation:
         d = self.collision.native_descriptor(self.flow)
         return nat.make_desc(type(self.flow.stencil).__name__, self.flow.f.dtype, self.flow.resolution,
                              d['collision'], d.get('tau', 1.0), d.get('tau_minus', 1.0),
-                             d.get('force', nat.LB_FORCE_NONE), d.get('acceleration', ()), d.get('force_tau', 1.0))
+                             d.get('force', nat.LB_FORCE_NONE), d.get('acceleration', ()), d.get('force_tau', 1.0),
+                             kernel_flags=getattr(self, 'kernel_flags', 0))
 
     def _pack_streaming_bits(self, desc):
         """no_streaming_mask [q, *res] uint8 -> one uint32 per node (bit q), once per mask version;

@@ -248,6 +248,10 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   c.mode = p.sbits ? lb::MODE_NCM_SBITS : (p.ncm ? lb::MODE_NCM : lb::MODE_PLAIN);
   c.stream = do_stream;
   c.halo = fl->halo != nullptr;
+  static const char* tma_env = getenv("LB_TMA");   // A/B timing: 0 = never, 1 = wherever the TMA kernel applies
+  if (tma_env) c.tma = atoi(tma_env) != 0 ? 1 : 0;
+  if (d->kernel_flags & LB_KF_NO_TMA) c.tma = 0;
+  if (d->kernel_flags & LB_KF_FORCE_TMA) c.tma = 1;
   c.vec = do_stream ? vector_width<S, T>(c.collision, c.mode, g, fl->f, fl->f_next, p.ncm, p.sbits,
                                             p.has_outlet && p.sbits == nullptr) : 1;
   p.nzv = g.nz / c.vec;
@@ -343,7 +347,7 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
     // small lattice: all n_steps in ONE cooperative launch (grid-wide barrier between steps);
     // launch_one falls back to the per-step path when the grid is not co-resident
     static const bool no_loop = getenv("LB_NO_LOOP") != nullptr;   // A/B timing only
-    if (!no_loop) {
+    if (!no_loop && !(d->kernel_flags & LB_KF_NO_LOOP)) {
       c.loop_steps = n_steps;
       c.obs = fl->obs_out != nullptr;
       p.f_in = a; p.f_out = b;
@@ -396,7 +400,7 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
     cudaError_t e = lb::launch_step<S, T>(c, p, st);
     if (e != cudaSuccess) return fail(LB_ECUDA, "step kernel launch failed: %s", cudaGetErrorString(e));
     if (c.obs) {   // second stage of the fused reduction: block partials -> obs_out[s]
-      e = launch_obs_finish(p.obs, (p.n_threads + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK, p.obs_out, lb::N_OBS_PART, st);
+      e = launch_obs_finish(p.obs, c.obs_blocks, p.obs_out, lb::N_OBS_PART, st);
       if (e != cudaSuccess) return fail(LB_ECUDA, "observable reduction launch failed: %s", cudaGetErrorString(e));
     }
     if (h && h->mode != LB_HALO_PACKED && h->mode != LB_HALO_LL) {
@@ -656,6 +660,109 @@ int moments_stencil(const lb_desc* d, const Geometry& g, const void* f, void* r,
   return fail(LB_EINVAL, "bad stencil");
 }
 
+// The same with V consecutive nodes of the contiguous axis per thread and 16-byte loads: 30 vector loads per V nodes
+// instead of 36 scalar loads per node (the stencil taps come from L1 / L2: the kernel is bound by the number of
+// load requests, not by HBM), one partial sum per block and obs_finish_kernel behind it (no ticket on the blocks).
+// The whole line and the ghost offset must be multiples of V (host-checked).
+template <typename T, int V>
+__device__ __forceinline__ void diff6_vec(const T* __restrict__ u, size_t first, long long stride, long long i, long long n,
+                                          bool periodic, T (&out)[V]) {
+  // derivative along a NON-contiguous axis: six whole vectors at i-3 .. i+3 of that axis; `first` = this thread's
+  // vector with the axis coordinate set to 0
+  auto vec_at = [&](int s) {
+    long long j = i + s;
+    if (periodic) { if (j < 0) j += n; if (j >= n) j -= n; }
+    return lb::ld_vec<T, V>(u + first + size_t(j) * size_t(stride));
+  };
+  const lb::Vec<T, V> m3 = vec_at(-3), m2 = vec_at(-2), m1 = vec_at(-1), p1 = vec_at(1), p2 = vec_at(2), p3 = vec_at(3);
+#pragma unroll
+  for (int k = 0; k < V; ++k)
+    out[k] = T(-1.0 / 60) * m3.v[k] + T(3.0 / 20) * m2.v[k] + T(-3.0 / 4) * m1.v[k] + T(3.0 / 4) * p1.v[k] +
+             T(-3.0 / 20) * p2.v[k] + T(1.0 / 60) * p3.v[k];
+}
+
+template <typename T, int V>
+__device__ __forceinline__ void diff6_line(const T* __restrict__ line, unsigned zv, unsigned nzv, bool periodic, T (&out)[V]) {
+  // derivative along the contiguous axis: a window of the line around this thread's vector
+  constexpr int W = (3 + V - 1) / V;      // vectors each side that cover the radius
+  T a[(2 * W + 1) * V];
+#pragma unroll
+  for (int w = -W; w <= W; ++w) {
+    long long j = (long long)zv + w;
+    if (periodic) { if (j < 0) j += nzv; if (j >= (long long)nzv) j -= nzv; }
+    const lb::Vec<T, V> v = lb::ld_vec<T, V>(line + j * V);   // non-periodic: ghost planes make j valid (may be < 0)
+#pragma unroll
+    for (int k = 0; k < V; ++k) a[(w + W) * V + k] = v.v[k];
+  }
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    const int c = W * V + k;
+    out[k] = T(-1.0 / 60) * a[c - 3] + T(3.0 / 20) * a[c - 2] + T(-3.0 / 4) * a[c - 1] + T(3.0 / 4) * a[c + 1] +
+             T(-3.0 / 20) * a[c + 2] + T(1.0 / 60) * a[c + 3];
+  }
+}
+
+template <typename T, int D, int V>
+__global__ void __launch_bounds__(lb::STEP_BLOCK)
+enstrophy_vec_kernel(const T* __restrict__ u, unsigned n0, unsigned n1, unsigned n2, unsigned n_threads, unsigned ghost,
+                     lb::ObsScratch scratch) {
+  const unsigned tid = blockIdx.x * lb::STEP_BLOCK + threadIdx.x;
+  double acc = 0.0;
+  if (tid < n_threads) {
+    const bool per = ghost == 0;
+    if constexpr (D == 2) {
+      const unsigned e1 = n1 + 2 * ghost, nzv = n1 / V;
+      const size_t n_ext = size_t(n0) * e1;
+      const unsigned i0 = tid / nzv, zv = tid - i0 * nzv;
+      const T* u0 = u;
+      const T* u1 = u + n_ext;
+      T d1u0[V], d0u1[V];
+      diff6_line<T, V>(u0 + size_t(i0) * e1 + ghost, zv, nzv, per, d1u0);                  // d u0 / d y
+      diff6_vec<T, V>(u1, size_t(ghost) + size_t(zv) * V, e1, i0, n0, true, d0u1);         // d u1 / d x
+#pragma unroll
+      for (int k = 0; k < V; ++k) { const T w = d1u0[k] - d0u1[k]; acc += double(w * w); }
+    } else {
+      const unsigned e2 = n2 + 2 * ghost, nzv = n2 / V;
+      const size_t n_ext = size_t(n0) * n1 * e2;
+      const unsigned i0 = tid / (n1 * nzv);
+      const unsigned r = tid - i0 * n1 * nzv;
+      const unsigned i1 = r / nzv, zv = r - i1 * nzv;
+      const T* u0 = u;
+      const T* u1 = u + n_ext;
+      const T* u2 = u + 2 * n_ext;
+      const size_t zoff = size_t(ghost) + size_t(zv) * V;
+      const size_t b0 = size_t(i1) * e2 + zoff;                // this vector with i0 = 0
+      const size_t b1 = size_t(i0) * n1 * e2 + zoff;           // ... with i1 = 0
+      const size_t ln = (size_t(i0) * n1 + i1) * e2 + ghost;   // this line's first interior element
+      const long long s0 = (long long)n1 * e2, s1 = e2;
+      T a[V], b[V];
+      diff6_vec<T, V>(u0, b1, s1, i1, n1, true, a);            // wz = d1 u0 - d0 u1
+      diff6_vec<T, V>(u1, b0, s0, i0, n0, true, b);
+      T wz[V];
+#pragma unroll
+      for (int k = 0; k < V; ++k) wz[k] = a[k] - b[k];
+      diff6_vec<T, V>(u2, b1, s1, i1, n1, true, a);            // wx = d1 u2 - d2 u1
+      diff6_line<T, V>(u1 + ln, zv, nzv, per, b);
+      T wx[V];
+#pragma unroll
+      for (int k = 0; k < V; ++k) wx[k] = a[k] - b[k];
+      diff6_line<T, V>(u0 + ln, zv, nzv, per, a);              // wy = d2 u0 - d0 u2
+      diff6_vec<T, V>(u2, b0, s0, i0, n0, true, b);
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        const T wy = a[k] - b[k];
+        acc += double(wz[k] * wz[k]) + double(wx[k] * wx[k] + wy * wy);
+      }
+    }
+  }
+  double z1 = 0.0, z2 = 0.0;
+  lb::block_reduce3<lb::STEP_BLOCK>(acc, z1, z2);
+  if (threadIdx.x == 0) {
+    double* bp = scratch.block_partials + size_t(blockIdx.x) * lb::N_OBS_PART;
+    bp[0] = acc; bp[1] = 0.0; bp[2] = 0.0;
+  }
+}
+
 template <typename T>
 int enstrophy_typed(const lb_desc* d, const Geometry& g, const void* u, int ghost, void* scratch, double* obs_out,
                     cudaStream_t st) {
@@ -668,6 +775,23 @@ int enstrophy_typed(const lb_desc* d, const Geometry& g, const void* u, int ghos
   lb::ObsScratch sc;
   const int rc = obs_prepare(g, scratch, &sc, st);
   if (rc) return rc;
+  constexpr int V = 16 / int(sizeof(T));
+  const unsigned nlast = unsigned(d->dims[g.d - 1]);
+  static const bool scalar_only = getenv("LB_ENSTROPHY_SCALAR") != nullptr;   // A/B timing only
+  if (!scalar_only && nlast % V == 0 && unsigned(ghost) % V == 0 && aligned_to(u, 16) && nlast / V >= 2u * ((3 + V - 1) / V) + 1u) {
+    const unsigned n_threads = g.n_nodes / V;
+    const unsigned blocks = (n_threads + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK;
+    if (g.d == 2)
+      enstrophy_vec_kernel<T, 2, V><<<blocks, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(u), (unsigned)d->dims[0],
+                                                                      (unsigned)d->dims[1], 1u, n_threads, unsigned(ghost), sc);
+    else
+      enstrophy_vec_kernel<T, 3, V><<<blocks, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(u), (unsigned)d->dims[0],
+                                                                      (unsigned)d->dims[1], (unsigned)d->dims[2], n_threads,
+                                                                      unsigned(ghost), sc);
+    LB_CUDA(cudaGetLastError());
+    LB_CUDA(launch_obs_finish(sc, blocks, obs_out + LB_OBS_ENSTROPHY, 1, st));
+    return LB_OK;
+  }
   const unsigned grid = (g.n_nodes + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK;
   if (g.d == 2)
     enstrophy_kernel<T, 2><<<grid, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(u), (unsigned)d->dims[0],

@@ -497,14 +497,19 @@ constexpr int step_min_blocks() {
   return 1;
 }
 
-// One time step of the lattice for this thread: f_in -> f_out (+ observables of f_in when OBS)
-template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO, bool TICKET>
-__device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __restrict__ f_in, T* __restrict__ f_out,
-                                          double* obs_out, T* u_out) {
+// One time step of the lattice for this thread and tile `blk` (STEP_BLOCK threads x V nodes): f_in -> f_out, and the
+// thread's observables of f_in (sum 0.5 |u|^2, max |u|^2, sum rho over its V nodes; zero for a thread beyond the
+// lattice) into t_e / t_m2 / t_mass when OBS.  SMEM_IN: the tile's populations are already in shared memory
+// (smem_in[q][STEP_BLOCK * V], brought in by bulk copies) instead of global memory.
+struct NoRefill { __device__ __forceinline__ void operator()() const {} };
+
+template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO, bool SMEM_IN = false,
+          class Refill = NoRefill>
+__device__ __forceinline__ void step_tile(const StepParams<T>& p, const T* __restrict__ f_in, T* __restrict__ f_out,
+                                          T* u_out, unsigned blk, const T* smem_in, T& t_e, T& t_m2, T& t_mass,
+                                          Refill smem_tile_consumed = Refill{}) {
   constexpr int Q = S::Q;
   const unsigned lane = threadIdx.x & 31u;
-  unsigned blk = blockIdx.x + p.block_rot;
-  if (blk >= gridDim.x) blk -= gridDim.x;
   const unsigned tid = blk * STEP_BLOCK + threadIdx.x;
   const bool active = tid < p.n_threads;
   const unsigned t = active ? tid : p.n_threads - 1u;  // clamp: keeps address math valid
@@ -539,10 +544,17 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
   {
     static_for<Q>([&](auto qc) {
       constexpr int q = decltype(qc)::value;
-      const Vec<T, V> v = ld_vec<T, V>(f_in + size_t(q) * N + node);
+      const Vec<T, V> v = SMEM_IN ? ld_vec<T, V>(smem_in + q * (STEP_BLOCK * V) + threadIdx.x * V)
+                                  : ld_vec<T, V>(f_in + size_t(q) * N + node);
 #pragma unroll
       for (int k = 0; k < V; ++k) f[q][k] = v.v[k];
     });
+  }
+  if constexpr (SMEM_IN) {
+    // the stage is free as soon as every thread holds its values: the producer refills it while this tile
+    // computes and stores (the caller issues the next bulk copies right behind this barrier)
+    __syncthreads();
+    smem_tile_consumed();
   }
   uint32_t mword = 0;
   if constexpr (MODE != MODE_PLAIN) mword = ld_mask<V>(p.ncm + node);
@@ -660,6 +672,9 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
     const bool st_right = active && has_right, st_noright = active && !has_right;
     const bool edge_up = active && (lane == 31 || last_in_line);   // owns the element that leaves the warp upwards
     const bool edge_dn = active && (lane == 0 || first_in_line);
+    // z-slabs: this thread's upward / downward element leaves through the slab's z face (to the neighbour rank)
+    const bool cross_up = HALO && active && last_in_line && p.halo_hi != nullptr;
+    const bool cross_dn = HALO && active && first_in_line && p.halo_lo != nullptr;
     // element offset of that edge element relative to this thread's own vector in the destination line
     const unsigned d_up = last_in_line ? 0u - z0 : unsigned(V);
     const unsigned d_dn = first_in_line ? nz - 1u : 0u - 1u;
@@ -733,29 +748,15 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
       T* const bq = f_out + size_t(q) * N;               // uniform
 
       // The ONE element of this thread that leaves its vector upwards (ez = +1) / downwards (ez = -1): into the
-      // next lane's vector, around the line end (periodic lattice), or -- z-slabs -- through the slab's z face to
-      // the neighbour rank.  `local_ok` = the destination node does not keep its own value (masked streaming).
-      // A z-face element is ALWAYS sent: the receiver drops it where its node keeps the population.
+      // next lane's vector or around the line end (periodic lattice).  `local_ok` = the destination node does not
+      // keep its own value (masked streaming).  With z-slabs the element of a line-end thread leaves through the
+      // slab's z face instead: that is done for all face populations together behind this loop (send_faces).
+      // Packed halo layouts ALSO store to the local wrap position: the value there is never read (the
+      // neighbour's element is consumed from the receive buffer at load time and scattered at the end
+      // of the call), but without it the boundary sector of every line stays partially written, and
+      // every partially written sector costs a read-modify-write in HBM (measured: 10 % of a step).
       [[maybe_unused]] auto push_edge = [&](T val, bool up, bool local_ok) {
-        constexpr int zf = zface_index<S>(q);
-        const bool cross = HALO && (up ? (last_in_line && p.halo_hi != nullptr) : (first_in_line && p.halo_lo != nullptr));
-        if constexpr (HALO) {
-          if (cross) {
-            if (staged) {
-              const unsigned slot = (unsigned((up ? 0 : NF) + zf) << sshift) | lline;
-              stage_val[slot] = val;
-              stage_dst[slot] = dlines;
-            } else {
-              halo_store(up ? p.halo_hi : p.halo_lo,
-                         (long long)(p.halo_compact ? zf : q) * p.halo_qs + (long long)(dlines) * p.halo_ls +
-                             (up ? p.halo_hi_off : p.halo_lo_off), val);
-            }
-          }
-        }
-        // Packed layouts: ALSO store to the local wrap position.  The value there is never read (the
-        // neighbour's element is consumed from the receive buffer at load time and scattered at the end
-        // of the call), but without it the boundary sector of every line stays partially written, and
-        // every partially written sector costs a read-modify-write in HBM (measured: 10 % of a step).
+        const bool cross = up ? cross_up : cross_dn;
         if ((!cross || p.halo_compact) && local_ok) bq[idx + (up ? d_up : d_dn)] = val;
       };
 
@@ -853,6 +854,35 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
       stream_all(std::false_type{});
     }
 
+    // ---- z-slab faces: the line-end threads hand their NF face populations to the neighbour rank -- staged per
+    // block (packed layouts) or stored directly.  One pass for all populations, entered by the line-end lanes
+    // only: the streaming loop above stays the plain kernel's.  A face element is ALWAYS sent: the receiver
+    // drops it where its node keeps the population (masked streaming).
+    if constexpr (HALO) {
+      if (cross_up || cross_dn) {
+        static_for<Q>([&](auto qc) {
+          constexpr int q = decltype(qc)::value;
+          constexpr int ez = S::e(q, 2);
+          if constexpr (ez != 0) {
+            constexpr int zf = zface_index<S>(q);
+            constexpr bool up = ez > 0;
+            if (up ? cross_up : cross_dn) {
+              const unsigned dlines = xs[S::e(q, 0) + 1] + ys[S::e(q, 1) + 1];
+              const T val = up ? f[q][V - 1] : f[q][0];
+              if (staged) {
+                const unsigned slot = (unsigned((up ? 0 : NF) + zf) << sshift) | lline;
+                stage_val[slot] = val;
+                stage_dst[slot] = dlines;
+              } else {
+                halo_store(up ? p.halo_hi : p.halo_lo,
+                           (long long)(p.halo_compact ? zf : q) * p.halo_qs + (long long)(dlines) * p.halo_ls +
+                               (up ? p.halo_hi_off : p.halo_lo_off), val);
+              }
+            }
+          }
+        });
+      }
+    }
     if constexpr (HALO && V > 1) {
       if (staged) {   // block-uniform
         __syncthreads();
@@ -872,9 +902,23 @@ __device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __res
     }
   }
 
+  if constexpr (OBS) {
+    t_e = active ? acc_e : T(0);
+    t_m2 = active ? acc_m2 : T(0);
+    t_mass = active ? acc_mass : T(0);
+  }
+}
+
+// One time step for the tile of this thread block + the fused reduction of its observables
+template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO, bool TICKET>
+__device__ __forceinline__ void step_body(const StepParams<T>& p, const T* __restrict__ f_in, T* __restrict__ f_out,
+                                          double* obs_out, T* u_out) {
+  unsigned blk = blockIdx.x + p.block_rot;
+  if (blk >= gridDim.x) blk -= gridDim.x;
+  T acc_e = T(0), acc_m2 = T(0), acc_mass = T(0);
+  step_tile<S, T, V, COLL, MODE, OBS, STREAM, HALO>(p, f_in, f_out, u_out, blk, nullptr, acc_e, acc_m2, acc_mass);
   // ---- fused observables of f_in ------------------------------------------------------------
   if constexpr (OBS) {
-    if (!active) { acc_e = T(0); acc_m2 = T(0); acc_mass = T(0); }
     if constexpr (TICKET) {
       reduce_observables<STEP_BLOCK>(double(acc_e), double(acc_m2), double(acc_mass), p.obs, obs_out);
     } else {
@@ -900,6 +944,99 @@ step_kernel(const __grid_constant__ StepParams<T> p) {
   asm volatile("griddepcontrol.launch_dependents;");
   asm volatile("griddepcontrol.wait;" ::: "memory");
   step_body<S, T, V, COLL, MODE, OBS, STREAM, HALO, false>(p, p.f_in, p.f_out, p.obs_out, p.u_out);
+}
+
+// --------------------------------------------------------------------------------------
+// Persistent variant with TMA prefetch (plain lattices: no masks, no halos).  One CTA per resident slot of the
+// device walks over the tiles blockIdx.x, blockIdx.x + gridDim.x, ...; a tile's Q population chunks (each
+// STEP_BLOCK * V contiguous values) are brought into shared memory by Q 1-D bulk copies (cp.async.bulk, the TMA
+// engine) that complete on an mbarrier, TMA_STAGES tiles deep.  The threads read their values from shared memory,
+// hand the stage back (one __syncthreads) and compute / store while the NEXT tiles' copies are in flight: the
+// loads of a CTA no longer wait behind its own arithmetic, which is what bounded the register-heavy kernels
+// (D3Q27 KBC: 160 registers, 3 CTAs per SM, top stall long_scoreboard at 0.91 of the HBM roofline).
+// --------------------------------------------------------------------------------------
+constexpr int TMA_STAGES = 2;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, unsigned bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy (bytes and both addresses multiples of 16), completion counted on `bar`
+__device__ __forceinline__ void bulk_copy_g2s(void* dst, const void* src, unsigned bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+template <class S, typename T, int V>
+constexpr size_t tma_smem_bytes() { return size_t(TMA_STAGES) * S::Q * STEP_BLOCK * V * sizeof(T); }
+
+template <class S, typename T, int V, int COLL, bool OBS>
+__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V, COLL, MODE_PLAIN>())
+step_tma_kernel(const __grid_constant__ StepParams<T> p) {
+  constexpr unsigned TILE = STEP_BLOCK * V;                    // nodes per tile
+  constexpr unsigned TILE_BYTES = TILE * sizeof(T);            // one population chunk
+  constexpr unsigned STAGE_ELEMS = S::Q * TILE;
+  extern __shared__ __align__(128) unsigned char tma_smem[];
+  T* const stages = reinterpret_cast<T*>(tma_smem);
+  __shared__ uint64_t full[TMA_STAGES];
+  asm volatile("griddepcontrol.launch_dependents;");
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < TMA_STAGES; ++s) mbar_init(&full[s], 1u);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const unsigned n_tiles = p.n_threads / STEP_BLOCK;           // whole tiles only (host-checked)
+  const size_t N = p.n_nodes;
+  auto issue = [&](unsigned tile, int s) {                     // one thread
+    mbar_arrive_expect_tx(&full[s], S::Q * TILE_BYTES);
+    const T* src = p.f_in + size_t(tile) * TILE;
+    T* dst = stages + size_t(s) * STAGE_ELEMS;
+#pragma unroll
+    for (int q = 0; q < S::Q; ++q) bulk_copy_g2s(dst + q * TILE, src + q * N, TILE_BYTES, &full[s]);
+  };
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int s = 0; s < TMA_STAGES; ++s) {
+      const unsigned tile = blockIdx.x + unsigned(s) * gridDim.x;
+      if (tile < n_tiles) issue(tile, s);
+    }
+  }
+  double e = 0.0, m2 = 0.0, mass = 0.0;
+  unsigned it = 0;
+  for (unsigned tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++it) {
+    const int s = int(it % TMA_STAGES);
+    mbar_wait(&full[s], (it / TMA_STAGES) & 1u);
+    T te = T(0), tm2 = T(0), tmass = T(0);
+    step_tile<S, T, V, COLL, MODE_PLAIN, OBS, true, false, true>(
+        p, p.f_in, p.f_out, p.u_out, tile, stages + size_t(s) * STAGE_ELEMS, te, tm2, tmass, [&]() {
+          const unsigned next = tile + unsigned(TMA_STAGES) * gridDim.x;
+          if (threadIdx.x == 0 && next < n_tiles) issue(next, s);
+        });
+    if constexpr (OBS) { e += double(te); m2 = fmax(m2, double(tm2)); mass += double(tmass); }
+  }
+  if constexpr (OBS) {   // one partial per CTA; obs_finish_kernel adds them up (fixed order: deterministic)
+    block_reduce3<STEP_BLOCK>(e, m2, mass);
+    if (threadIdx.x == 0) {
+      double* bp = p.obs.block_partials + size_t(blockIdx.x) * N_OBS_PART;
+      bp[0] = e; bp[1] = m2; bp[2] = mass;
+    }
+  }
 }
 
 // Small lattices (the whole grid co-resident on the 148 SMs, state in L2): ONE cooperative launch
@@ -1015,7 +1152,16 @@ struct StepConfig {
   bool obs;
   bool stream;
   bool halo;      // z-slab halo plumbing compiled in (multi-GPU)
+  int tma = -1;   // persistent TMA-prefetch kernel: -1 = the compiled-in default, 0 = never, 1 = wherever it applies
+  unsigned obs_blocks = 0;   // out: thread blocks that wrote a partial of the fused reduction
 };
+
+// where the persistent TMA kernel is the default (measured): the register-heavy
+// collisions of D3Q27, whose three CTAs per SM cannot cover their own load latency
+template <class S, typename T, int COLL>
+constexpr bool tma_default() {
+  return S::Q == 27 && (COLL == COLL_KBC || COLL == COLL_TRT || COLL == COLL_SMAGORINSKY);
+}
 
 // one explicit specialisation per (stencil, dtype, collision), each in its own translation unit
 // (lb_inst_*.cu) so that `make -j` spreads the ~400 kernel variants over all cores
@@ -1073,9 +1219,55 @@ int coresident_blocks(K kernel) {
   return cached;
 }
 
+template <class S, typename T, int V, int COLL, bool OBS>
+cudaError_t launch_tma(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+  auto kernel = step_tma_kernel<S, T, V, COLL, OBS>;
+  constexpr size_t smem = tma_smem_bytes<S, T, V>();
+  static int resident = -1;   // CTAs the device holds at once
+  if (resident < 0) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    if (e == cudaSuccess) e = cudaGetDevice(&dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, STEP_BLOCK, smem);
+    if (e != cudaSuccess) return e;
+    resident = sms * per_sm;
+    if (resident <= 0) return cudaErrorLaunchOutOfResources;
+  }
+  const unsigned n_tiles = p.n_threads / STEP_BLOCK;
+  const unsigned grid = n_tiles < unsigned(resident) ? n_tiles : unsigned(resident);
+  c.obs_blocks = grid;
+  static const bool no_pdl = getenv("LB_NO_PDL") != nullptr;   // A/B timing only
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(STEP_BLOCK);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = no_pdl ? 0 : 1;
+  return cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
+// the persistent TMA kernel applies to: plain lattices (no masks, no halos) made of whole tiles whose population
+// chunks are 16-byte aligned in global memory
+template <typename T, int V>
+bool tma_applicable(const StepConfig& c, const StepParams<T>& p) {
+  return V > 1 && c.stream && !c.halo && c.mode == MODE_PLAIN && c.loop_steps <= 1 && p.n_threads % STEP_BLOCK == 0 &&
+         (size_t(p.n_nodes) * sizeof(T)) % 16 == 0 && (reinterpret_cast<uintptr_t>(p.f_in) & 15u) == 0 &&
+         p.n_threads / STEP_BLOCK >= 4u * 148u;
+}
+
 template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO>
 cudaError_t launch_one(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   const unsigned grid = (p.n_threads + STEP_BLOCK - 1) / STEP_BLOCK;
+  c.obs_blocks = grid;
+  if constexpr (STREAM && !HALO && MODE == MODE_PLAIN && V > 1) {
+    if ((c.tma == 1 || (c.tma < 0 && tma_default<S, T, COLL>())) && tma_applicable<T, V>(c, p))
+      return launch_tma<S, T, V, COLL, OBS>(c, p, st);
+  }
   if (c.loop_steps > 1) {
     // request for ONE launch covering loop_steps steps: honoured if the grid is co-resident, otherwise
     // nothing is launched and the caller (c.looped == false) issues one launch per step

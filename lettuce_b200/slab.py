@@ -452,14 +452,15 @@ class SlabSimulation(Simulation):
     def _finalize_obs(self, obs):
         return self._reduce_obs(obs).cpu()
 
-    GRADIENT_RADIUS = 3   # 6th-order central difference (util.torch_gradient, utility.py:37-99)
+    GRADIENT_RADIUS = 4   # planes of velocity halo: the 6th-order central difference (util.torch_gradient,
+    #                       utility.py:37-99) needs 3; 4 keeps the interior 16-byte aligned for the vector kernel
 
     def _exchange_velocity_halo(self, u):
-        """u [d, *res] -> u_ext [d, *res[:-1], nz + 6]: the 3 planes next to each z face come from the neighbours
+        """u [d, *res] -> u_ext [d, *res[:-1], nz + 2 g]: the g planes next to each z face come from the neighbours
         (a real exchange step, on enstrophy-reporting steps only: torch.distributed send / recv)"""
         g = self.GRADIENT_RADIUS
         if u.shape[-1] < g:
-            raise NotImplementedError("Enstrophy across slabs needs slabs of at least 3 planes")
+            raise NotImplementedError(f"Enstrophy across slabs needs slabs of at least {g} planes")
         lo, hi = u[..., :g].contiguous(), u[..., -g:].contiguous()
         from_down, from_up = torch.empty_like(hi), torch.empty_like(lo)
         ops = [dist.P2POp(dist.isend, hi, self.up, self.group), dist.P2POp(dist.isend, lo, self.down, self.group),

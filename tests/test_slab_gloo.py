@@ -129,9 +129,10 @@ def _masked_worker(rank, world, port, stencil, res, n_steps, q):
         # the 3-plane velocity halo of the enstrophy reporter (SlabSimulation._exchange_velocity_halo)
         u_global = torch.arange(S.d * f_global[0].numel(), dtype=torch.float64).reshape([S.d, *res])
         ok_u = True
-        if z1 - z0 >= 3:
+        g = sim.GRADIENT_RADIUS
+        if z1 - z0 >= g:
             ext = sim._exchange_velocity_halo(u_global[..., z0:z1].contiguous())
-            idx = torch.arange(z0 - 3, z1 + 3) % res[-1]
+            idx = torch.arange(z0 - g, z1 + g) % res[-1]
             ok_u = bool(torch.equal(ext, u_global[..., idx]))
         oks = [None] * world
         dist.all_gather_object(oks, ok_u)
