@@ -78,54 +78,13 @@ def grid_to_vtr(path, x, y, z, point_data: Dict[str, np.ndarray], _preordered: b
     filename = str(path) + ".vtr"
     header = "".join(head).encode("ascii")
     tail = b'\n</AppendedData>\n</VTKFile>\n'
-    payload = sum(8 + data.nbytes for data in blocks)
-    if payload < _PARALLEL_WRITE_MIN:
-        with open(filename, "wb") as fh:
-            fh.write(header)
-            for data in blocks:
-                fh.write(np.uint64(data.nbytes).tobytes())
-                fh.write(memoryview(data).cast('B'))
-            fh.write(tail)
-        return filename
-    # large files: the layout is known up front, so the arrays go to disk as positioned writes of 16 MiB pieces
-    # from a small thread pool (os.pwrite releases the GIL; one thread fills the page cache at ~3 GB/s)
-    fd = os.open(filename, os.O_WRONLY | os.O_CREAT | os.O_TRUNC, 0o644)
-    try:
-        os.ftruncate(fd, len(header) + payload + len(tail))
-        os.pwrite(fd, header, 0)
-        jobs, pos = [], len(header)
+    with open(filename, "wb") as fh:
+        fh.write(header)
         for data in blocks:
-            os.pwrite(fd, np.uint64(data.nbytes).tobytes(), pos)
-            pos += 8
-            view = memoryview(data).cast('B')
-            for off in range(0, data.nbytes, _WRITE_PIECE):
-                jobs.append(_write_pool().submit(_pwrite_all, fd, view[off:off + _WRITE_PIECE], pos + off))
-            pos += data.nbytes
-        os.pwrite(fd, tail, pos)
-        for j in jobs:
-            j.result()
-    finally:
-        os.close(fd)
+            fh.write(np.uint64(data.nbytes).tobytes())
+            fh.write(memoryview(data).cast('B'))
+        fh.write(tail)
     return filename
-
-
-_PARALLEL_WRITE_MIN = 32 << 20
-_WRITE_PIECE = 16 << 20
-_pool = None
-
-
-def _write_pool():
-    global _pool
-    if _pool is None:
-        from concurrent.futures import ThreadPoolExecutor
-        _pool = ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1), thread_name_prefix="vtr-write")
-    return _pool
-
-
-def _pwrite_all(fd, view, pos):
-    done = 0
-    while done < len(view):
-        done += os.pwrite(fd, view[done:], pos + done)
 
 
 def read_vtr(filename):

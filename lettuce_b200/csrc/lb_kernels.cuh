@@ -485,6 +485,58 @@ __device__ __forceinline__ void packed_update(F2 (&g)[S::Q], const StepParams<fl
   collide_node<S, F2, COLL, float>(g, a, b, rho, u, p.cp);
 }
 
+// collide / boundaries of the V nodes of a thread, all in registers.
+// fp32 threads that own an even number of nodes run them two at a time as packed F2 values
+// (FADD2 / FMUL2 / FFMA2); a pair that contains a boundary node, and every other case, goes node
+// by node.  Both routes round identically (lb_physics.cuh), so the result does not depend on V.
+template <class S, typename T, int V, int COLL, int MODE, bool OBS>
+__device__ __forceinline__ void collide_thread(T (&f)[S::Q][V], uint32_t mword, const StepParams<T>& p,
+                                               const T* __restrict__ f_in, T* u_out, unsigned x, unsigned y, unsigned z0,
+                                               unsigned node, bool active, T& acc_e, T& acc_m2, T& acc_mass) {
+  constexpr int Q = S::Q;
+  constexpr bool PACK = (sizeof(T) == 4) && (V % 2 == 0);
+  // the outlet kinds are compiled into the kernels that can meet them: outlets come with a
+  // no-streaming mask (MODE_NCM_SBITS); collide-only calls and odd layouts run V == 1
+  constexpr bool OUTL = (V == 1) || (MODE == MODE_NCM_SBITS);
+  if constexpr (PACK) {
+#pragma unroll
+    for (int kk = 0; kk < V / 2; ++kk) {
+      const unsigned m2 = (MODE == MODE_PLAIN) ? 0u : ((mword >> (16 * kk)) & 0xffffu);
+      if (m2 == 0) {
+        F2 g[Q];
+        static_for<Q>([&](auto qc) {
+          constexpr int q = decltype(qc)::value;
+          g[q] = F2(f[q][2 * kk], f[q][2 * kk + 1]);
+        });
+        packed_update<S, COLL, OBS>(g, p, u_out, node + 2 * kk, active, acc_e, acc_m2, acc_mass);
+        static_for<Q>([&](auto qc) {
+          constexpr int q = decltype(qc)::value;
+          f[q][2 * kk] = g[q].x;
+          f[q][2 * kk + 1] = g[q].y;
+        });
+      } else {
+#pragma unroll
+        for (int k = 2 * kk; k < 2 * kk + 2; ++k) {
+          T g[Q];
+          static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
+          node_update<S, T, COLL, MODE, OBS, OUTL>(g, (m2 >> (8 * (k - 2 * kk))) & 0xffu, p, f_in, u_out, x, y, z0 + k, node + k, active,
+                                             acc_e, acc_m2, acc_mass);
+          static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
+        }
+      }
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      T g[Q];
+      static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
+      const unsigned m = (MODE == MODE_PLAIN) ? 0u : ((mword >> (8 * k)) & 0xffu);
+      node_update<S, T, COLL, MODE, OBS, OUTL>(g, m, p, f_in, u_out, x, y, z0 + k, node + k, active, acc_e, acc_m2, acc_mass);
+      static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
+    }
+  }
+}
+
 // Resident blocks asked of the register allocator.  D3Q19 fp32 with 4 nodes per thread: 76 population
 // registers, 4 blocks (<= 128 registers) as measured at the HBM roofline -- except TRT, whose packed
 // pair form keeps a_p, b_p, S_p, D_p of two nodes live and spills below 168; D3Q27 fp32 with 2 or 4
@@ -600,50 +652,7 @@ __device__ __forceinline__ void step_tile(const StepParams<T>& p, const T* __res
   T acc_e = T(0), acc_mass = T(0), acc_m2 = T(0);   // per-thread partials over V nodes; widened below
 
   // ---- collide / boundaries, all in registers -----------------------------------------
-  // fp32 threads that own an even number of nodes run them two at a time as packed F2 values
-  // (FADD2 / FMUL2 / FFMA2); a pair that contains a boundary node, and every other case, goes node
-  // by node.  Both routes round identically (lb_physics.cuh), so the result does not depend on V.
-  constexpr bool PACK = (sizeof(T) == 4) && (V % 2 == 0);
-  // the outlet kinds are compiled into the kernels that can meet them: outlets come with a
-  // no-streaming mask (MODE_NCM_SBITS); collide-only calls and odd layouts run V == 1
-  constexpr bool OUTL = (V == 1) || (MODE == MODE_NCM_SBITS);
-  if constexpr (PACK) {
-#pragma unroll
-    for (int kk = 0; kk < V / 2; ++kk) {
-      const unsigned m2 = (MODE == MODE_PLAIN) ? 0u : ((mword >> (16 * kk)) & 0xffffu);
-      if (m2 == 0) {
-        F2 g[Q];
-        static_for<Q>([&](auto qc) {
-          constexpr int q = decltype(qc)::value;
-          g[q] = F2(f[q][2 * kk], f[q][2 * kk + 1]);
-        });
-        packed_update<S, COLL, OBS>(g, p, u_out, node + 2 * kk, active, acc_e, acc_m2, acc_mass);
-        static_for<Q>([&](auto qc) {
-          constexpr int q = decltype(qc)::value;
-          f[q][2 * kk] = g[q].x;
-          f[q][2 * kk + 1] = g[q].y;
-        });
-      } else {
-#pragma unroll
-        for (int k = 2 * kk; k < 2 * kk + 2; ++k) {
-          T g[Q];
-          static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
-          node_update<S, T, COLL, MODE, OBS, OUTL>(g, (m2 >> (8 * (k - 2 * kk))) & 0xffu, p, f_in, u_out, x, y, z0 + k, node + k, active,
-                                             acc_e, acc_m2, acc_mass);
-          static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
-        }
-      }
-    }
-  } else {
-#pragma unroll
-    for (int k = 0; k < V; ++k) {
-      T g[Q];
-      static_for<Q>([&](auto qc) { g[decltype(qc)::value] = f[decltype(qc)::value][k]; });
-      const unsigned m = (MODE == MODE_PLAIN) ? 0u : ((mword >> (8 * k)) & 0xffu);
-      node_update<S, T, COLL, MODE, OBS, OUTL>(g, m, p, f_in, u_out, x, y, z0 + k, node + k, active, acc_e, acc_m2, acc_mass);
-      static_for<Q>([&](auto qc) { f[decltype(qc)::value][k] = g[decltype(qc)::value]; });
-    }
-  }
+  collide_thread<S, T, V, COLL, MODE, OBS>(f, mword, p, f_in, u_out, x, y, z0, node, active, acc_e, acc_m2, acc_mass);
 
   // ---- stream: push to (x + ex, y + ey, z + ez), periodic -----------------------------
   if constexpr (!STREAM) {
@@ -1003,14 +1012,19 @@ step_tma_kernel(const __grid_constant__ StepParams<T> p) {
   asm volatile("griddepcontrol.wait;" ::: "memory");
   const unsigned n_tiles = p.n_threads / STEP_BLOCK;           // whole tiles only (host-checked)
   const size_t N = p.n_nodes;
-  auto issue = [&](unsigned tile, int s) {                     // one thread
-    mbar_arrive_expect_tx(&full[s], S::Q * TILE_BYTES);
-    const T* src = p.f_in + size_t(tile) * TILE;
-    T* dst = stages + size_t(s) * STAGE_ELEMS;
-#pragma unroll
-    for (int q = 0; q < S::Q; ++q) bulk_copy_g2s(dst + q * TILE, src + q * N, TILE_BYTES, &full[s]);
+  // warp 0 issues a tile: lane 0 arms the barrier with the byte count, then lane q issues the copy of population q
+  // (one thread issuing all Q copies put ~150 serial instructions on the critical path of every tile)
+  static_assert(S::Q <= 32, "one lane per population");
+  auto issue = [&](unsigned tile, int s) {                     // all lanes of warp 0
+    if (threadIdx.x == 0) mbar_arrive_expect_tx(&full[s], S::Q * TILE_BYTES);
+    __syncwarp();
+    if (threadIdx.x < unsigned(S::Q)) {
+      const T* src = p.f_in + size_t(tile) * TILE + size_t(threadIdx.x) * N;
+      T* dst = stages + size_t(s) * STAGE_ELEMS + threadIdx.x * TILE;
+      bulk_copy_g2s(dst, src, TILE_BYTES, &full[s]);
+    }
   };
-  if (threadIdx.x == 0) {
+  if (threadIdx.x < 32u) {
 #pragma unroll
     for (int s = 0; s < TMA_STAGES; ++s) {
       const unsigned tile = blockIdx.x + unsigned(s) * gridDim.x;
@@ -1026,7 +1040,7 @@ step_tma_kernel(const __grid_constant__ StepParams<T> p) {
     step_tile<S, T, V, COLL, MODE_PLAIN, OBS, true, false, true>(
         p, p.f_in, p.f_out, p.u_out, tile, stages + size_t(s) * STAGE_ELEMS, te, tm2, tmass, [&]() {
           const unsigned next = tile + unsigned(TMA_STAGES) * gridDim.x;
-          if (threadIdx.x == 0 && next < n_tiles) issue(next, s);
+          if (threadIdx.x < 32u && next < n_tiles) issue(next, s);
         });
     if constexpr (OBS) { e += double(te); m2 = fmax(m2, double(tm2)); mass += double(tmass); }
   }
@@ -1036,6 +1050,94 @@ step_tma_kernel(const __grid_constant__ StepParams<T> p) {
       double* bp = p.obs.block_partials + size_t(blockIdx.x) * N_OBS_PART;
       bp[0] = e; bp[1] = m2; bp[2] = mass;
     }
+  }
+}
+
+// --------------------------------------------------------------------------------------
+// Small plain lattices, many steps per call (BASELINE config 1: 256^2, 1000 steps): step_chain_kernel.
+// All threads are co-resident (cooperative launch) and a call of n steps is ONE launch WITHOUT any barrier between
+// the steps: between two steps the populations travel as (payload, tag) words -- the LL protocol of the slab
+// transport, here between thread blocks of one GPU through L2 -- in a triple-buffered exchange array
+// chain[tag % 3][q][node].  Step s of a thread polls ITS OWN Q x V incoming words until they carry the tag of step
+// s, collides, and pushes tagged words to the destination nodes for step s + 1.  A thread therefore waits only for
+// the (at most 26) neighbouring nodes it really depends on, and a step costs one L2 store -> load hand-over
+// (~1 us) instead of store + fence + grid barrier + load (the cooperative loop kernel: 3.0 us per step at 256^2).
+// Triple buffering: whoever writes slot (s+1) % 3 at step s has read tags s from all its neighbours, so they have
+// finished step s-1 -- the last reader of that slot's previous contents (tags s-2, read at step s-2).
+// First step: plain loads from f_in; last step: plain stores, into f_out when n is odd and f_in when it is even
+// (the convention of n separate launches; a neighbour can only be that far when this thread's loads are done).
+// --------------------------------------------------------------------------------------
+constexpr size_t CHAIN_HEADER = 64;   // error flag in front of the exchange array
+
+template <class S, typename T>
+__host__ __device__ constexpr size_t chain_bytes(size_t n_nodes) {
+  return CHAIN_HEADER + size_t(3) * S::Q * n_nodes * sizeof(typename LLWord<T>::type);
+}
+
+template <class S, typename T, int V, int COLL>
+__global__ void __launch_bounds__(STEP_BLOCK)
+step_chain_kernel(const __grid_constant__ StepParams<T> p, int n_loop, void* scratch, uint32_t tag0) {
+  using W = typename LLWord<T>::type;
+  constexpr int Q = S::Q;
+  uint32_t* const err = static_cast<uint32_t*>(scratch);
+  W* const chain = reinterpret_cast<W*>(static_cast<char*>(scratch) + CHAIN_HEADER);
+  const unsigned tid = blockIdx.x * STEP_BLOCK + threadIdx.x;
+  const bool active = tid < p.n_threads;
+  const unsigned t = active ? tid : p.n_threads - 1u;
+  const unsigned nzv = p.nzv, nz = p.nz, ny = p.ny, nx = p.nx;
+  const unsigned line = t / nzv, zv = t - line * nzv;
+  const unsigned x = line / ny, y = line - x * ny;
+  const unsigned z0 = zv * V, node = line * nz + z0;
+  const size_t N = p.n_nodes;
+  const unsigned xp = (x + 1 == nx) ? 0u : x + 1, xm = (x == 0) ? nx - 1 : x - 1;
+  const unsigned yp = (y + 1 == ny) ? 0u : y + 1, ym = (y == 0) ? ny - 1 : y - 1;
+  const unsigned xs[3] = {xm * ny, x * ny, xp * ny};
+  const unsigned ys[3] = {ym, y, yp};
+
+  T f[Q][V];
+  static_for<Q>([&](auto qc) {
+    constexpr int q = decltype(qc)::value;
+    const Vec<T, V> v = ld_vec<T, V>(p.f_in + size_t(q) * N + node);
+#pragma unroll
+    for (int k = 0; k < V; ++k) f[q][k] = v.v[k];
+  });
+  T* const f_last = (n_loop & 1) ? p.f_out : const_cast<T*>(p.f_in);
+  for (int s = 0; s < n_loop; ++s) {
+    if (s > 0 && active) {
+      // incoming populations of this step: my own Q x V words, all loads in flight, re-polled until complete
+      const uint32_t tag = tag0 + uint32_t(s);
+      const W* src = chain + size_t(tag % 3u) * Q * N + node;
+      const long long t_start = clock64();
+      for (;;) {
+        bool ok = true;
+        static_for<Q>([&](auto qc) {
+          constexpr int q = decltype(qc)::value;
+#pragma unroll
+          for (int k = 0; k < V; ++k) ok &= ll_load(src + size_t(q) * N + k, tag, f[q][k]);
+        });
+        if (ok) break;
+        if (clock64() - t_start > LL_TIMEOUT_CYCLES) { *err = 1u; break; }   // never hang the GPU
+      }
+    }
+    T e = T(0), m2 = T(0), mass = T(0);
+    collide_thread<S, T, V, COLL, MODE_PLAIN, false>(f, 0u, p, p.f_in, nullptr, x, y, z0, node, active, e, m2, mass);
+    if (!active) continue;
+    const bool last = (s == n_loop - 1);
+    const uint32_t tag_out = tag0 + uint32_t(s) + 1u;
+    W* const dst = chain + size_t(tag_out % 3u) * Q * N;
+    static_for<Q>([&](auto qc) {
+      constexpr int q = decltype(qc)::value;
+      constexpr int ex = S::e(q, 0), ey = S::e(q, 1), ez = S::e(q, 2);
+      const unsigned dline = (xs[ex + 1] + ys[ey + 1]) * nz;
+#pragma unroll
+      for (int k = 0; k < V; ++k) {
+        unsigned zz = z0 + k;
+        if constexpr (ez > 0) zz = (zz + 1 == nz) ? 0u : zz + 1;
+        if constexpr (ez < 0) zz = (zz == 0) ? nz - 1 : zz - 1;
+        if (last) f_last[size_t(q) * N + dline + zz] = f[q][k];
+        else ll_store(dst + size_t(q) * N + dline + zz, f[q][k], tag_out);
+      }
+    });
   }
 }
 
@@ -1152,15 +1254,19 @@ struct StepConfig {
   bool obs;
   bool stream;
   bool halo;      // z-slab halo plumbing compiled in (multi-GPU)
+  void* chain_scratch = nullptr;   // exchange array of step_chain_kernel (chain_bytes), or null
+  uint32_t chain_tag0 = 0;         // time steps taken through that array so far
+  bool chained = false;            // out: step_chain_kernel was used
   int tma = -1;   // persistent TMA-prefetch kernel: -1 = the compiled-in default, 0 = never, 1 = wherever it applies
   unsigned obs_blocks = 0;   // out: thread blocks that wrote a partial of the fused reduction
 };
 
-// where the persistent TMA kernel is the default (measured): the register-heavy
-// collisions of D3Q27, whose three CTAs per SM cannot cover their own load latency
+// where the persistent TMA kernel is the default (measured, DESIGN.md section 4 and profiles/r2_bench_tma*.jsonl):
+// the 2-D lattices (D2Q9 fp32 2048 x 1024: BGK 1.11x, KBC 1.20x of the classic kernel); on the 3-D lattices the
+// classic kernel's four (three) CTAs per SM already sit at the HBM ceiling and the persistent variant is slower
 template <class S, typename T, int COLL>
 constexpr bool tma_default() {
-  return S::Q == 27 && (COLL == COLL_KBC || COLL == COLL_TRT || COLL == COLL_SMAGORINSKY);
+  return S::Q == 9;
 }
 
 // one explicit specialisation per (stencil, dtype, collision), each in its own translation unit
@@ -1271,6 +1377,20 @@ cudaError_t launch_one(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   if (c.loop_steps > 1) {
     // request for ONE launch covering loop_steps steps: honoured if the grid is co-resident, otherwise
     // nothing is launched and the caller (c.looped == false) issues one launch per step
+    if constexpr (STREAM && !HALO && V > 1 && MODE == MODE_PLAIN && !OBS) {
+      // plain lattice, no reductions, exchange array given: the barrier-free chain kernel
+      auto chain = step_chain_kernel<S, T, V, COLL>;
+      if (c.chain_scratch != nullptr && int(grid) <= coresident_blocks(chain)) {
+        int n_loop = c.loop_steps;
+        void* scratch = c.chain_scratch;
+        uint32_t tag0 = c.chain_tag0;
+        void* args[] = {const_cast<StepParams<T>*>(&p), &n_loop, &scratch, &tag0};
+        const cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(chain), dim3(grid), dim3(STEP_BLOCK),
+                                                          args, 0, st);
+        if (e == cudaSuccess) { c.looped = true; c.chained = true; return cudaSuccess; }
+        (void)cudaGetLastError();
+      }
+    }
     if constexpr (STREAM && !HALO && V > 1) {
       auto kernel = step_loop_kernel<S, T, V, COLL, MODE, OBS>;
       if (int(grid) <= coresident_blocks(kernel)) {

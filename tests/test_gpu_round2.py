@@ -117,3 +117,28 @@ def test_collision_call_with_outlet_boundary_is_deterministic_and_right():
     assert float((got - ref).abs().max() / ref.abs().max()) <= 1e-12
     flow.f = f0.to("cuda")
     assert torch.equal(sim._collide().cpu(), got)       # and again: the same bits
+
+
+@pytest.mark.parametrize("stencil,dtype,res,collision", [
+    ("D2Q9", torch.float64, [256, 256], "bgk"), ("D2Q9", torch.float32, [128, 256], "kbc"),
+    ("D3Q19", torch.float32, [16, 24, 64], "bgk"), ("D3Q27", torch.float64, [12, 10, 16], "kbc"),
+    ("D3Q19", torch.float64, [8, 8, 32], "trt"), ("D2Q9", torch.float64, [64, 6], "none"),
+])
+def test_chain_kernel_equals_per_step_launches(stencil, dtype, res, collision):
+    """small plain lattices: simulation(n) is ONE launch of the barrier-free chain kernel (tagged words between the
+    steps, lb_fields.chain_scratch); it must leave the bits n launches of the classic kernel leave -- across
+    several calls of odd and even length (ping-pong convention, running tags, triple-buffered slots)"""
+    gu, lt = _lt()
+    nat = lt.native
+    outs = []
+    for flags in (nat.LB_KF_NO_LOOP, 0, nat.LB_KF_NO_CHAIN):
+        ctx = lt.Context(device="cuda", dtype=dtype, use_native=True)
+        flow = lt.TaylorGreenVortex(ctx, resolution=res, reynolds_number=200, mach_number=0.05, stencil=getattr(lt, stencil))
+        sim = lt.Simulation(flow, _collision(lt, flow, collision), [])
+        sim.kernel_flags = flags
+        for n in (7, 2, 30, 1, 11):
+            sim(n)
+        outs.append(flow.f.clone())
+        if flags == 0:
+            assert sim._chain_scratch is not None and sim._chain_epoch == 50      # the chain kernel really ran
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
