@@ -99,8 +99,7 @@ typedef struct lb_desc {
 enum {
   LB_KF_NO_TMA = 1,    /* never use the persistent TMA-prefetch step kernel                                */
   LB_KF_FORCE_TMA = 2, /* use it wherever it applies (plain lattices of whole, 16-byte aligned tiles)      */
-  LB_KF_NO_LOOP = 4,   /* one launch per time step also where the cooperative multi-step kernel would fit */
-  LB_KF_NO_CHAIN = 8   /* cooperative loop kernel (grid barrier per step) instead of the barrier-free chain kernel */
+  LB_KF_NO_LOOP = 4    /* one launch per time step also where the cooperative multi-step kernel would fit */
 };
 
 /* One entry per boundary object, in the order lettuce sorted them
@@ -226,15 +225,6 @@ typedef struct lb_fields {
   void* u_out;                      /* device [d][*res] or NULL: velocity of the consumed
                                        state of the LAST step of the call (for enstrophy) */
   const lb_halo* halo;              /* NULL: the slab is periodic in z by itself             */
-  /* Optional, small plain lattices only (no masks, no obs_out, no halo; all thread blocks co-resident): an
-   * exchange array of lb_chain_scratch_bytes() bytes, ZERO when first used and then left to the library, lets a
-   * call of n_steps > 1 run as ONE launch without any barrier between the steps (populations handed from step
-   * to step as tagged words through L2; include the kernel's description in lb_kernels.cuh).  chain_epoch = the
-   * number of time steps taken through this array so far (the caller adds n_steps after every call that had
-   * n_steps > 1); word [0] of the array is set to 1 if a wait ever timed out (state then invalid). */
-  void* chain_scratch;
-  uint32_t chain_epoch;
-  uint32_t _pad2;
 } lb_fields;
 
 LB_API int lb_abi_version(void);
@@ -328,8 +318,6 @@ LB_API int lb_ipc_free(void* dptr);
 LB_API int lb_ipc_export(void* dptr, unsigned char handle[64]);
 LB_API int lb_ipc_open(const unsigned char handle[64], void** dptr);
 LB_API int lb_ipc_close(void* dptr);
-
-LB_API size_t lb_chain_scratch_bytes(const lb_desc* desc);   /* bytes of lb_fields.chain_scratch for this lattice */
 
 /* Introspection for tests / roofline arithmetic */
 LB_API int lb_stencil_q(int stencil);

@@ -47,8 +47,7 @@ class Fields(C.Structure):          # lb_fields
     _fields_ = [("f", C.c_void_p), ("f_next", C.c_void_p), ("no_collision_mask", C.c_void_p),
                 ("streaming_bits", C.c_void_p), ("boundaries", C.POINTER(Boundary)),
                 ("n_boundaries", C.c_int32), ("_pad", C.c_int32), ("obs_out", C.c_void_p),
-                ("obs_scratch", C.c_void_p), ("u_out", C.c_void_p), ("halo", C.c_void_p),
-                ("chain_scratch", C.c_void_p), ("chain_epoch", C.c_uint32), ("_pad2", C.c_uint32)]
+                ("obs_scratch", C.c_void_p), ("u_out", C.c_void_p), ("halo", C.c_void_p)]
 
 
 def lib():

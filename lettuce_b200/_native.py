@@ -34,7 +34,7 @@ EXPORTED_SYMBOLS = (
     "lb_enstrophy", "lb_run_host", "lb_stencil_q", "lb_bytes_per_update", "lb_vector_width",
     "lb_unpack_halo", "lb_zface_count", "lb_ipc_alloc", "lb_ipc_free", "lb_ipc_export",
     "lb_ipc_open", "lb_ipc_close", "lb_output_fields", "lb_unpack_halo_ex", "lb_halo_ll_bytes",
-    "lb_enstrophy_slab", "lb_chain_scratch_bytes",
+    "lb_enstrophy_slab",
 )
 
 
@@ -53,7 +53,7 @@ class LbDesc(C.Structure):
                 ("force", C.c_int32), ("kernel_flags", C.c_int32)]
 
 
-LB_KF_NO_TMA, LB_KF_FORCE_TMA, LB_KF_NO_LOOP, LB_KF_NO_CHAIN = 1, 2, 4, 8
+LB_KF_NO_TMA, LB_KF_FORCE_TMA, LB_KF_NO_LOOP = 1, 2, 4
 
 
 class LbBoundary(C.Structure):
@@ -82,8 +82,7 @@ class LbFields(C.Structure):
     _fields_ = [("f", C.c_void_p), ("f_next", C.c_void_p), ("no_collision_mask", C.c_void_p),
                 ("streaming_bits", C.c_void_p), ("boundaries", C.POINTER(LbBoundary)),
                 ("n_boundaries", C.c_int32), ("_pad", C.c_int32), ("obs_out", C.c_void_p),
-                ("obs_scratch", C.c_void_p), ("u_out", C.c_void_p), ("halo", C.POINTER(LbHalo)),
-                ("chain_scratch", C.c_void_p), ("chain_epoch", C.c_uint32), ("_pad2", C.c_uint32)]
+                ("obs_scratch", C.c_void_p), ("u_out", C.c_void_p), ("halo", C.POINTER(LbHalo))]
 
 
 _lib = None
@@ -114,8 +113,6 @@ def lib() -> C.CDLL:
                                 C.c_void_p]
     L.lb_obs_scratch_bytes.argtypes = [C.POINTER(LbDesc)]
     L.lb_obs_scratch_bytes.restype = C.c_size_t
-    L.lb_chain_scratch_bytes.argtypes = [C.POINTER(LbDesc)]
-    L.lb_chain_scratch_bytes.restype = C.c_size_t
     L.lb_observables.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                  C.c_void_p, C.c_void_p]
     L.lb_enstrophy.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]

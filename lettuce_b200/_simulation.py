@@ -88,7 +88,6 @@ class Simulation:
         self._streaming_bits = None
         self._mask_version = None
         self._obs_scratch = None
-        self._chain_scratch, self._chain_epoch = None, 0
         self._keepalive = []
         self._collide_and_stream = self._native_seam
 
@@ -206,23 +205,6 @@ class Simulation:
         self._keepalive = [arr, keep]
         return fl
 
-    CHAIN_SCRATCH_MAX_BYTES = 96 << 20     # the exchange array of the chain kernel should stay L2-resident (126 MB)
-
-    def _chain_fields(self, desc, fl, n):
-        """small plain lattices, calls of several steps without fused reductions: hand the library the exchange
-        array of its barrier-free multi-step kernel (lb_fields.chain_scratch)"""
-        if n <= 1 or self.no_collision_mask is not None or fl.obs_out or fl.halo:
-            return False
-        nbytes = nat.lib().lb_chain_scratch_bytes(desc)
-        if nbytes == 0 or nbytes > self.CHAIN_SCRATCH_MAX_BYTES:
-            return False
-        if self._chain_scratch is None or self._chain_scratch.numel() != nbytes:
-            self._chain_scratch = torch.zeros(nbytes, dtype=torch.uint8, device=self.context.device)
-            self._chain_epoch = 0
-        fl.chain_scratch = self._chain_scratch.data_ptr()
-        fl.chain_epoch = self._chain_epoch
-        return True
-
     def _advance(self, n, obs_out=None, u_out=None):
         """n native time steps; flow.f / flow.f_next are swapped so that flow.f is the new state"""
         if n <= 0:
@@ -230,10 +212,7 @@ class Simulation:
         desc = self._desc()
         with torch.cuda.device(self.context.device):
             fl = self._fields(desc, obs_out, u_out)
-            chained = self._chain_fields(desc, fl, n)
             nat.check(nat.lib().lb_step(desc, fl, n, nat.current_stream_ptr(self.context.device)))
-            if chained:
-                self._chain_epoch += n
         if n % 2 == 1:
             self.flow.f, self.flow.f_next = self.flow.f_next, self.flow.f
 
@@ -303,9 +282,6 @@ class Simulation:
                 flush()
         torch.cuda.synchronize(self.context.device)
         end = timer()
-        if self._chain_scratch is not None and int(self._chain_scratch[:4].view(torch.int32).item()) != 0:
-            raise RuntimeError("the multi-step chain kernel gave up waiting for a neighbouring thread block (~10 s): "
-                               "the populations of this call are invalid")
         n_nodes = 1
         for n in flow.resolution:     # == flow.rho().numel() (_simulation.py:207) without a moments pass
             n_nodes *= int(n)

@@ -350,11 +350,6 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
     if (!no_loop && !(d->kernel_flags & LB_KF_NO_LOOP)) {
       c.loop_steps = n_steps;
       c.obs = fl->obs_out != nullptr;
-      static const bool no_chain = getenv("LB_NO_CHAIN") != nullptr;   // A/B timing only
-      if (!no_chain && !(d->kernel_flags & LB_KF_NO_CHAIN)) {
-        c.chain_scratch = fl->chain_scratch;
-        c.chain_tag0 = fl->chain_epoch;
-      }
       p.f_in = a; p.f_out = b;
       p.obs_out = fl->obs_out;
       p.u_out = c.obs ? static_cast<T*>(fl->u_out) : nullptr;
@@ -624,13 +619,6 @@ int lb_pack_streaming_mask(const lb_desc* desc, const uint8_t* nsm, uint32_t* bi
   mark_sbits_neighbourhood_kernel<<<grid, block, 0, static_cast<cudaStream_t>(stream)>>>(bits, g.nx, g.ny, g.nz);
   LB_CUDA(cudaGetLastError());
   return LB_OK;
-}
-
-size_t lb_chain_scratch_bytes(const lb_desc* desc) {
-  Geometry g;
-  if (check_desc(desc, &g)) return 0;
-  const size_t word = desc->dtype == LB_F64 ? 16 : 8;
-  return lb::CHAIN_HEADER + size_t(3) * size_t(g.q) * g.n_nodes * word;
 }
 
 size_t lb_obs_scratch_bytes(const lb_desc* desc) {

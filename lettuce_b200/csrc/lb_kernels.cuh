@@ -602,6 +602,9 @@ __device__ __forceinline__ void step_tile(const StepParams<T>& p, const T* __res
       for (int k = 0; k < V; ++k) f[q][k] = v.v[k];
     });
   }
+  [[maybe_unused]] uint32_t smem_mword = 0;
+  if constexpr (SMEM_IN && MODE != MODE_PLAIN)
+    smem_mword = ld_mask<V>(reinterpret_cast<const uint8_t*>(smem_in + Q * (STEP_BLOCK * V)) + threadIdx.x * V);
   if constexpr (SMEM_IN) {
     // the stage is free as soon as every thread holds its values: the producer refills it while this tile
     // computes and stores (the caller issues the next bulk copies right behind this barrier)
@@ -609,7 +612,10 @@ __device__ __forceinline__ void step_tile(const StepParams<T>& p, const T* __res
     smem_tile_consumed();
   }
   uint32_t mword = 0;
-  if constexpr (MODE != MODE_PLAIN) mword = ld_mask<V>(p.ncm + node);
+  if constexpr (MODE != MODE_PLAIN) {
+    if constexpr (SMEM_IN) mword = smem_mword;     // the tile's mask bytes came with the populations
+    else mword = ld_mask<V>(p.ncm + node);
+  }
   // ---- incoming halo (multi-GPU): issued right behind the population loads so that both are in flight
   // together (LL transport: the tag test then waits for these few words only, not in front of the population
   // loads); a thread is on at most one z face unless the line is a single vector.
@@ -990,15 +996,23 @@ __device__ __forceinline__ void bulk_copy_g2s(void* dst, const void* src, unsign
                "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
 
-template <class S, typename T, int V>
-constexpr size_t tma_smem_bytes() { return size_t(TMA_STAGES) * S::Q * STEP_BLOCK * V * sizeof(T); }
+// a stage: Q population chunks, then (MODE_NCM) the tile's no_collision_mask bytes, padded to 128 bytes
+template <class S, typename T, int V, int MODE>
+constexpr size_t tma_stage_bytes() {
+  return (size_t(S::Q) * STEP_BLOCK * V * sizeof(T) + (MODE != MODE_PLAIN ? size_t(STEP_BLOCK) * V : 0) + 127) / 128 * 128;
+}
+template <class S, typename T, int V, int MODE>
+constexpr size_t tma_smem_bytes() { return size_t(TMA_STAGES) * tma_stage_bytes<S, T, V, MODE>(); }
 
-template <class S, typename T, int V, int COLL, bool OBS>
-__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V, COLL, MODE_PLAIN>())
+template <class S, typename T, int V, int COLL, int MODE, bool OBS>
+__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V, COLL, MODE>())
 step_tma_kernel(const __grid_constant__ StepParams<T> p) {
+  static_assert(MODE == MODE_PLAIN || MODE == MODE_NCM, "no masked streaming in the TMA kernel");
   constexpr unsigned TILE = STEP_BLOCK * V;                    // nodes per tile
   constexpr unsigned TILE_BYTES = TILE * sizeof(T);            // one population chunk
-  constexpr unsigned STAGE_ELEMS = S::Q * TILE;
+  constexpr unsigned STAGE_ELEMS = unsigned(tma_stage_bytes<S, T, V, MODE>() / sizeof(T));
+  constexpr bool MASK = MODE != MODE_PLAIN;
+  static_assert(!MASK || (TILE % 16 == 0), "mask chunk is a bulk copy: multiple of 16 bytes");
   extern __shared__ __align__(128) unsigned char tma_smem[];
   T* const stages = reinterpret_cast<T*>(tma_smem);
   __shared__ uint64_t full[TMA_STAGES];
@@ -1014,14 +1028,16 @@ step_tma_kernel(const __grid_constant__ StepParams<T> p) {
   const size_t N = p.n_nodes;
   // warp 0 issues a tile: lane 0 arms the barrier with the byte count, then lane q issues the copy of population q
   // (one thread issuing all Q copies put ~150 serial instructions on the critical path of every tile)
-  static_assert(S::Q <= 32, "one lane per population");
+  static_assert(S::Q + (MASK ? 1 : 0) <= 32, "one lane per chunk");
   auto issue = [&](unsigned tile, int s) {                     // all lanes of warp 0
-    if (threadIdx.x == 0) mbar_arrive_expect_tx(&full[s], S::Q * TILE_BYTES);
+    if (threadIdx.x == 0) mbar_arrive_expect_tx(&full[s], S::Q * TILE_BYTES + (MASK ? TILE : 0u));
     __syncwarp();
     if (threadIdx.x < unsigned(S::Q)) {
       const T* src = p.f_in + size_t(tile) * TILE + size_t(threadIdx.x) * N;
       T* dst = stages + size_t(s) * STAGE_ELEMS + threadIdx.x * TILE;
       bulk_copy_g2s(dst, src, TILE_BYTES, &full[s]);
+    } else if (MASK && threadIdx.x == unsigned(S::Q)) {
+      bulk_copy_g2s(stages + size_t(s) * STAGE_ELEMS + S::Q * TILE, p.ncm + size_t(tile) * TILE, TILE, &full[s]);
     }
   };
   if (threadIdx.x < 32u) {
@@ -1037,7 +1053,7 @@ step_tma_kernel(const __grid_constant__ StepParams<T> p) {
     const int s = int(it % TMA_STAGES);
     mbar_wait(&full[s], (it / TMA_STAGES) & 1u);
     T te = T(0), tm2 = T(0), tmass = T(0);
-    step_tile<S, T, V, COLL, MODE_PLAIN, OBS, true, false, true>(
+    step_tile<S, T, V, COLL, MODE, OBS, true, false, true>(
         p, p.f_in, p.f_out, p.u_out, tile, stages + size_t(s) * STAGE_ELEMS, te, tm2, tmass, [&]() {
           const unsigned next = tile + unsigned(TMA_STAGES) * gridDim.x;
           if (threadIdx.x < 32u && next < n_tiles) issue(next, s);
@@ -1050,94 +1066,6 @@ step_tma_kernel(const __grid_constant__ StepParams<T> p) {
       double* bp = p.obs.block_partials + size_t(blockIdx.x) * N_OBS_PART;
       bp[0] = e; bp[1] = m2; bp[2] = mass;
     }
-  }
-}
-
-// --------------------------------------------------------------------------------------
-// Small plain lattices, many steps per call (BASELINE config 1: 256^2, 1000 steps): step_chain_kernel.
-// All threads are co-resident (cooperative launch) and a call of n steps is ONE launch WITHOUT any barrier between
-// the steps: between two steps the populations travel as (payload, tag) words -- the LL protocol of the slab
-// transport, here between thread blocks of one GPU through L2 -- in a triple-buffered exchange array
-// chain[tag % 3][q][node].  Step s of a thread polls ITS OWN Q x V incoming words until they carry the tag of step
-// s, collides, and pushes tagged words to the destination nodes for step s + 1.  A thread therefore waits only for
-// the (at most 26) neighbouring nodes it really depends on, and a step costs one L2 store -> load hand-over
-// (~1 us) instead of store + fence + grid barrier + load (the cooperative loop kernel: 3.0 us per step at 256^2).
-// Triple buffering: whoever writes slot (s+1) % 3 at step s has read tags s from all its neighbours, so they have
-// finished step s-1 -- the last reader of that slot's previous contents (tags s-2, read at step s-2).
-// First step: plain loads from f_in; last step: plain stores, into f_out when n is odd and f_in when it is even
-// (the convention of n separate launches; a neighbour can only be that far when this thread's loads are done).
-// --------------------------------------------------------------------------------------
-constexpr size_t CHAIN_HEADER = 64;   // error flag in front of the exchange array
-
-template <class S, typename T>
-__host__ __device__ constexpr size_t chain_bytes(size_t n_nodes) {
-  return CHAIN_HEADER + size_t(3) * S::Q * n_nodes * sizeof(typename LLWord<T>::type);
-}
-
-template <class S, typename T, int V, int COLL>
-__global__ void __launch_bounds__(STEP_BLOCK)
-step_chain_kernel(const __grid_constant__ StepParams<T> p, int n_loop, void* scratch, uint32_t tag0) {
-  using W = typename LLWord<T>::type;
-  constexpr int Q = S::Q;
-  uint32_t* const err = static_cast<uint32_t*>(scratch);
-  W* const chain = reinterpret_cast<W*>(static_cast<char*>(scratch) + CHAIN_HEADER);
-  const unsigned tid = blockIdx.x * STEP_BLOCK + threadIdx.x;
-  const bool active = tid < p.n_threads;
-  const unsigned t = active ? tid : p.n_threads - 1u;
-  const unsigned nzv = p.nzv, nz = p.nz, ny = p.ny, nx = p.nx;
-  const unsigned line = t / nzv, zv = t - line * nzv;
-  const unsigned x = line / ny, y = line - x * ny;
-  const unsigned z0 = zv * V, node = line * nz + z0;
-  const size_t N = p.n_nodes;
-  const unsigned xp = (x + 1 == nx) ? 0u : x + 1, xm = (x == 0) ? nx - 1 : x - 1;
-  const unsigned yp = (y + 1 == ny) ? 0u : y + 1, ym = (y == 0) ? ny - 1 : y - 1;
-  const unsigned xs[3] = {xm * ny, x * ny, xp * ny};
-  const unsigned ys[3] = {ym, y, yp};
-
-  T f[Q][V];
-  static_for<Q>([&](auto qc) {
-    constexpr int q = decltype(qc)::value;
-    const Vec<T, V> v = ld_vec<T, V>(p.f_in + size_t(q) * N + node);
-#pragma unroll
-    for (int k = 0; k < V; ++k) f[q][k] = v.v[k];
-  });
-  T* const f_last = (n_loop & 1) ? p.f_out : const_cast<T*>(p.f_in);
-  for (int s = 0; s < n_loop; ++s) {
-    if (s > 0 && active) {
-      // incoming populations of this step: my own Q x V words, all loads in flight, re-polled until complete
-      const uint32_t tag = tag0 + uint32_t(s);
-      const W* src = chain + size_t(tag % 3u) * Q * N + node;
-      const long long t_start = clock64();
-      for (;;) {
-        bool ok = true;
-        static_for<Q>([&](auto qc) {
-          constexpr int q = decltype(qc)::value;
-#pragma unroll
-          for (int k = 0; k < V; ++k) ok &= ll_load(src + size_t(q) * N + k, tag, f[q][k]);
-        });
-        if (ok) break;
-        if (clock64() - t_start > LL_TIMEOUT_CYCLES) { *err = 1u; break; }   // never hang the GPU
-      }
-    }
-    T e = T(0), m2 = T(0), mass = T(0);
-    collide_thread<S, T, V, COLL, MODE_PLAIN, false>(f, 0u, p, p.f_in, nullptr, x, y, z0, node, active, e, m2, mass);
-    if (!active) continue;
-    const bool last = (s == n_loop - 1);
-    const uint32_t tag_out = tag0 + uint32_t(s) + 1u;
-    W* const dst = chain + size_t(tag_out % 3u) * Q * N;
-    static_for<Q>([&](auto qc) {
-      constexpr int q = decltype(qc)::value;
-      constexpr int ex = S::e(q, 0), ey = S::e(q, 1), ez = S::e(q, 2);
-      const unsigned dline = (xs[ex + 1] + ys[ey + 1]) * nz;
-#pragma unroll
-      for (int k = 0; k < V; ++k) {
-        unsigned zz = z0 + k;
-        if constexpr (ez > 0) zz = (zz + 1 == nz) ? 0u : zz + 1;
-        if constexpr (ez < 0) zz = (zz == 0) ? nz - 1 : zz - 1;
-        if (last) f_last[size_t(q) * N + dline + zz] = f[q][k];
-        else ll_store(dst + size_t(q) * N + dline + zz, f[q][k], tag_out);
-      }
-    });
   }
 }
 
@@ -1254,9 +1182,6 @@ struct StepConfig {
   bool obs;
   bool stream;
   bool halo;      // z-slab halo plumbing compiled in (multi-GPU)
-  void* chain_scratch = nullptr;   // exchange array of step_chain_kernel (chain_bytes), or null
-  uint32_t chain_tag0 = 0;         // time steps taken through that array so far
-  bool chained = false;            // out: step_chain_kernel was used
   int tma = -1;   // persistent TMA-prefetch kernel: -1 = the compiled-in default, 0 = never, 1 = wherever it applies
   unsigned obs_blocks = 0;   // out: thread blocks that wrote a partial of the fused reduction
 };
@@ -1266,7 +1191,7 @@ struct StepConfig {
 // classic kernel's four (three) CTAs per SM already sit at the HBM ceiling and the persistent variant is slower
 template <class S, typename T, int COLL>
 constexpr bool tma_default() {
-  return S::Q == 9;
+  return S::Q == 9 && sizeof(T) == 4;
 }
 
 // one explicit specialisation per (stencil, dtype, collision), each in its own translation unit
@@ -1325,10 +1250,10 @@ int coresident_blocks(K kernel) {
   return cached;
 }
 
-template <class S, typename T, int V, int COLL, bool OBS>
+template <class S, typename T, int V, int COLL, int MODE, bool OBS>
 cudaError_t launch_tma(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
-  auto kernel = step_tma_kernel<S, T, V, COLL, OBS>;
-  constexpr size_t smem = tma_smem_bytes<S, T, V>();
+  auto kernel = step_tma_kernel<S, T, V, COLL, MODE, OBS>;
+  constexpr size_t smem = tma_smem_bytes<S, T, V, MODE>();
   static int resident = -1;   // CTAs the device holds at once
   if (resident < 0) {
     int dev = 0, sms = 0, per_sm = 0;
@@ -1357,40 +1282,27 @@ cudaError_t launch_tma(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   return cudaLaunchKernelEx(&cfg, kernel, p);
 }
 
-// the persistent TMA kernel applies to: plain lattices (no masks, no halos) made of whole tiles whose population
-// chunks are 16-byte aligned in global memory
+// the persistent TMA kernel applies to: lattices without masked streaming, outlets and halos, made of whole tiles
+// whose population (and mask) chunks are 16-byte aligned in global memory
 template <typename T, int V>
 bool tma_applicable(const StepConfig& c, const StepParams<T>& p) {
-  return V > 1 && c.stream && !c.halo && c.mode == MODE_PLAIN && c.loop_steps <= 1 && p.n_threads % STEP_BLOCK == 0 &&
+  return V > 1 && c.stream && !c.halo && (c.mode == MODE_PLAIN || (c.mode == MODE_NCM && !p.has_outlet)) &&
+         c.loop_steps <= 1 && p.n_threads % STEP_BLOCK == 0 &&
          (size_t(p.n_nodes) * sizeof(T)) % 16 == 0 && (reinterpret_cast<uintptr_t>(p.f_in) & 15u) == 0 &&
-         p.n_threads / STEP_BLOCK >= 4u * 148u;
+         (reinterpret_cast<uintptr_t>(p.ncm) & 15u) == 0 && p.n_threads / STEP_BLOCK >= 4u * 148u;
 }
 
 template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO>
 cudaError_t launch_one(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   const unsigned grid = (p.n_threads + STEP_BLOCK - 1) / STEP_BLOCK;
   c.obs_blocks = grid;
-  if constexpr (STREAM && !HALO && MODE == MODE_PLAIN && V > 1) {
+  if constexpr (STREAM && !HALO && (MODE == MODE_PLAIN || MODE == MODE_NCM) && V > 1) {
     if ((c.tma == 1 || (c.tma < 0 && tma_default<S, T, COLL>())) && tma_applicable<T, V>(c, p))
-      return launch_tma<S, T, V, COLL, OBS>(c, p, st);
+      return launch_tma<S, T, V, COLL, MODE, OBS>(c, p, st);
   }
   if (c.loop_steps > 1) {
     // request for ONE launch covering loop_steps steps: honoured if the grid is co-resident, otherwise
     // nothing is launched and the caller (c.looped == false) issues one launch per step
-    if constexpr (STREAM && !HALO && V > 1 && MODE == MODE_PLAIN && !OBS) {
-      // plain lattice, no reductions, exchange array given: the barrier-free chain kernel
-      auto chain = step_chain_kernel<S, T, V, COLL>;
-      if (c.chain_scratch != nullptr && int(grid) <= coresident_blocks(chain)) {
-        int n_loop = c.loop_steps;
-        void* scratch = c.chain_scratch;
-        uint32_t tag0 = c.chain_tag0;
-        void* args[] = {const_cast<StepParams<T>*>(&p), &n_loop, &scratch, &tag0};
-        const cudaError_t e = cudaLaunchCooperativeKernel(reinterpret_cast<void*>(chain), dim3(grid), dim3(STEP_BLOCK),
-                                                          args, 0, st);
-        if (e == cudaSuccess) { c.looped = true; c.chained = true; return cudaSuccess; }
-        (void)cudaGetLastError();
-      }
-    }
     if constexpr (STREAM && !HALO && V > 1) {
       auto kernel = step_loop_kernel<S, T, V, COLL, MODE, OBS>;
       if (int(grid) <= coresident_blocks(kernel)) {

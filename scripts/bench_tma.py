@@ -66,6 +66,10 @@ case("TGV3D D3Q19 BGK f64 256^3", 256, lt.D3Q19, f64, "bgk", S)
 case("TGV3D D3Q19 TRT f32 256^3", 256, lt.D3Q19, f32, "trt", S)
 case("TGV2D D2Q9 BGK f32 2048x1024", [2048, 1024], lt.D2Q9, f32, "bgk", 5 * S)
 case("TGV2D D2Q9 KBC f32 2048x1024", [2048, 1024], lt.D2Q9, f32, "kbc", 5 * S)
+case("TGV2D D2Q9 BGK f64 2048x1024", [2048, 1024], lt.D2Q9, f64, "bgk", 5 * S)
+case("TGV2D D2Q9 KBC f64 2048x1024", [2048, 1024], lt.D2Q9, f64, "kbc", 5 * S)
+case("TGV2D D2Q9 TRT f32 2048x1024", [2048, 1024], lt.D2Q9, f32, "trt", 5 * S)
+case("TGV2D D2Q9 BGK f32 4096x4096 (302 MB of populations: beyond L2)", [4096, 4096], lt.D2Q9, f32, "bgk", S)
 if not quick:
     case("cfg4 TGV3D D3Q27 KBC f32 512^3", 512, lt.D3Q27, f32, "kbc", 50)
     case("cfg4 TGV3D D3Q27 KBC f32 512^3 energy every step", 512, lt.D3Q27, f32, "kbc", 50, interval=1)

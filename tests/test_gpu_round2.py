@@ -119,26 +119,78 @@ def test_collision_call_with_outlet_boundary_is_deterministic_and_right():
     assert torch.equal(sim._collide().cpu(), got)       # and again: the same bits
 
 
-@pytest.mark.parametrize("stencil,dtype,res,collision", [
-    ("D2Q9", torch.float64, [256, 256], "bgk"), ("D2Q9", torch.float32, [128, 256], "kbc"),
-    ("D3Q19", torch.float32, [16, 24, 64], "bgk"), ("D3Q27", torch.float64, [12, 10, 16], "kbc"),
-    ("D3Q19", torch.float64, [8, 8, 32], "trt"), ("D2Q9", torch.float64, [64, 6], "none"),
-])
-def test_chain_kernel_equals_per_step_launches(stencil, dtype, res, collision):
-    """small plain lattices: simulation(n) is ONE launch of the barrier-free chain kernel (tagged words between the
-    steps, lb_fields.chain_scratch); it must leave the bits n launches of the classic kernel leave -- across
-    several calls of odd and even length (ping-pong convention, running tags, triple-buffered slots)"""
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64], ids=["f32", "f64"])
+@pytest.mark.parametrize("dims", [2, 3])
+def test_tma_kernel_with_no_collision_mask(dtype, dims):
+    """bounce-back solid + two equilibrium boundaries (no masked streaming): the persistent TMA kernel brings the
+    mask bytes of a tile in with the populations -- same bits as the classic kernel"""
     gu, lt = _lt()
     nat = lt.native
-    outs = []
-    for flags in (nat.LB_KF_NO_LOOP, 0, nat.LB_KF_NO_CHAIN):
+    res = [1024, 512] if dims == 2 else [64, 64, 128]
+    stencil = lt.D2Q9 if dims == 2 else lt.D3Q19
+    out = []
+    for flag in (nat.LB_KF_NO_TMA, nat.LB_KF_FORCE_TMA):
         ctx = lt.Context(device="cuda", dtype=dtype, use_native=True)
-        flow = lt.TaylorGreenVortex(ctx, resolution=res, reynolds_number=200, mach_number=0.05, stencil=getattr(lt, stencil))
-        sim = lt.Simulation(flow, _collision(lt, flow, collision), [])
-        sim.kernel_flags = flags
-        for n in (7, 2, 30, 1, 11):
-            sim(n)
-        outs.append(flow.f.clone())
-        if flags == 0:
-            assert sim._chain_scratch is not None and sim._chain_epoch == 50      # the chain kernel really ran
-    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+        class LocalObstacle(lt.Obstacle):
+            @property
+            def boundaries(self):
+                x = self.grid[0]
+                u_in = self.units.characteristic_velocity_pu * self._unit_vector()
+                return [lt.EquilibriumBoundaryPU(context=self.context, mask=torch.abs(x) < 1e-6, velocity=u_in),
+                        lt.EquilibriumBoundaryPU(context=self.context, mask=torch.abs(x - x.max()) < 1e-6, velocity=u_in),
+                        lt.BounceBackBoundary(self.mask)]
+        flow = LocalObstacle(ctx, res, reynolds_number=200, mach_number=0.05, domain_length_x=1, stencil=stencil)
+        g = flow.grid
+        flow.mask = sum((c - 0.4 * c.max()) ** 2 for c in g) < (0.1 * g[1].max()) ** 2
+        rep = lt.ObservableReporter(lt.IncompressibleKineticEnergy(flow), interval=1, out=None)
+        sim = lt.Simulation(flow, lt.BGKCollision(tau=max(float(flow.units.relaxation_parameter_lu), 0.55)), [rep])
+        sim.kernel_flags = flag | nat.LB_KF_NO_LOOP
+        sim(6)
+        out.append((flow.f.clone(), [r[2] for r in rep.out]))
+    assert torch.equal(out[0][0], out[1][0]) and bool(torch.isfinite(out[0][0]).all())
+    assert out[0][1] == pytest.approx(out[1][1], rel=1e-6 if dtype == torch.float32 else 1e-13)
+
+
+@pytest.mark.parametrize("case", ["plain", "ncm", "sbits", "tma", "halo_ll"])
+def test_every_output_element_is_written(case):
+    """the push scheme writes every (q, node) of the output exactly once: pre-fill the output buffer with NaN, step
+    once, no NaN may be left (compute-sanitizer is closed on this pool: this is the write-coverage check)"""
+    import ctypes as C
+    gu, lt = _lt()
+    nat = lt.native
+    L = nat.lib()
+    res = [64, 64, 128] if case == "tma" else [12, 10, 24]
+    ctx = lt.Context(device="cuda", dtype=torch.float32, use_native=True)
+    if case in ("ncm", "sbits"):
+        flow = lt.Obstacle(ctx, res, reynolds_number=100, mach_number=0.05, domain_length_x=1, stencil=lt.D3Q19)
+        g = flow.grid
+        flow.mask = sum((c - 0.4 * c.max()) ** 2 for c in g) < (0.15 * g[1].max()) ** 2
+        if case == "ncm":
+            flow.__class__ = type("B", (lt.Obstacle,), {"boundaries": property(lambda self: [lt.BounceBackBoundary(self.mask)])})
+    else:
+        flow = lt.TaylorGreenVortex(ctx, resolution=res, reynolds_number=400, mach_number=0.1, stencil=lt.D3Q19)
+    sim = lt.Simulation(flow, lt.BGKCollision(tau=0.7), [])
+    sim.kernel_flags = nat.LB_KF_FORCE_TMA if case == "tma" else nat.LB_KF_NO_TMA
+    flow.f_next.fill_(float("nan"))
+    if case != "halo_ll":
+        sim._collide_and_stream(sim)
+        assert bool(torch.isfinite(flow.f).all())
+        return
+    desc = sim._desc()
+    nb = L.lb_halo_ll_bytes(desc)
+    lo = [torch.zeros([nb], dtype=torch.uint8, device="cuda") for _ in range(3)]
+    hi = [torch.zeros([nb], dtype=torch.uint8, device="cuda") for _ in range(3)]
+    flags = torch.zeros([8], dtype=torch.int32, device="cuda")
+    h = nat.LbHalo()
+    h.mode = nat.LB_HALO_LL
+    for k in range(3):
+        h.recv_lo[k], h.recv_hi[k] = lo[k].data_ptr(), hi[k].data_ptr()
+        h.peer_up_recv_lo[k], h.peer_down_recv_hi[k] = lo[k].data_ptr(), hi[k].data_ptr()
+    h.wait_slots = flags.data_ptr()
+    A, B = flow.f.clone(), torch.full_like(flow.f, float("nan"))
+    fl = nat.LbFields()
+    fl.f, fl.f_next = A.data_ptr(), B.data_ptr()
+    fl.halo = C.pointer(h)
+    nat.check(L.lb_step(desc, fl, 1, torch.cuda.current_stream().cuda_stream))
+    assert bool(torch.isfinite(B).all()) and int(flags[2].item()) == 0
