@@ -36,6 +36,11 @@ struct alignas(8) F2 {
 template <typename R> struct ValueTraits { using scalar = R; static constexpr int lanes = 1; };
 template <> struct ValueTraits<F2> { using scalar = float; static constexpr int lanes = 2; };
 
+#if defined(__CUDACC__)
+// -0.0 that ptxas cannot see through (constant memory may be rewritten by the host): operator* below
+static __constant__ float2 LB_NEG_ZERO2 = {-0.0f, -0.0f};
+#endif
+
 #if defined(__CUDA_ARCH__)
 __device__ __forceinline__ F2 operator+(F2 a, F2 b) {
   const float2 r = __fadd2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y));
@@ -46,7 +51,14 @@ __device__ __forceinline__ F2 operator-(F2 a, F2 b) {
   return F2(r.x, r.y);
 }
 __device__ __forceinline__ F2 operator*(F2 a, F2 b) {
-  const float2 r = __fmul2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y));
+  // a * b as fma(a, b, -0) with a -0 from constant memory: the same value as mul.rn (x * y + (-0) rounds x * y once
+  // and keeps the sign of a zero product), but ptxas can neither fold it back into a multiply nor contract it with
+  // a following add.  It DOES contract mul.rn.f32x2 + add.rn.f32x2 into FFMA2 -- despite the explicit rounding
+  // modifiers and -fmad=false, and unlike the scalar mul.rn / add.rn -- wherever a product feeds additions, which
+  // made the packed kernels round differently from the one-node-per-thread kernels (found at 8 GPUs, where 48 / 8 =
+  // 6 planes per slab run one node per thread: scripts/dev/scalar_vs_packed.cu, scripts/check_vec_width.py,
+  // profiles/r2_vector_width_dependence_*.log).
+  const float2 r = __ffma2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y), LB_NEG_ZERO2);
   return F2(r.x, r.y);
 }
 __device__ __forceinline__ F2 fma_(F2 a, F2 b, F2 c) {
