@@ -1195,6 +1195,62 @@ bool tma_default(size_t n_nodes) {
   return S::Q == 9 && n_nodes * S::Q * sizeof(T) <= (size_t(96) << 20);
 }
 
+// one explicit specialisation per (stencil, dtype, collision), each in its own translation unit
+// (lb_inst_*.cu) so that `make -j` spreads the ~400 kernel variants over all cores
+template <class S, typename T, int COLL>
+cudaError_t launch_step_coll(StepConfig& c, const StepParams<T>& p, cudaStream_t st);
+
+template <class S, typename T>
+cudaError_t launch_step(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
+  switch (c.collision) {
+    case COLL_NONE: return launch_step_coll<S, T, COLL_NONE>(c, p, st);
+    case COLL_BGK: return launch_step_coll<S, T, COLL_BGK>(c, p, st);
+    case COLL_TRT: return launch_step_coll<S, T, COLL_TRT>(c, p, st);
+    case COLL_KBC:
+      if constexpr (S::ID != 1) return launch_step_coll<S, T, COLL_KBC>(c, p, st);
+      else return cudaErrorNotSupported;
+    case COLL_REGULARIZED: return launch_step_coll<S, T, COLL_REGULARIZED>(c, p, st);
+    case COLL_SMAGORINSKY: return launch_step_coll<S, T, COLL_SMAGORINSKY>(c, p, st);
+    case COLL_BGK_FORCE: return launch_step_coll<S, T, COLL_BGK_FORCE>(c, p, st);
+  }
+  return cudaErrorInvalidValue;
+}
+
+// Nodes per thread along the contiguous axis that are COMPILED for (stencil, dtype, collision, mode): one
+// node per thread (any shape, any alignment) and one vector width -- 16 bytes, except where the register
+// budget says otherwise (measured):
+//   D3Q27 KBC / TRT / Smagorinsky hold ~60 values per node beside the populations: fp32 runs two nodes per
+//     thread as packed F2 values (<= 168 registers, three blocks per SM; 0.92 / 0.97 / 0.96 of the HBM
+//     roofline against 0.82 / 0.91 / 0.91 with four nodes), fp64 KBC one node per thread;
+//   D3Q27 with masked streaming: 212 registers (2 blocks per SM) with four nodes, 161 (3 blocks) with two;
+//     0.89 vs 0.92 on the stock obstacle.
+// Lines whose length or alignment does not fit the vector run one node per thread.
+template <class S, typename T>
+__host__ __device__ constexpr int vector_nodes(int coll, int mode) {
+  int v = 16 / int(sizeof(T));
+  if (S::Q == 27 && coll == COLL_KBC) v = (sizeof(T) == 4) ? 2 : 1;
+  if (S::Q == 27 && sizeof(T) == 4 && (coll == COLL_TRT || coll == COLL_SMAGORINSKY)) v = 2;
+  if (S::Q == 27 && sizeof(T) == 4 && mode == MODE_NCM_SBITS && v > 2) v = 2;
+  return v;
+}
+
+// blocks of a kernel that fit on the device at once (cached per instantiation)
+template <class K>
+int coresident_blocks(K kernel) {
+  static int cached = -1;
+  if (cached < 0) {
+    int dev = 0, sms = 0, per_sm = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess ||
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, STEP_BLOCK, 0) != cudaSuccess) {
+      (void)cudaGetLastError();
+      return 0;
+    }
+    cached = sms * per_sm;
+  }
+  return cached;
+}
+
 template <class S, typename T, int V, int COLL, int MODE, bool OBS>
 cudaError_t launch_tma(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   auto kernel = step_tma_kernel<S, T, V, COLL, MODE, OBS>;
