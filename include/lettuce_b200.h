@@ -294,6 +294,20 @@ LB_API int lb_enstrophy(const lb_desc* desc, const void* u, void* obs_scratch, d
 LB_API int lb_enstrophy_slab(const lb_desc* desc, const void* u_ext, int ghost, void* obs_scratch, double* obs_out,
                       void* stream);
 
+/* lb_observables without any allocation, the caller's included (no counterpart in the reference: added
+ * for callers that cannot call cudaMalloc -- code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same kernel and same result as lb_observables(desc, f, 0, NULL, scratch,
+ * obs_out, stream): obs_out[LB_OBS_ENERGY / MAXU2 / MASS] (device, double; LB_OBS_ENSTROPHY is left untouched).  The
+ * reduction scratch is a static __device__ array inside the library, sized for lattices of at most
+ * LB_STATIC_OBS_MAX_NODES nodes (about 3.0 MiB; every GPU that loads the library holds it until the process exits);
+ * a larger lattice returns LB_EUNSUPPORTED.  The call makes no cudaMalloc / cudaFree and calls no allocating
+ * library routine; it launches on `stream` of the CURRENT device (f must live there) and does not synchronise.
+ * All calls on a device share the one array: calls that may overlap on the GPU (different streams, no ordering
+ * between them) race on it -- serialise them, or use lb_observables with a scratch buffer per stream. */
+#define LB_STATIC_OBS_MAX_NODES 16777216ull /* 256^3 */
+LB_API size_t lb_static_obs_max_nodes(void);
+LB_API int lb_observables_static(const lb_desc* desc, const void* f, double* obs_out, void* stream);
+
 /* Host-buffer convenience entry (end-to-end path): copies f_host -> device, runs n_steps,
  * copies the result back into f_host, synchronises.  masks / boundary arrays are HOST
  * pointers here as well (nsm is the raw uint8 [q][*res] mask or NULL). */

@@ -34,7 +34,7 @@ EXPORTED_SYMBOLS = (
     "lb_enstrophy", "lb_run_host", "lb_stencil_q", "lb_bytes_per_update", "lb_vector_width",
     "lb_unpack_halo", "lb_zface_count", "lb_ipc_alloc", "lb_ipc_free", "lb_ipc_export",
     "lb_ipc_open", "lb_ipc_close", "lb_output_fields", "lb_unpack_halo_ex", "lb_halo_ll_bytes",
-    "lb_enstrophy_slab",
+    "lb_enstrophy_slab", "lb_static_obs_max_nodes", "lb_observables_static",
 )
 
 
@@ -125,6 +125,10 @@ def lib() -> C.CDLL:
     L.lb_halo_ll_bytes.restype = C.c_size_t
     L.lb_enstrophy_slab.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
     L.lb_zface_count.argtypes = [C.c_int]
+    L.lb_static_obs_max_nodes.argtypes = []
+    L.lb_static_obs_max_nodes.restype = C.c_size_t
+    L.lb_observables_static.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p]
+    L.lb_observables_static.restype = C.c_int
     L.lb_ipc_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
     L.lb_ipc_free.argtypes = [C.c_void_p]
     L.lb_ipc_export.argtypes = [C.c_void_p, C.c_char_p]

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "../../include/lettuce_b200.h"
@@ -1014,6 +1015,73 @@ int lb_enstrophy_slab(const lb_desc* desc, const void* u, int ghost, void* obs_s
 
 int lb_enstrophy(const lb_desc* desc, const void* u, void* obs_scratch, double* obs_out, void* stream) {
   return lb_enstrophy_slab(desc, u, 0, obs_scratch, obs_out, stream);
+}
+
+}  // extern "C"
+
+// ---- lb_observables_static: lb_observables without a caller-provided (or any) allocation ----------------------
+// The reduction scratch (ticket counters + per-block and per-group partials, lb::obs_scratch_bytes) lives in a
+// file-scope device array of a fixed maximum size: LB_STATIC_OBS_MAX_NODES nodes.  Every GPU that loads the library
+// holds these bytes until the process exits.  All calls on a device share the array.
+namespace {
+constexpr size_t STATIC_OBS_MAX_BLOCKS = (size_t(LB_STATIC_OBS_MAX_NODES) + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK;
+constexpr size_t STATIC_OBS_GROUPS = (STATIC_OBS_MAX_BLOCKS + lb::OBS_GROUP - 1) / lb::OBS_GROUP;
+constexpr size_t STATIC_OBS_BYTES =   // == lb::obs_scratch_bytes(STATIC_OBS_MAX_BLOCKS), checked at set-up
+    64 + ((STATIC_OBS_GROUPS * sizeof(unsigned) + 63) / 64) * 64 +
+    (STATIC_OBS_MAX_BLOCKS + STATIC_OBS_GROUPS) * lb::N_OBS_PART * sizeof(double);
+static __device__ __align__(256) unsigned char g_static_obs_scratch[STATIC_OBS_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+void* g_static_obs_ptr[STATIC_MAX_DEVICES] = {};   // device address of the array, per device ordinal
+std::mutex g_static_obs_mutex;
+
+// Device address of g_static_obs_scratch on the CURRENT device.  In host code the array's name is only a stand-in
+// for the symbol, not a device address: the address comes from cudaGetSymbolAddress, once per device, with that
+// device current.
+int static_obs_scratch(int dev, void** out) {
+  if (dev < 0 || dev >= STATIC_MAX_DEVICES) return fail(LB_EUNSUPPORTED, "device ordinal %d beyond %d", dev, STATIC_MAX_DEVICES);
+  std::lock_guard<std::mutex> lock(g_static_obs_mutex);
+  if (!g_static_obs_ptr[dev]) {
+    if (lb::obs_scratch_bytes(STATIC_OBS_MAX_BLOCKS) != STATIC_OBS_BYTES)
+      return fail(LB_ECUDA, "static scratch size out of step with lb::obs_scratch_bytes");
+    void* ptr = nullptr;
+    LB_CUDA(cudaGetSymbolAddress(&ptr, g_static_obs_scratch));
+    if (!ptr) return fail(LB_ECUDA, "cudaGetSymbolAddress returned a null address");
+    g_static_obs_ptr[dev] = ptr;
+  }
+  *out = g_static_obs_ptr[dev];
+  return LB_OK;
+}
+}  // namespace
+
+extern "C" {
+
+size_t lb_static_obs_max_nodes(void) { return size_t(LB_STATIC_OBS_MAX_NODES); }
+
+int lb_observables_static(const lb_desc* desc, const void* f, double* obs_out, void* stream) {
+  Geometry g;
+  int rc = check_desc(desc, &g);
+  if (rc) return rc;
+  if (!f || !obs_out) return fail(LB_EINVAL, "null pointer");
+  if (size_t(g.n_nodes) > size_t(LB_STATIC_OBS_MAX_NODES))
+    return fail(LB_EUNSUPPORTED,
+                "lb_observables_static: %u nodes exceed the built-in scratch of LB_STATIC_OBS_MAX_NODES = %llu nodes "
+                "(%llu bytes); use lb_observables with caller-provided scratch",
+                g.n_nodes, (unsigned long long)LB_STATIC_OBS_MAX_NODES, (unsigned long long)STATIC_OBS_BYTES);
+  int dev = -1;
+  LB_CUDA(cudaGetDevice(&dev));
+  cudaPointerAttributes attr{};
+  LB_CUDA(cudaPointerGetAttributes(&attr, f));
+  if (attr.type == cudaMemoryTypeDevice && attr.device != dev)
+    return fail(LB_EINVAL, "f lives on device %d but device %d is current: the built-in scratch is per device", attr.device, dev);
+  void* scratch = nullptr;
+  rc = static_obs_scratch(dev, &scratch);
+  if (rc) return rc;
+  // moments_typed clears the ticket counters (cudaMemsetAsync on `stream`, the only part that must start at zero;
+  // the partials are written before they are read) and launches the same moments_kernel<OBS> as lb_observables
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return desc->dtype == LB_F32 ? moments_stencil<float>(desc, g, f, nullptr, nullptr, scratch, obs_out, st)
+                               : moments_stencil<double>(desc, g, f, nullptr, nullptr, scratch, obs_out, st);
 }
 
 }  // extern "C"
