@@ -99,7 +99,10 @@ typedef struct lb_desc {
 enum {
   LB_KF_NO_TMA = 1,    /* never use the persistent TMA-prefetch step kernel                                */
   LB_KF_FORCE_TMA = 2, /* use it wherever it applies (plain lattices of whole, 16-byte aligned tiles)      */
-  LB_KF_NO_LOOP = 4    /* one launch per time step also where the cooperative multi-step kernel would fit */
+  LB_KF_NO_LOOP = 4,   /* one launch per time step also where the cooperative multi-step kernel would fit */
+  LB_KF_FORCE_PREFETCH = 8, /* persistent per-thread prefetch (cp.async) step kernel wherever it is compiled and applies */
+  LB_KF_NO_PREFETCH = 16,   /* never use it                                                                    */
+  LB_KF_NO_RESIDENT = 32    /* small 2-D lattices: not the tile-resident multi-step kernel (state in shared memory) */
 };
 
 /* One entry per boundary object, in the order lettuce sorted them

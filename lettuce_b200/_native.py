@@ -54,6 +54,7 @@ class LbDesc(C.Structure):
 
 
 LB_KF_NO_TMA, LB_KF_FORCE_TMA, LB_KF_NO_LOOP = 1, 2, 4
+LB_KF_FORCE_PREFETCH, LB_KF_NO_PREFETCH, LB_KF_NO_RESIDENT = 8, 16, 32
 
 
 class LbBoundary(C.Structure):

@@ -253,6 +253,12 @@ int step_typed(const lb_desc* d, const Geometry& g, const lb_fields* fl, int n_s
   if (tma_env) c.tma = atoi(tma_env) != 0 ? 1 : 0;
   if (d->kernel_flags & LB_KF_NO_TMA) c.tma = 0;
   if (d->kernel_flags & LB_KF_FORCE_TMA) c.tma = 1;
+  static const char* pf_env = getenv("LB_PF");     // A/B timing: the per-thread prefetch kernel, 0 = never, 1 = wherever
+  if (pf_env) c.pf = atoi(pf_env) != 0 ? 1 : 0;
+  if (d->kernel_flags & LB_KF_NO_PREFETCH) c.pf = 0;
+  if (d->kernel_flags & LB_KF_FORCE_PREFETCH) { c.pf = 1; c.tma = 0; }
+  static const bool no_resident = getenv("LB_NO_RESIDENT") != nullptr;   // A/B timing only
+  c.resident = !no_resident && !(d->kernel_flags & LB_KF_NO_RESIDENT);
   c.vec = do_stream ? vector_width<S, T>(c.collision, c.mode, g, fl->f, fl->f_next, p.ncm, p.sbits,
                                             p.has_outlet && p.sbits == nullptr) : 1;
   p.nzv = g.nz / c.vec;

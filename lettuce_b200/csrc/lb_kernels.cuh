@@ -127,6 +127,7 @@ struct StepParams {
   // plane at the END of the lattice to the front: they run the long boundary path (neighbour loads,
   // masked stores), and as the last blocks of the grid that path was a tail of 6-9 us per step.
   unsigned block_rot;
+  unsigned pf_chunk;   // prefetch kernel: > 0 = consecutive tiles per CTA, scheduled by the hardware (see step_pf_kernel)
 };
 
 // number of directions q' < q that leave through the same z face as q
@@ -392,6 +393,17 @@ __device__ __forceinline__ void outlet_node(T (&g)[S::Q], const BoundaryDev<T>& 
   });
 }
 
+// u [D][n_nodes] of one node for the enstrophy kernel.  Out of line ON PURPOSE: only the reporting steps of an
+// Enstrophy reporter take it, but inlined the compiler predicates the D stores and their 64-bit address arithmetic into
+// the hot path of every OBS kernel; a call is a branch that the other steps skip.  c0, c1, c2 = components in lattice
+// order (c2 ignored in 2-D).
+template <int D, typename T>
+__device__ __noinline__ void store_velocity(T* u_out, unsigned n_nodes, unsigned node, T c0, T c1, T c2) {
+  u_out[node] = c0;
+  u_out[size_t(n_nodes) + node] = c1;
+  if constexpr (D == 3) u_out[2 * size_t(n_nodes) + node] = c2;
+}
+
 // One node: moments -> (fused observables) -> collision where ncm == 0, boundary i where ncm == i
 // OUTLETS: compile the in-order boundary loop that outlet planes need (the masked-streaming kernels --
 // outlets always come with a streaming mask -- and the one-node-per-thread kernels)
@@ -411,10 +423,8 @@ __device__ __forceinline__ void node_update(T (&g)[S::Q], unsigned m, const Step
     acc_e += T(0.5) * u2;
     acc_m2 = max_(acc_m2, u2);
     acc_mass += rho;
-    if (u_out != nullptr && active) {   // only on steps that feed the enstrophy kernel
-#pragma unroll
-      for (int c = 0; c < S::D; ++c) u_out[c * size_t(p.n_nodes) + node] = u[S::axis(c)];
-    }
+    if (u_out != nullptr && active)    // only on steps that feed the enstrophy kernel
+      store_velocity<S::D, T>(u_out, p.n_nodes, node, u[S::axis(0)], u[S::axis(1)], u[S::axis(S::D - 1)]);
   }
   if (m == 0) {
     collide_node<S, T, COLL, T>(g, a, b, rho, u, p.cp);
@@ -475,11 +485,8 @@ __device__ __forceinline__ void packed_update(F2 (&g)[S::Q], const StepParams<fl
     acc_mass += rho.x;
     acc_mass += rho.y;
     if (u_out != nullptr && active) {
-#pragma unroll
-      for (int c = 0; c < S::D; ++c) {
-        u_out[c * size_t(p.n_nodes) + node] = u[S::axis(c)].x;
-        u_out[c * size_t(p.n_nodes) + node + 1] = u[S::axis(c)].y;
-      }
+      store_velocity<S::D, float>(u_out, p.n_nodes, node, u[S::axis(0)].x, u[S::axis(1)].x, u[S::axis(S::D - 1)].x);
+      store_velocity<S::D, float>(u_out, p.n_nodes, node + 1, u[S::axis(0)].y, u[S::axis(1)].y, u[S::axis(S::D - 1)].y);
     }
   }
   collide_node<S, F2, COLL, float>(g, a, b, rho, u, p.cp);
@@ -551,15 +558,19 @@ constexpr int step_min_blocks() {
 
 // One time step of the lattice for this thread and tile `blk` (STEP_BLOCK threads x V nodes): f_in -> f_out, and the
 // thread's observables of f_in (sum 0.5 |u|^2, max |u|^2, sum rho over its V nodes; zero for a thread beyond the
-// lattice) into t_e / t_m2 / t_mass when OBS.  SMEM_IN: the tile's populations are already in shared memory
-// (smem_in[q][STEP_BLOCK * V], brought in by bulk copies) instead of global memory.
+// lattice) into t_e / t_m2 / t_mass when OBS.  SMEM_IN != 0: the tile's populations are already in shared memory
+// (smem_in[q][STEP_BLOCK * V]) instead of global memory --
+//   SMEM_TMA:     brought in by bulk copies for the whole block; the block hands the stage back with a barrier;
+//   SMEM_PRIVATE: every thread copied ITS OWN V values per population (cp.async) and reads only those: no barrier,
+//                 the tile's mask word arrives in `mword_pf` (loaded into a register one tile ahead).
+enum { SMEM_NONE = 0, SMEM_TMA = 1, SMEM_PRIVATE = 2 };
 struct NoRefill { __device__ __forceinline__ void operator()() const {} };
 
-template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO, bool SMEM_IN = false,
+template <class S, typename T, int V, int COLL, int MODE, bool OBS, bool STREAM, bool HALO, int SMEM_IN = SMEM_NONE,
           class Refill = NoRefill>
 __device__ __forceinline__ void step_tile(const StepParams<T>& p, const T* __restrict__ f_in, T* __restrict__ f_out,
                                           T* u_out, unsigned blk, const T* smem_in, T& t_e, T& t_m2, T& t_mass,
-                                          Refill smem_tile_consumed = Refill{}) {
+                                          Refill smem_tile_consumed = Refill{}, uint32_t mword_pf = 0u) {
   constexpr int Q = S::Q;
   const unsigned lane = threadIdx.x & 31u;
   const unsigned tid = blk * STEP_BLOCK + threadIdx.x;
@@ -603,17 +614,19 @@ __device__ __forceinline__ void step_tile(const StepParams<T>& p, const T* __res
     });
   }
   [[maybe_unused]] uint32_t smem_mword = 0;
-  if constexpr (SMEM_IN && MODE != MODE_PLAIN)
+  if constexpr (SMEM_IN == SMEM_TMA && MODE != MODE_PLAIN)
     smem_mword = ld_mask<V>(reinterpret_cast<const uint8_t*>(smem_in + Q * (STEP_BLOCK * V)) + threadIdx.x * V);
-  if constexpr (SMEM_IN) {
+  if constexpr (SMEM_IN == SMEM_TMA) {
     // the stage is free as soon as every thread holds its values: the producer refills it while this tile
     // computes and stores (the caller issues the next bulk copies right behind this barrier)
     __syncthreads();
     smem_tile_consumed();
   }
+  if constexpr (SMEM_IN == SMEM_PRIVATE) smem_tile_consumed();   // the thread's own slots: refilled at once
   uint32_t mword = 0;
   if constexpr (MODE != MODE_PLAIN) {
-    if constexpr (SMEM_IN) mword = smem_mword;     // the tile's mask bytes came with the populations
+    if constexpr (SMEM_IN == SMEM_TMA) mword = smem_mword;     // the tile's mask bytes came with the populations
+    else if constexpr (SMEM_IN == SMEM_PRIVATE) mword = mword_pf;
     else mword = ld_mask<V>(p.ncm + node);
   }
   // ---- incoming halo (multi-GPU): issued right behind the population loads so that both are in flight
@@ -1053,7 +1066,7 @@ step_tma_kernel(const __grid_constant__ StepParams<T> p) {
     const int s = int(it % TMA_STAGES);
     mbar_wait(&full[s], (it / TMA_STAGES) & 1u);
     T te = T(0), tm2 = T(0), tmass = T(0);
-    step_tile<S, T, V, COLL, MODE, OBS, true, false, true>(
+    step_tile<S, T, V, COLL, MODE, OBS, true, false, SMEM_TMA>(
         p, p.f_in, p.f_out, p.u_out, tile, stages + size_t(s) * STAGE_ELEMS, te, tm2, tmass, [&]() {
           const unsigned next = tile + unsigned(TMA_STAGES) * gridDim.x;
           if (threadIdx.x < 32u && next < n_tiles) issue(next, s);
@@ -1061,6 +1074,87 @@ step_tma_kernel(const __grid_constant__ StepParams<T> p) {
     if constexpr (OBS) { e += double(te); m2 = fmax(m2, double(tm2)); mass += double(tmass); }
   }
   if constexpr (OBS) {   // one partial per CTA; obs_finish_kernel adds them up (fixed order: deterministic)
+    block_reduce3<STEP_BLOCK>(e, m2, mass);
+    if (threadIdx.x == 0) {
+      double* bp = p.obs.block_partials + size_t(blockIdx.x) * N_OBS_PART;
+      bp[0] = e; bp[1] = m2; bp[2] = mass;
+    }
+  }
+}
+
+// --------------------------------------------------------------------------------------
+// Persistent variant with PER-THREAD prefetch (cp.async / LDGSTS).  For the register-heavy collisions (D3Q27 KBC:
+// 160 registers, three CTAs per SM, ncu: long_scoreboard, 0.91 of the HBM roofline at 512^3) the classic kernel is
+// latency-bound: a CTA's loads are in flight only while it waits for them, not while it computes and stores, and
+// there are no registers for a second tile.  Here every thread copies the Q x V values of ITS OWN part of the next
+// tile into its own shared-memory slots while it works on the current one -- asynchronously, without registers.
+// A thread reads only what it copied itself, so there is no block barrier and no mbarrier anywhere (the TMA
+// variant above runs its CTAs in lock step per tile): cp.async.wait_group orders the thread's own copies, the
+// occupancy and the body are the classic kernel's.  One stage: Q * V * sizeof(T) bytes per thread.
+// --------------------------------------------------------------------------------------
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void* smem_dst, const void* gmem_src) {
+  static_assert(BYTES == 4 || BYTES == 8 || BYTES == 16, "cp.async sizes");
+  if constexpr (BYTES == 16)
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+  else
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "n"(BYTES) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+template <class S, typename T, int V>
+constexpr size_t pf_smem_bytes() { return size_t(S::Q) * STEP_BLOCK * V * sizeof(T); }
+
+template <class S, typename T, int V, int COLL, int MODE, bool OBS>
+__global__ void __launch_bounds__(STEP_BLOCK, step_min_blocks<S, T, V, COLL, MODE>())
+step_pf_kernel(const __grid_constant__ StepParams<T> p) {
+  static_assert(MODE == MODE_PLAIN || MODE == MODE_NCM, "no masked streaming in the prefetch kernel");
+  constexpr unsigned TILE = STEP_BLOCK * V;                    // nodes per tile
+  extern __shared__ __align__(128) unsigned char pf_smem[];
+  T* const stage = reinterpret_cast<T*>(pf_smem);
+  asm volatile("griddepcontrol.launch_dependents;");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const unsigned n_tiles = p.n_threads / STEP_BLOCK;           // whole tiles only (host-checked)
+  const size_t N = p.n_nodes;
+  T* const mine = stage + threadIdx.x * V;                     // + q * TILE: this thread's V values of population q
+  uint32_t mword_next = 0;
+  auto prefetch = [&](unsigned tile) {
+    const size_t node = size_t(tile) * TILE + threadIdx.x * V;
+    static_for<S::Q>([&](auto qc) {
+      constexpr int q = decltype(qc)::value;
+      cp_async<int(V * sizeof(T))>(mine + q * TILE, p.f_in + size_t(q) * N + node);
+    });
+    cp_async_commit();
+    if constexpr (MODE != MODE_PLAIN) mword_next = ld_mask<V>(p.ncm + node);   // needed one tile from now
+  };
+  // Which tiles a CTA works on (kernel-uniform):
+  //   p.pf_chunk = K > 0 (the default, K = 2 .. 4, see pf_chunk()): the K consecutive tiles blockIdx.x * K ...; the grid has n_tiles / K
+  //     CTAs and the hardware block scheduler balances the SMs exactly as it does for the classic kernel.  A CTA's
+  //     first tile is not prefetched, the others are;
+  //   p.pf_chunk = 0: persistent, one CTA per resident slot, tiles blockIdx.x + k * gridDim.x.  Measured 15 - 30 %
+  //     SLOWER than the classic kernel (profiles/r2_bench_prefetch_persistent_by_stride.jsonl): the SMs do not all see
+  //     the same memory bandwidth and the call ends when the slowest CTA has done its fixed share.  With the tiles
+  //     handed out dynamically (atomic counter, experiment) the same kernel was 4 % FASTER than the classic one; the
+  //     chunked schedule gets the same effect from the hardware scheduler, needs no counter, and its tile -> CTA map
+  //     is fixed, which keeps the fused reductions bitwise reproducible.
+  const unsigned chunk = p.pf_chunk;
+  unsigned tile = chunk ? blockIdx.x * chunk : blockIdx.x;
+  const unsigned tile_end = chunk ? min(n_tiles, tile + chunk) : n_tiles;
+  const unsigned stride = chunk ? 1u : gridDim.x;
+  if (tile < tile_end) prefetch(tile);
+  double e = 0.0, m2 = 0.0, mass = 0.0;
+  for (; tile < tile_end; tile += stride) {
+    cp_async_wait_all();
+    const uint32_t mword = mword_next;
+    T te = T(0), tm2 = T(0), tmass = T(0);
+    step_tile<S, T, V, COLL, MODE, OBS, true, false, SMEM_PRIVATE>(
+        p, p.f_in, p.f_out, p.u_out, tile, stage, te, tm2, tmass, [&]() {
+          if (tile + stride < tile_end) prefetch(tile + stride);
+        }, mword);
+    if constexpr (OBS) { e += double(te); m2 = fmax(m2, double(tm2)); mass += double(tmass); }
+  }
+  if constexpr (OBS) {   // one partial per CTA (fixed tiles per CTA); obs_finish_kernel adds them up in a fixed order
     block_reduce3<STEP_BLOCK>(e, m2, mass);
     if (threadIdx.x == 0) {
       double* bp = p.obs.block_partials + size_t(blockIdx.x) * N_OBS_PART;
@@ -1170,6 +1264,10 @@ cudaError_t launch_moments_impl(const MomentsParams<T>& p, cudaStream_t st) {
   return cudaGetLastError();
 }
 
+}  // namespace lb
+#include "lb_resident.cuh"
+namespace lb {
+
 // --------------------------------------------------------------------------------------
 // host-side dispatch (runtime descriptor -> template instantiation), one per (stencil, T)
 // --------------------------------------------------------------------------------------
@@ -1183,6 +1281,8 @@ struct StepConfig {
   bool stream;
   bool halo;      // z-slab halo plumbing compiled in (multi-GPU)
   int tma = -1;   // persistent TMA-prefetch kernel: -1 = the compiled-in default, 0 = never, 1 = wherever it applies
+  int pf = -1;    // persistent per-thread prefetch kernel (cp.async): the same three values
+  bool resident = true;   // small 2-D lattices: the tile-resident multi-step kernel (lb_resident.cuh) where it fits
   unsigned obs_blocks = 0;   // out: thread blocks that wrote a partial of the fused reduction
 };
 
@@ -1283,6 +1383,65 @@ cudaError_t launch_tma(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
   return cudaLaunchKernelEx(&cfg, kernel, p);
 }
 
+// The per-thread prefetch kernel is compiled for the stencil whose collisions are register-bound (D3Q27: three CTAs
+// per SM or fewer) and for D2Q9, and is the default where it was measured to win (profiles/r2_bench_prefetch.jsonl,
+// 256^3 fp32, fraction of the HBM roofline classic -> prefetch: KBC 0.95 -> 0.99, with an every-step energy reporter
+// 0.86 -> 0.93, TRT 0.99 -> 1.01, Smagorinsky 0.96 -> 1.00; BGK 1.03 -> 1.00, regularized 1.00 -> 0.97 and every fp64
+// variant -- KBC fp64, one node per thread: 0.83 -> 0.75 -- stay with the classic kernel).
+template <class S, typename T, int COLL>
+constexpr bool pf_compiled() { return (S::Q == 27 && COLL != COLL_NONE) || S::Q == 9; }
+template <class S, typename T, int COLL>
+bool pf_default(size_t n_nodes) {
+  if (S::Q == 27) return sizeof(T) == 4 && (COLL == COLL_KBC || COLL == COLL_TRT || COLL == COLL_SMAGORINSKY);
+  // D2Q9 KBC fp32 beyond the L2-sized lattices that the TMA kernel takes (4096^2: 0.95 -> 1.03; TMA 0.81)
+  return S::Q == 9 && sizeof(T) == 4 && COLL == COLL_KBC && !tma_default<S, T, COLL>(n_nodes);
+}
+// Tiles per CTA.  More tiles per CTA = more of them prefetched, fewer CTAs = a coarser tail: measured on D3Q27 KBC
+// fp32, fraction of the HBM roofline, at 256^3 (65 536 tiles, 444 resident CTAs): 2 -> 1.00, 4 -> 0.99, 8 -> 0.96,
+// 16 -> 0.92; at 512^3 (524 288 tiles): 2 -> 0.92, 3 -> 0.93, 4 -> 0.94, 8 -> 0.92.  So: 4 where that still leaves
+// >= 64 waves of CTAs, else 3, else 2.
+inline unsigned pf_chunk(unsigned n_tiles, unsigned resident) {
+  for (unsigned k = 4; k > 2; --k)
+    if (n_tiles / k >= 64u * resident) return k;
+  return 2;
+}
+
+template <class S, typename T, int V, int COLL, int MODE, bool OBS>
+cudaError_t launch_pf(StepConfig& c, const StepParams<T>& p_in, cudaStream_t st) {
+  auto kernel = step_pf_kernel<S, T, V, COLL, MODE, OBS>;
+  constexpr size_t smem = pf_smem_bytes<S, T, V>();
+  static int resident = -1;   // CTAs the device holds at once
+  if (resident < 0) {
+    int dev = 0, sms = 0, per_sm = 0;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    if (e == cudaSuccess) e = cudaGetDevice(&dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e == cudaSuccess) e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, STEP_BLOCK, smem);
+    if (e != cudaSuccess) return e;
+    resident = sms * per_sm;
+    if (resident <= 0) return cudaErrorLaunchOutOfResources;
+  }
+  static const int chunk_env = getenv("LB_PF_CHUNK") ? atoi(getenv("LB_PF_CHUNK")) : -1;   // A/B timing only
+  StepParams<T> p = p_in;
+  const unsigned n_tiles = p.n_threads / STEP_BLOCK;
+  p.pf_chunk = chunk_env >= 0 ? unsigned(chunk_env) : pf_chunk(n_tiles, unsigned(resident));
+  unsigned grid = n_tiles < unsigned(resident) ? n_tiles : unsigned(resident);
+  if (p.pf_chunk) grid = (n_tiles + p.pf_chunk - 1u) / p.pf_chunk;
+  c.obs_blocks = grid;
+  static const bool no_pdl = getenv("LB_NO_PDL") != nullptr;   // A/B timing only
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(STEP_BLOCK);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = no_pdl ? 0 : 1;
+  return cudaLaunchKernelEx(&cfg, kernel, p);
+}
+
 // the persistent TMA kernel applies to: lattices without masked streaming, outlets and halos, made of whole tiles
 // whose population (and mask) chunks are 16-byte aligned in global memory
 template <typename T, int V>
@@ -1301,7 +1460,25 @@ cudaError_t launch_one(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
     if ((c.tma == 1 || (c.tma < 0 && tma_default<S, T, COLL>(p.n_nodes))) && tma_applicable<T, V>(c, p))
       return launch_tma<S, T, V, COLL, MODE, OBS>(c, p, st);
   }
+  if constexpr (STREAM && !HALO && (MODE == MODE_PLAIN || MODE == MODE_NCM) && pf_compiled<S, T, COLL>()) {
+    // whole tiles, a grid of several waves, no outlet planes (they read neighbours from global memory)
+    const bool applies = (c.mode == MODE_PLAIN || !p.has_outlet) && c.loop_steps <= 1 && p.n_threads % STEP_BLOCK == 0 &&
+                         p.n_threads / STEP_BLOCK >= 4u * 148u &&
+                         (V == 1 || ((size_t(p.n_nodes) * sizeof(T)) % 16 == 0 && (reinterpret_cast<uintptr_t>(p.f_in) & 15u) == 0));
+    if ((c.pf == 1 || (c.pf < 0 && pf_default<S, T, COLL>(p.n_nodes))) && applies)
+      return launch_pf<S, T, V, COLL, MODE, OBS>(c, p, st);
+  }
   if (c.loop_steps > 1) {
+    // small 2-D lattice without masks and reductions: the state stays in shared memory for several steps
+    if constexpr (STREAM && !HALO && MODE == MODE_PLAIN && !OBS && S::D == 2) {
+      if (c.resident) {
+        bool done = false;
+        const cudaError_t e = launch_resident<S, T, COLL>(const_cast<T*>(p.f_in), p.f_out, p.ny, p.nz, p.cp, c.loop_steps,
+                                                          st, &done);
+        if (e != cudaSuccess) return e;
+        if (done) { c.looped = true; return cudaSuccess; }
+      }
+    }
     // request for ONE launch covering loop_steps steps: honoured if the grid is co-resident, otherwise
     // nothing is launched and the caller (c.looped == false) issues one launch per step
     if constexpr (STREAM && !HALO && V > 1) {

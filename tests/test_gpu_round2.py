@@ -194,3 +194,98 @@ def test_every_output_element_is_written(case):
     fl.halo = C.pointer(h)
     nat.check(L.lb_step(desc, fl, 1, torch.cuda.current_stream().cuda_stream))
     assert bool(torch.isfinite(B).all()) and int(flags[2].item()) == 0
+
+
+@pytest.mark.parametrize("stencil,dtype,res,collision", [
+    ("D3Q27", torch.float32, [64, 64, 128], "kbc"), ("D3Q27", torch.float32, [64, 64, 128], "trt"),
+    ("D3Q27", torch.float32, [64, 64, 128], "bgk"), ("D3Q27", torch.float32, [64, 64, 128], "smagorinsky"),
+    ("D3Q27", torch.float32, [64, 64, 128], "regularized"), ("D3Q27", torch.float64, [48, 64, 64], "bgk"),
+    ("D3Q27", torch.float32, [37, 64, 256], "kbc"), ("D3Q27", torch.float64, [48, 64, 64], "kbc"),
+    ("D3Q27", torch.float32, [64, 64, 65], "kbc"), ("D3Q27", torch.float32, [66, 64, 66], "trt"), ("D2Q9", torch.float32, [1024, 512], "kbc"),
+    ("D2Q9", torch.float64, [999, 512], "bgk"), ("D2Q9", torch.float32, [1024, 512], "none"),
+])
+def test_prefetch_kernel_equals_classic_kernel(stencil, dtype, res, collision):
+    """LB_KF_FORCE_PREFETCH (every thread copies its own part of the CTA's next tile into shared memory with cp.async
+    while it works on the current one; a CTA takes consecutive tiles) against the classic kernel: the same
+    populations bit for bit, the same fused energy / max-velocity series up to the order of the partial sums.
+    D3Q27 and D2Q9 (where it is compiled), vector and one-node-per-thread widths (D3Q27 KBC fp64, odd line
+    lengths), tile counts that are not a multiple of the tiles per CTA."""
+    gu, lt = _lt()
+    nat = lt.native
+    out = {}
+    for flag in (nat.LB_KF_NO_PREFETCH | nat.LB_KF_NO_TMA, nat.LB_KF_FORCE_PREFETCH):
+        ctx = lt.Context(device="cuda", dtype=dtype, use_native=True)
+        flow = lt.TaylorGreenVortex(ctx, resolution=res, reynolds_number=800, mach_number=0.1, stencil=getattr(lt, stencil))
+        reps = [lt.ObservableReporter(lt.IncompressibleKineticEnergy(flow), interval=1, out=None),
+                lt.ObservableReporter(lt.MaximumVelocity(flow), interval=2, out=None)]
+        sim = lt.Simulation(flow, _collision(lt, flow, collision), reps)
+        sim.kernel_flags = flag | nat.LB_KF_NO_LOOP
+        sim(5)
+        plain = lt.Simulation(flow, _collision(lt, flow, collision), [])     # and without the fused reductions
+        plain.kernel_flags = flag | nat.LB_KF_NO_LOOP
+        plain(4)
+        out[flag] = (flow.f.clone(), [r[2] for r in reps[0].out], [r[2] for r in reps[1].out])
+    a, b = out[nat.LB_KF_NO_PREFETCH | nat.LB_KF_NO_TMA], out[nat.LB_KF_FORCE_PREFETCH]
+    assert torch.equal(a[0], b[0]) and bool(torch.isfinite(a[0]).all())
+    tol = 1e-6 if dtype == torch.float32 else 1e-13
+    assert a[1] == pytest.approx(b[1], rel=tol) and a[2] == pytest.approx(b[2], rel=tol)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64], ids=["f32", "f64"])
+def test_prefetch_kernel_with_no_collision_mask(dtype):
+    """bounce-back solid + two equilibrium boundaries on D3Q27: the prefetch kernel loads a tile's mask word one tile
+    ahead into a register -- same bits as the classic kernel; and every output element is written (NaN pre-fill)"""
+    gu, lt = _lt()
+    nat = lt.native
+    out = []
+    for flag in (nat.LB_KF_NO_PREFETCH | nat.LB_KF_NO_TMA, nat.LB_KF_FORCE_PREFETCH):
+        ctx = lt.Context(device="cuda", dtype=dtype, use_native=True)
+
+        class LocalObstacle(lt.Obstacle):
+            @property
+            def boundaries(self):
+                x = self.grid[0]
+                u_in = self.units.characteristic_velocity_pu * self._unit_vector()
+                return [lt.EquilibriumBoundaryPU(context=self.context, mask=torch.abs(x) < 1e-6, velocity=u_in),
+                        lt.EquilibriumBoundaryPU(context=self.context, mask=torch.abs(x - x.max()) < 1e-6, velocity=u_in),
+                        lt.BounceBackBoundary(self.mask)]
+        flow = LocalObstacle(ctx, [64, 64, 128], reynolds_number=200, mach_number=0.05, domain_length_x=1, stencil=lt.D3Q27)
+        g = flow.grid
+        flow.mask = sum((c - 0.4 * c.max()) ** 2 for c in g) < (0.1 * g[1].max()) ** 2
+        rep = lt.ObservableReporter(lt.IncompressibleKineticEnergy(flow), interval=1, out=None)
+        sim = lt.Simulation(flow, lt.BGKCollision(tau=max(float(flow.units.relaxation_parameter_lu), 0.55)), [rep])
+        sim.kernel_flags = flag | nat.LB_KF_NO_LOOP
+        sim(5)
+        flow.f_next.fill_(float("nan"))
+        sim._collide_and_stream(sim)
+        out.append((flow.f.clone(), [r[2] for r in rep.out]))
+    assert torch.equal(out[0][0], out[1][0]) and bool(torch.isfinite(out[0][0]).all())
+    assert out[0][1] == pytest.approx(out[1][1], rel=1e-6 if dtype == torch.float32 else 1e-13)
+
+
+@pytest.mark.parametrize("dtype,res,collision,steps", [
+    (torch.float64, [256, 256], "bgk", 50), (torch.float64, [256, 256], "bgk", 37), (torch.float32, [256, 256], "bgk", 64),
+    (torch.float64, [128, 128], "kbc", 21), (torch.float32, [96, 160], "trt", 30), (torch.float64, [100, 36], "bgk", 2),
+    (torch.float64, [100, 36], "bgk", 3), (torch.float32, [64, 64], "none", 70), (torch.float64, [97, 64], "regularized", 9),
+    (torch.float32, [16, 16], "bgk", 25), (torch.float64, [384, 320], "bgk", 12), (torch.float32, [256, 256], "smagorinsky", 11),
+])
+def test_tile_resident_kernel_equals_one_launch_per_step(dtype, res, collision, steps):
+    """small 2-D lattices: the multi-step call keeps tiles of the lattice in shared memory for h steps per grid
+    barrier (lb_resident.cuh; halo nodes recomputed by the neighbouring CTAs).  Same populations, bit for bit, as one
+    launch per step (LB_KF_NO_LOOP) and as the cooperative loop kernel (LB_KF_NO_RESIDENT); two calls in a row (the
+    state must end in the buffer the host expects for odd and even step counts)."""
+    gu, lt = _lt()
+    nat = lt.native
+    out = []
+    for flag in (nat.LB_KF_NO_LOOP | nat.LB_KF_NO_TMA, nat.LB_KF_NO_RESIDENT, 0):
+        ctx = lt.Context(device="cuda", dtype=dtype, use_native=True)
+        flow = lt.TaylorGreenVortex(ctx, resolution=res, reynolds_number=100, mach_number=0.05, stencil=lt.D2Q9)
+        sim = lt.Simulation(flow, _collision(lt, flow, collision), [])
+        sim.kernel_flags = flag
+        sim(steps)
+        a = flow.f.clone()
+        sim(steps + 1)
+        out.append((a, flow.f.clone(), flow.i))
+    for o in out[1:]:
+        assert torch.equal(o[0], out[0][0]) and torch.equal(o[1], out[0][1]) and o[2] == out[0][2]
+    assert bool(torch.isfinite(out[0][1]).all())
