@@ -12,7 +12,8 @@ from typing import Optional, Sequence
 
 import torch
 
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "liblettuce_b200.so")
+# LETTUCE_B200_LIB: another build of the same library (A/B of build variants in scripts/; never a fallback)
+LIB_PATH = os.environ.get("LETTUCE_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "liblettuce_b200.so")
 
 LB_D2Q9, LB_D3Q19, LB_D3Q27 = 0, 1, 2
 LB_F32, LB_F64 = 0, 1

@@ -99,7 +99,7 @@ __host__ __device__ __forceinline__ F2 div_(F2 a, F2 b) { return F2(a.x / b.x, a
 
 // 1-ulp reciprocal (one MUFU.RCP, no range fix-up) for fp32, exact division for fp64
 __host__ __device__ __forceinline__ float rcp_fast(float x) {
-#if defined(__CUDA_ARCH__)
+#if defined(__CUDA_ARCH__) && !defined(LB_EXACT_RCP)   // -DLB_EXACT_RCP: IEEE division (scripts/kbc_rcp_count.py, A/B only)
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
   return r;

@@ -289,3 +289,4 @@ def test_tile_resident_kernel_equals_one_launch_per_step(dtype, res, collision, 
     for o in out[1:]:
         assert torch.equal(o[0], out[0][0]) and torch.equal(o[1], out[0][1]) and o[2] == out[0][2]
     assert bool(torch.isfinite(out[0][1]).all())
+
