@@ -651,8 +651,13 @@ int moments_typed(const Geometry& g, const void* f, void* rho_out, void* u_out, 
     const int rc = obs_prepare(g, scratch, &p.obs, st);
     if (rc) return rc;
   }
-  cudaError_t e = lb::launch_moments<S, T>(p, st);
+  unsigned obs_blocks = 0;
+  cudaError_t e = lb::launch_moments<S, T>(p, st, &obs_blocks);
   if (e != cudaSuccess) return fail(LB_ECUDA, "moments kernel launch failed: %s", cudaGetErrorString(e));
+  if (obs_out) {   // second stage of the reduction: block partials -> obs_out
+    e = launch_obs_finish(p.obs, obs_blocks, obs_out, lb::N_OBS_PART, st);
+    if (e != cudaSuccess) return fail(LB_ECUDA, "observable reduction launch failed: %s", cudaGetErrorString(e));
+  }
   return LB_OK;
 }
 

@@ -1238,22 +1238,33 @@ moments_kernel(const __grid_constant__ MomentsParams<T> p) {
     }
   }
   if constexpr (OBS) {
+    // one partial per block, no fence and no ticket (as in the step kernels: a global round trip per block on the
+    // critical path held this kernel at 0.82 of the roofline); obs_finish_kernel, launched behind this grid, adds
+    // the partials up in a fixed order
     if (!active) { acc_e = T(0); acc_m2 = T(0); acc_mass = T(0); }
-    reduce_observables<STEP_BLOCK>(double(acc_e), double(acc_m2), double(acc_mass), p.obs, p.obs_out);
+    double a, b, c;
+    block_reduce3<STEP_BLOCK, T>(acc_e, acc_m2, acc_mass, a, b, c);
+    if (threadIdx.x == 0) {
+      double* bp = p.obs.block_partials + size_t(blockIdx.x) * N_OBS_PART;
+      bp[0] = a; bp[1] = b; bp[2] = c;
+    }
   }
 }
 
+// *obs_blocks = thread blocks that wrote a partial of the reduction (when p.obs_out is set): the caller launches
+// obs_finish_kernel over them
 template <class S, typename T>
-cudaError_t launch_moments(const MomentsParams<T>& p, cudaStream_t st);
+cudaError_t launch_moments(const MomentsParams<T>& p, cudaStream_t st, unsigned* obs_blocks);
 
 template <class S, typename T>
-cudaError_t launch_moments_impl(const MomentsParams<T>& p, cudaStream_t st) {
+cudaError_t launch_moments_impl(const MomentsParams<T>& p, cudaStream_t st, unsigned* obs_blocks) {
   constexpr int VEC = 16 / int(sizeof(T));
   auto aligned = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
   const bool vec = p.n_nodes % VEC == 0 && aligned(p.f) && aligned(p.rho_out) && aligned(p.u_out) &&
                    (size_t(p.n_nodes) * sizeof(T)) % 16 == 0;
   const unsigned n_threads = vec ? p.n_nodes / VEC : p.n_nodes;
   const unsigned grid = (n_threads + STEP_BLOCK - 1) / STEP_BLOCK;
+  *obs_blocks = grid;
   if (vec) {
     if (p.obs_out) moments_kernel<S, T, VEC, true><<<grid, STEP_BLOCK, 0, st>>>(p);
     else moments_kernel<S, T, VEC, false><<<grid, STEP_BLOCK, 0, st>>>(p);
@@ -1560,8 +1571,8 @@ cudaError_t launch_step_coll_impl(StepConfig& c, const StepParams<T>& p, cudaStr
 
 #define LB_INSTANTIATE_MOMENTS(S, T)                                                      \
   template <>                                                                             \
-  cudaError_t lb::launch_moments<S, T>(const MomentsParams<T>& p, cudaStream_t st) {      \
-    return launch_moments_impl<S, T>(p, st);                                              \
+  cudaError_t lb::launch_moments<S, T>(const MomentsParams<T>& p, cudaStream_t st, unsigned* obs_blocks) { \
+    return launch_moments_impl<S, T>(p, st, obs_blocks);                                  \
   }
 
 }  // namespace lb
