@@ -340,6 +340,11 @@ LB_API int lb_ipc_close(void* dptr);
 LB_API int lb_stencil_q(int stencil);
 LB_API size_t lb_bytes_per_update(const lb_desc* desc); /* 2 * Q * sizeof(dtype) */
 LB_API int lb_vector_width(const lb_desc* desc, int has_streaming_bits); /* nodes per thread chosen for aligned fields */
+/* How a call of n_steps time steps on a small 2-D lattice would be run by the tile-resident kernel (state in shared
+ * memory, csrc/lb_resident.cuh) on a device with `sms` multiprocessors and `smem_max` bytes of shared memory per block:
+ * out = {applies, tile_y, tile_z, rounds, steps_base, steps_extra, region elements per population, shared bytes};
+ * round r advances steps_base + (r < steps_extra) time steps.  Pure host arithmetic (tests). */
+LB_API int lb_plan_resident(const lb_desc* desc, int n_steps, int sms, size_t smem_max, int out[8]);
 
 #ifdef __cplusplus
 }

@@ -36,6 +36,7 @@ EXPORTED_SYMBOLS = (
     "lb_unpack_halo", "lb_zface_count", "lb_ipc_alloc", "lb_ipc_free", "lb_ipc_export",
     "lb_ipc_open", "lb_ipc_close", "lb_output_fields", "lb_unpack_halo_ex", "lb_halo_ll_bytes",
     "lb_enstrophy_slab", "lb_static_obs_max_nodes", "lb_observables_static",
+    "lb_plan_resident",
 )
 
 
@@ -131,6 +132,8 @@ def lib() -> C.CDLL:
     L.lb_static_obs_max_nodes.restype = C.c_size_t
     L.lb_observables_static.argtypes = [C.POINTER(LbDesc), C.c_void_p, C.c_void_p, C.c_void_p]
     L.lb_observables_static.restype = C.c_int
+    L.lb_plan_resident.argtypes = [C.POINTER(LbDesc), C.c_int, C.c_int, C.c_size_t, C.POINTER(C.c_int)]
+    L.lb_plan_resident.restype = C.c_int
     L.lb_ipc_alloc.argtypes = [C.c_size_t, C.POINTER(C.c_void_p)]
     L.lb_ipc_free.argtypes = [C.c_void_p]
     L.lb_ipc_export.argtypes = [C.c_void_p, C.c_char_p]

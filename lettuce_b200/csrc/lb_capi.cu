@@ -589,6 +589,20 @@ int lb_vector_width(const lb_desc* d, int has_streaming_bits) {
   return -1;
 }
 
+int lb_plan_resident(const lb_desc* desc, int n_steps, int sms, size_t smem_max, int out[8]) {
+  Geometry g;
+  int rc = check_desc(desc, &g);
+  if (rc) return rc;
+  if (!out || sms < 1) return fail(LB_EINVAL, "bad argument");
+  for (int k = 0; k < 8; ++k) out[k] = 0;
+  if (g.d != 2) return LB_OK;   // the tile-resident kernel is for the 2-D stencil
+  const lb::ResidentPlan pl = lb::plan_resident(g.ny, g.nz, g.q, desc->dtype == LB_F64 ? 8 : 4, n_steps, sms, smem_max, 0);
+  if (!pl.ok) return LB_OK;
+  out[0] = 1; out[1] = int(pl.ty); out[2] = int(pl.tz); out[3] = pl.rounds; out[4] = pl.steps_base; out[5] = pl.steps_extra;
+  out[6] = int(pl.plane_max); out[7] = int(pl.smem);
+  return LB_OK;
+}
+
 int lb_step(const lb_desc* desc, const lb_fields* fields, int n_steps, void* stream) {
   return step_any(desc, fields, n_steps, true, stream);
 }
