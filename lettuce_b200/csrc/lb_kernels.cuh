@@ -128,6 +128,12 @@ struct StepParams {
   // masked stores), and as the last blocks of the grid that path was a tail of 6-9 us per step.
   unsigned block_rot;
   unsigned pf_chunk;   // prefetch kernel: > 0 = consecutive tiles per CTA, scheduled by the hardware (see step_pf_kernel)
+  // prefetch kernel: the base pointer of every population, f_in + q N / f_out + q N, computed by the host.  Read from
+  // the constant bank they cost nothing; derived in the kernel they were ~170 64-bit integer adds per thread in vector
+  // registers (of 1300 instructions of the D3Q27 KBC kernel: the compiler keeps them in the uniform datapath only in
+  // the leanest variants)
+  const T* in_q[27];
+  T* out_q[27];
 };
 
 // number of directions q' < q that leave through the same z face as q
@@ -773,7 +779,7 @@ __device__ __forceinline__ void step_tile(const StepParams<T>& p, const T* __res
       const unsigned dlines = xs[ex + 1] + ys[ey + 1];   // destination line number
       const unsigned dline = dlines * nz;                // its first element
       [[maybe_unused]] const unsigned idx = dline + z0;  // this thread's vector in the destination line
-      T* const bq = f_out + size_t(q) * N;               // uniform
+      T* const bq = (SMEM_IN == SMEM_PRIVATE) ? p.out_q[q] : f_out + size_t(q) * N;   // uniform
 
       // The ONE element of this thread that leaves its vector upwards (ez = +1) / downwards (ez = -1): into the
       // next lane's vector or around the line end (periodic lattice).  `local_ok` = the destination node does not
@@ -1123,7 +1129,7 @@ step_pf_kernel(const __grid_constant__ StepParams<T> p) {
     const size_t node = size_t(tile) * TILE + threadIdx.x * V;
     static_for<S::Q>([&](auto qc) {
       constexpr int q = decltype(qc)::value;
-      cp_async<int(V * sizeof(T))>(mine + q * TILE, p.f_in + size_t(q) * N + node);
+      cp_async<int(V * sizeof(T))>(mine + q * TILE, p.in_q[q] + node);
     });
     cp_async_commit();
     if constexpr (MODE != MODE_PLAIN) mword_next = ld_mask<V>(p.ncm + node);   // needed one tile from now
@@ -1396,16 +1402,17 @@ cudaError_t launch_tma(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
 
 // The per-thread prefetch kernel is compiled for the stencil whose collisions are register-bound (D3Q27: three CTAs
 // per SM or fewer) and for D2Q9, and is the default where it was measured to win (profiles/r2_bench_prefetch.jsonl,
-// 256^3 fp32, fraction of the HBM roofline classic -> prefetch: KBC 0.95 -> 0.99, with an every-step energy reporter
-// 0.86 -> 0.93, TRT 0.99 -> 1.01, Smagorinsky 0.96 -> 1.00; BGK 1.03 -> 1.00, regularized 1.00 -> 0.97 and every fp64
-// variant -- KBC fp64, one node per thread: 0.83 -> 0.75 -- stay with the classic kernel).
+// 256^3 fp32, fraction of the HBM roofline classic -> prefetch: KBC 0.95 -> 1.01, with an every-step energy reporter
+// 0.85 -> 0.96, TRT 0.99 -> 1.015, Smagorinsky 0.965 -> 1.00; BGK 1.03 -> 1.01, regularized 1.00 -> 1.00 and every
+// D3Q27 fp64 variant -- KBC fp64, one node per thread: 0.84 -> 0.81 -- stay with the classic kernel).
 template <class S, typename T, int COLL>
 constexpr bool pf_compiled() { return (S::Q == 27 && COLL != COLL_NONE) || S::Q == 9; }
 template <class S, typename T, int COLL>
 bool pf_default(size_t n_nodes) {
   if (S::Q == 27) return sizeof(T) == 4 && (COLL == COLL_KBC || COLL == COLL_TRT || COLL == COLL_SMAGORINSKY);
-  // D2Q9 KBC fp32 beyond the L2-sized lattices that the TMA kernel takes (4096^2: 0.95 -> 1.03; TMA 0.81)
-  return S::Q == 9 && sizeof(T) == 4 && COLL == COLL_KBC && !tma_default<S, T, COLL>(n_nodes);
+  // D2Q9 KBC beyond the L2-sized lattices that the TMA kernel takes (fp32 4096^2: 0.95 -> 1.03, TMA 0.80; fp64
+  // 2048 x 1024: 0.84 -> 0.90, TMA 0.89)
+  return S::Q == 9 && COLL == COLL_KBC && !tma_default<S, T, COLL>(n_nodes);
 }
 // Tiles per CTA.  More tiles per CTA = more of them prefetched, fewer CTAs = a coarser tail: measured on D3Q27 KBC
 // fp32, fraction of the HBM roofline, at 256^3 (65 536 tiles, 444 resident CTAs): 2 -> 1.00, 4 -> 0.99, 8 -> 0.96,
@@ -1434,6 +1441,10 @@ cudaError_t launch_pf(StepConfig& c, const StepParams<T>& p_in, cudaStream_t st)
   }
   static const int chunk_env = getenv("LB_PF_CHUNK") ? atoi(getenv("LB_PF_CHUNK")) : -1;   // A/B timing only
   StepParams<T> p = p_in;
+  for (int q = 0; q < S::Q; ++q) {
+    p.in_q[q] = p.f_in + size_t(q) * p.n_nodes;
+    p.out_q[q] = p.f_out + size_t(q) * p.n_nodes;
+  }
   const unsigned n_tiles = p.n_threads / STEP_BLOCK;
   p.pf_chunk = chunk_env >= 0 ? unsigned(chunk_env) : pf_chunk(n_tiles, unsigned(resident));
   unsigned grid = n_tiles < unsigned(resident) ? n_tiles : unsigned(resident);
