@@ -11,6 +11,7 @@ import sys
 from abc import ABC, abstractmethod
 from typing import Optional
 
+import numpy as np
 import torch
 
 from . import _native as nat
@@ -157,8 +158,14 @@ class ObservableReporter(Reporter):
     def record_lattice(self, simulation, i, value_lu):
         """entry point of the fused path: value in lattice units from the step kernel"""
         v = self.observable.from_lattice(value_lu)
-        # round through the context dtype as the reference's tensor -> numpy conversion does
-        v = torch.tensor(v, dtype=self.observable.context.dtype).item()
+        # round through the context dtype as the reference's tensor -> numpy conversion does.  (Not through a torch
+        # tensor per value: with an every-step reporter that was ~5 us of host time per step and reporter, as much
+        # as half a time step of a 2048 x 1024 lattice.)
+        dtype = self.observable.context.dtype
+        if dtype == torch.float32:
+            v = float(np.float32(v))
+        elif dtype != torch.float64:
+            v = torch.tensor(v, dtype=dtype).item()
         self.record(simulation, i, [v])
 
     def __call__(self, simulation: 'Simulation'):

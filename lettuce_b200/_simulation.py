@@ -356,8 +356,9 @@ class Simulation:
             if i1 in need_u:
                 self._enstrophy(desc, u_buf, obs[len(idx)])
             row[i1] = len(idx)
-        host = self._finalize_obs(obs)   # the one device->host sync of the segment
+        host = self._finalize_obs(obs).tolist()   # the one device->host sync of the segment; plain floats from here
         flow.i = i1
         for i in sorted(wanted):
+            values = host[row[i]]
             for r in wanted[i]:
-                r.record_lattice(self, i, float(host[row[i], r.native_slot]))
+                r.record_lattice(self, i, values[r.native_slot])
