@@ -1126,7 +1126,7 @@ step_pf_kernel(const __grid_constant__ StepParams<T> p) {
   T* const mine = stage + threadIdx.x * V;                     // + q * TILE: this thread's V values of population q
   uint32_t mword_next = 0;
   auto prefetch = [&](unsigned tile) {
-    const size_t node = size_t(tile) * TILE + threadIdx.x * V;
+    const unsigned node = tile * TILE + threadIdx.x * V;   // < 2^31 nodes: a 32-bit index, one wide multiply-add per address
     static_for<S::Q>([&](auto qc) {
       constexpr int q = decltype(qc)::value;
       cp_async<int(V * sizeof(T))>(mine + q * TILE, p.in_q[q] + node);

@@ -149,10 +149,16 @@ inline ResidentPlan plan_resident(unsigned ny, unsigned nz, int q, size_t elem, 
   if (n_steps < 2) return best;
   double best_cost = 1e30;
   const double fixed_ns = 1700.0, node_ns = elem == 8 ? 2.6 : 1.9;   // measured (256^2): per round, per node update of ONE CTA
-  for (unsigned ty = 1; ty <= ny; ++ty) {
-    if (ny % ty) continue;
-    for (unsigned tz = 1; tz <= nz; ++tz) {
-      if (nz % tz) continue;
+  // (divisors first: the search runs on the host inside every multi-step call)
+  unsigned dy[128], dz[128];
+  int ndy = 0, ndz = 0;
+  const unsigned t_max = 4096;   // a tile edge beyond that cannot fit: (ty + 2)(tz + 2) 2 q elem <= 227 KB
+  for (unsigned t = 1; t <= ny && t <= t_max && ndy < 128; ++t) if (ny % t == 0) dy[ndy++] = t;
+  for (unsigned t = 1; t <= nz && t <= t_max && ndz < 128; ++t) if (nz % t == 0) dz[ndz++] = t;
+  for (int iy = 0; iy < ndy; ++iy) {
+    const unsigned ty = dy[iy];
+    for (int iz = 0; iz < ndz; ++iz) {
+      const unsigned tz = dz[iz];
       const unsigned tiles = (ny / ty) * (nz / tz);
       if (tiles > unsigned(sms)) continue;
       for (int h = 1; h <= 16 && h <= n_steps; ++h) {
