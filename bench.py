@@ -255,7 +255,17 @@ def extras_single_gpu(dev, peak):
         sim = lt.Simulation(flow, lt.BGKCollision(tau=flow.units.relaxation_parameter_lu), [])
         t = _timed(sim, 1000, 1000, dev)
         out.append(_extra_line("cfg1 TGV2D D2Q9 BGK f64 256^2 x1000 steps", 256 * 256, 9, 8, t, 1000, peak,
-                               note="4.7 MB of state: L2-resident, bounded by the per-step grid barrier, not by HBM"))
+                               note="4.7 MB of state, never HBM-bound: tile-resident kernel (tiles in shared memory, one grid "
+                                    "barrier per ~6 time steps); the limit is the arithmetic of the tiles incl. their halo rings"))
+
+    def cfg2_reporter():   # the headline lattice with the reporter the reference's examples attach (03_outputs_TGV.py)
+        ctx = lt.Context(device=dev, dtype=torch.float32, use_native=True)
+        flow = lt.TaylorGreenVortex(ctx, resolution=256, reynolds_number=1600, mach_number=0.1, stencil=lt.D3Q19)
+        rep = lt.ObservableReporter(lt.IncompressibleKineticEnergy(flow), interval=1, out=None)
+        sim = lt.Simulation(flow, lt.BGKCollision(tau=flow.units.relaxation_parameter_lu), [rep])
+        t = _timed(sim, 200, 20, dev)
+        out.append(_extra_line("cfg2 TGV3D D3Q19 BGK f32 256^3 with a fused energy reporter every step", 256 ** 3, 19, 4, t,
+                               200, peak))
 
     class LocalObstacle(lt.Obstacle):
         """BASELINE config 3, "bounce-back + equilibrium inlet/outlet" read as all node-local boundaries
@@ -315,7 +325,7 @@ def extras_single_gpu(dev, peak):
         out.append(_extra_line("cfg5 slab geometry on ONE GPU: TGV3D D3Q19 BGK f32 1024x1024x128 (periodic by itself)",
                                1024 * 1024 * 128, 19, 4, t, 30, peak))
 
-    for fn in (cfg1, cfg3, cfg4, cfg5_one_gpu):
+    for fn in (cfg1, cfg2_reporter, cfg3, cfg4, cfg5_one_gpu):
         guarded(fn)
     return out
 
