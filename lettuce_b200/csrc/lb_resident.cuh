@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(RES_BLOCK, 1) step_resident_kernel(const __gri
 }
 
 // Plan of a call of n_steps time steps on an ny x nz lattice: tile, rounds, steps per round.  Cost model per round:
-// a fixed part (load + store + grid barrier, measured ~2 us) + the node updates of the shrinking region at the
+// a fixed part (load + store + grid barrier) + the node updates of the shrinking region at the
 // measured rate per CTA; the best (tile, h) minimises the time per step.  Constraints: all CTAs co-resident (one per
 // SM: the tile needs most of the shared memory), two region buffers within the shared memory of an SM.
 struct ResidentPlan {
@@ -148,7 +148,9 @@ inline ResidentPlan plan_resident(unsigned ny, unsigned nz, int q, size_t elem, 
   ResidentPlan best;
   if (n_steps < 2) return best;
   double best_cost = 1e30;
-  const double fixed_ns = 1700.0, node_ns = elem == 8 ? 2.6 : 1.9;   // measured (256^2): per round, per node update of ONE CTA
+  // measured on B200 (h sweep at 256^2, profiles/r2_bench_small_lattices_resident_h_sweep.jsonl): ~4.5 us per round
+  // (load + store + grid barrier) and 1.7 (fp64) / 1.2 (fp32) ns per node update of ONE CTA
+  const double fixed_ns = 4500.0, node_ns = elem == 8 ? 1.7 : 1.2;
   // (divisors first: the search runs on the host inside every multi-step call)
   unsigned dy[128], dz[128];
   int ndy = 0, ndz = 0;
