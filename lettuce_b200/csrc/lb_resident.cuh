@@ -26,7 +26,7 @@ struct ResidentParams {
   unsigned ny, nz;     // the lattice in kernel axes (Z contiguous)
   unsigned n_nodes;
   unsigned ty, tz;     // tile of a CTA; ty | ny, tz | nz; grid = (ny / ty) * (nz / tz) CTAs, all co-resident
-  unsigned plane_max;  // elements per population of the largest region: (ty + 2 h_max) * (tz + 2 h_max)
+  unsigned plane_max;  // elements per population of the largest padded region: (ty + 2 h_max + 2) * (tz + 2 h_max + 2)
   int rounds;          // global exchanges of the call
   int steps_base;      // round r advances steps_base + (r < steps_extra ? 1 : 0) time steps
   int steps_extra;
@@ -47,7 +47,11 @@ __global__ void __launch_bounds__(RES_BLOCK, 1) step_resident_kernel(const __gri
   int h_prev = -1;
   for (int r = 0; r < p.rounds; ++r) {
     const int h = p.steps_base + (r < p.steps_extra ? 1 : 0);   // time steps of this round = width of the halo
-    const unsigned RY = p.ty + 2u * unsigned(h), RZ = p.tz + 2u * unsigned(h), plane = RY * RZ;
+    // The buffers carry one ring of padding around the region: a push from the region's edge lands in the padding
+    // instead of needing a bounds test (18 compare / predicate instructions per node update).  PZ = pitch of a row,
+    // at(ry, rz) = element of region node (ry, rz).
+    const unsigned RY = p.ty + 2u * unsigned(h), RZ = p.tz + 2u * unsigned(h), PZ = RZ + 2u, plane = (RY + 2u) * PZ;
+    auto at = [&](unsigned ry, unsigned rz) { return (ry + 1u) * PZ + rz + 1u; };
     const T* __restrict__ src = p.buf[r & 1];
     T* __restrict__ dst = p.buf[(r + 1) & 1];
     // ---- tile + halo: global (L2) -> shared, periodic wrap.  ld.cg: the lines were written by other CTAs.
@@ -56,7 +60,7 @@ __global__ void __launch_bounds__(RES_BLOCK, 1) step_resident_kernel(const __gri
     // neighbours' results -- is loaded, at most one node per thread, i.e. one L2 round trip for the whole load.
     const bool frame_only = r > 0 && h == h_prev;
     h_prev = h;
-    const unsigned uh = unsigned(h), n_band = 2u * uh * RZ, n_load = frame_only ? n_band + 2u * uh * p.ty : plane;
+    const unsigned uh = unsigned(h), n_band = 2u * uh * RZ, n_load = frame_only ? n_band + 2u * uh * p.ty : RY * RZ;
     for (unsigned j = threadIdx.x; j < n_load; j += RES_BLOCK) {
       unsigned ry, rz;
       if (!frame_only) {
@@ -73,7 +77,7 @@ __global__ void __launch_bounds__(RES_BLOCK, 1) step_resident_kernel(const __gri
       if (gy < 0) gy += int(p.ny);
       if (gz < 0) gz += int(p.nz);
       const unsigned g = unsigned(gy) * p.nz + unsigned(gz);
-      const unsigned i = ry * RZ + rz;
+      const unsigned i = at(ry, rz);
       T v[Q];
 #pragma unroll
       for (int q = 0; q < Q; ++q) v[q] = __ldcg(src + size_t(q) * N + g);
@@ -104,15 +108,14 @@ __global__ void __launch_bounds__(RES_BLOCK, 1) step_resident_kernel(const __gri
       auto push = [&](const T (&g)[Q], unsigned ry, unsigned rz) {
         static_for<Q>([&](auto qc) {
           constexpr int q = decltype(qc)::value;
-          const unsigned dy = ry + unsigned(S::e(q, 1)), dz = rz + unsigned(S::e(q, 2));   // wraps below 0 to >= RY
-          if (dy < RY && dz < RZ) B[q * plane + dy * RZ + dz] = g[q];
+          B[q * plane + at(ry + unsigned(S::e(q, 1)), rz + unsigned(S::e(q, 2)))] = g[q];   // edge pushes: into the padding
         });
       };
       for (unsigned i = threadIdx.x; i < n_sub; i += RES_BLOCK) {
         const unsigned ry0 = y + o, rz0 = z + o;
         advance();
         T g0[Q];
-        load(g0, ry0 * RZ + rz0);
+        load(g0, at(ry0, rz0));
         collide(g0);
         push(g0, ry0, rz0);
       }
@@ -123,7 +126,7 @@ __global__ void __launch_bounds__(RES_BLOCK, 1) step_resident_kernel(const __gri
     for (unsigned i = threadIdx.x; i < p.ty * p.tz; i += RES_BLOCK) {
       const unsigned y = i / p.tz, z = i - y * p.tz;
       const unsigned g = (unsigned(ty0) + y) * p.nz + unsigned(tz0) + z;
-      const unsigned idx = (y + unsigned(h)) * RZ + z + unsigned(h);
+      const unsigned idx = at(y + unsigned(h), z + unsigned(h));
 #pragma unroll
       for (int q = 0; q < Q; ++q) dst[size_t(q) * N + g] = A[q * plane + idx];
     }
@@ -166,7 +169,7 @@ inline ResidentPlan plan_resident(unsigned ny, unsigned nz, int q, size_t elem, 
       for (int h = 1; h <= 16 && h <= n_steps; ++h) {
         if (force_h > 0 && h != force_h) continue;
         if (unsigned(h) > ny || unsigned(h) > nz) break;
-        const size_t plane = size_t(ty + 2 * h) * (tz + 2 * h);
+        const size_t plane = size_t(ty + 2 * h + 2) * (tz + 2 * h + 2);   // region + one ring of padding
         const size_t smem = 2 * size_t(q) * plane * elem;
         if (smem > smem_max) break;
         double updates = 0;
@@ -187,7 +190,7 @@ inline ResidentPlan plan_resident(unsigned ny, unsigned nz, int q, size_t elem, 
   best.steps_base = n_steps / rounds;
   best.steps_extra = n_steps % rounds;
   const int hmax = best.steps_base + (best.steps_extra ? 1 : 0);
-  best.plane_max = (best.ty + 2 * hmax) * (best.tz + 2 * hmax);
+  best.plane_max = (best.ty + 2 * hmax + 2) * (best.tz + 2 * hmax + 2);
   best.smem = 2 * size_t(q) * best.plane_max * elem;
   return best;
 }

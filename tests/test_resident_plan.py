@@ -35,7 +35,7 @@ def test_plan_invariants(res, dtype):
         assert rounds >= 1 and rounds % 2 == n % 2                                     # state ends where n steps leave it
         assert base * rounds + extra == n and 0 <= extra < rounds and base >= 1        # every step is taken once
         hmax = base + (1 if extra else 0)
-        assert plane_max == (ty + 2 * hmax) * (tz + 2 * hmax)
+        assert plane_max == (ty + 2 * hmax + 2) * (tz + 2 * hmax + 2)   # region + one ring of padding
         assert smem == 2 * 9 * plane_max * elem and smem <= SMEM                       # two region buffers fit
         assert hmax <= ny and hmax <= nz                                               # one periodic wrap per halo node
 
