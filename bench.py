@@ -387,6 +387,33 @@ def slab_bit_exact(dev, rank, world):
     return ok
 
 
+def _bind_to_gpu_numa_node(local):
+    """Run this rank on the CPUs of the NUMA node its GPU hangs off, so that the pinned host buffers of the end-to-end
+    leg (allocated below: first touch) and the copies do not cross the socket interconnect.  Returns
+    {"node": n, "cpus": k} or None where the box has no such information (single node, container without sysfs).
+    LB_NO_NUMA_BIND=1 leaves the affinity alone (A/B)."""
+    if os.environ.get("LB_NO_NUMA_BIND"):
+        return None
+    try:
+        import torch
+        p = torch.cuda.get_device_properties(local)
+        bdf = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = os.sched_getaffinity(0) & cpus
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return {"node": node, "cpus": len(allowed)}
+    except Exception:
+        return None
+
+
 def run_native(args):
     import torch
     import torch.distributed as dist
@@ -399,6 +426,7 @@ def run_native(args):
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = _bind_to_gpu_numa_node(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -559,6 +587,7 @@ def run_native(args):
         "clocks": clocks, "gpu_launches": launches_all,
     }
     if e2e is not None:
+        e2e["host_numa_binding"] = numa   # rank 0's: {"node", "cpus"} or null where the box offers none
         line["e2e"] = e2e
     if parity is not None:
         line["parity"] = parity
