@@ -141,6 +141,7 @@ int vector_width(int coll, int mode, const Geometry& g, const void* a, const voi
 // the chunking depends on n_blocks only.
 constexpr int OBS_FINISH_CHUNKS = 128;
 constexpr int OBS_FINISH_BLOCK = 256;
+constexpr int OBS_FINISH_SINGLE = 4096;
 
 __global__ void __launch_bounds__(OBS_FINISH_BLOCK)
 obs_finish_kernel(lb::ObsScratch sc, unsigned n_blocks, double* out, int n_out) {
@@ -161,6 +162,14 @@ obs_finish_kernel(lb::ObsScratch sc, unsigned n_blocks, double* out, int n_out) 
     c += bp[2];
   }
   lb::block_reduce3<OBS_FINISH_BLOCK>(a, b, c);
+  if (gridDim.x == 1) {   // few partials (persistent kernels, 2-D lattices): one block, no fence, no ticket
+    if (threadIdx.x == 0) {
+      out[0] = a;
+      if (n_out > 1) out[1] = b;
+      if (n_out > 2) out[2] = c;
+    }
+    return;
+  }
   if (threadIdx.x == 0) {
     double* gp = sc.group_partials + size_t(blockIdx.x) * lb::N_OBS_PART;
     gp[0] = a; gp[1] = b; gp[2] = c;
@@ -185,7 +194,9 @@ obs_finish_kernel(lb::ObsScratch sc, unsigned n_blocks, double* out, int n_out) 
 }
 
 cudaError_t launch_obs_finish(const lb::ObsScratch& sc, unsigned n_blocks, double* out, int n_out, cudaStream_t st) {
-  const unsigned chunks = (n_blocks + OBS_FINISH_BLOCK - 1) / OBS_FINISH_BLOCK;
+  // up to OBS_FINISH_SINGLE partials: ONE block (measured: the three-block ticket version took 5 us to add up the 740
+  // partials of a persistent kernel -- two fences and an atomic round trip -- between two 22 us time steps)
+  const unsigned chunks = n_blocks <= unsigned(OBS_FINISH_SINGLE) ? 1u : (n_blocks + OBS_FINISH_BLOCK - 1) / OBS_FINISH_BLOCK;
   const unsigned grid = chunks < unsigned(OBS_FINISH_CHUNKS) ? (chunks ? chunks : 1u) : unsigned(OBS_FINISH_CHUNKS);
   static const bool no_pdl = getenv("LB_NO_PDL") != nullptr;   // A/B timing only
   cudaLaunchConfig_t cfg{};
