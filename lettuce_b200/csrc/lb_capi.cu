@@ -936,10 +936,101 @@ initialize_kernel(const T* __restrict__ rho, const T* __restrict__ u, T* __restr
   });
 }
 
+// The same with V nodes of a z line per thread: 16-byte loads of rho and u, the 6 x 3 taps of a derivative as whole
+// vectors (diff6_vec / diff6_line, shared with the enstrophy kernel), 16-byte stores of the populations.  The scalar
+// kernel above issues 54 + 4 scalar loads and 19 - 27 scalar stores per node and ran at 0.23 of the HBM roofline (it
+// writes Q values per node once: 1.0 ms at 256^3 D3Q19 fp32).  Element by element the arithmetic is the scalar kernel's.
+template <class S, typename T, int V>
+__global__ void __launch_bounds__(lb::STEP_BLOCK)
+initialize_vec_kernel(const T* __restrict__ rho, const T* __restrict__ u, T* __restrict__ f, unsigned nx, unsigned ny,
+                      unsigned nz, unsigned ghost, T tau, int with_fneq) {
+  const unsigned nzv = nz / V;
+  const size_t tid = size_t(blockIdx.x) * lb::STEP_BLOCK + threadIdx.x;
+  const size_t n = size_t(nx) * ny * nz;
+  if (tid >= size_t(nx) * ny * nzv) return;
+  const unsigned zv = unsigned(tid % nzv);
+  const unsigned y = unsigned((tid / nzv) % ny);
+  const unsigned x = unsigned(tid / (size_t(nzv) * ny));
+  const unsigned nze = nz + 2 * ghost;
+  const size_t n_ext = size_t(nx) * ny * nze;
+  const size_t zoff = size_t(ghost) + size_t(zv) * V;
+  const size_t e = (size_t(x) * ny + y) * nze + zoff;        // this vector in the extended arrays
+  const lb::Vec<T, V> rv = lb::ld_vec<T, V>(rho + e);
+  T uu[3][V] = {};
+#pragma unroll
+  for (int c = 0; c < S::D; ++c) {
+    const lb::Vec<T, V> v = lb::ld_vec<T, V>(u + c * n_ext + e);
+#pragma unroll
+    for (int k = 0; k < V; ++k) uu[S::axis(c)][k] = v.v[k];
+  }
+  T gd[3][3][V] = {};                                        // gd[a][b][k] = d u_a / d x_b of node k (kernel axes)
+  if (with_fneq) {
+#pragma unroll
+    for (int c = 0; c < S::D; ++c) {
+      const int a = S::axis(c);
+      const T* ua = u + c * n_ext;
+      if (S::D == 3) diff6_vec<T, V>(ua, size_t(y) * nze + zoff, (long long)ny * nze, x, nx, true, gd[a][0]);
+      diff6_vec<T, V>(ua, size_t(x) * ny * nze + zoff, nze, y, ny, true, gd[a][1]);
+      diff6_line<T, V>(ua + (size_t(x) * ny + y) * nze + ghost, zv, nzv, ghost == 0, gd[a][2]);
+    }
+  }
+  T out[S::Q][V];
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    const T r = rv.v[k];
+    const T un[3] = {uu[0][k], uu[1][k], uu[2][k]};
+    T feq[S::Q];
+    lb::equilibrium<S, T>(r, un, feq);
+    if (with_fneq) {
+      const T cs2 = T(LB_CS2);
+      const T cs2_eye = T(float(LB_CS2));                    // torch.eye(d) * cs ** 2 is float32 in the reference (see above)
+      T pi[3][3];
+#pragma unroll
+      for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int b = 0; b < 3; ++b) pi[a][b] = tau * r * gd[a][b][k] / cs2;
+      lb::static_for<S::Q>([&](auto qc) {
+        constexpr int q = decltype(qc)::value;
+        T acc = T(0);
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+#pragma unroll
+          for (int b = 0; b < 3; ++b) {
+            if (S::D == 2 && (a == 0 || b == 0)) continue;
+            const T qab = T(S::e(q, a) * S::e(q, b)) - (a == b ? cs2_eye : T(0));
+            acc += pi[a][b] * qab;
+          }
+        feq[q] -= T(S::w(q)) * acc;
+      });
+    }
+    lb::static_for<S::Q>([&](auto qc) { out[decltype(qc)::value][k] = feq[decltype(qc)::value]; });
+  }
+  const size_t node = tid * V;                               // interior index of this thread's first node
+  lb::static_for<S::Q>([&](auto qc) {
+    constexpr int q = decltype(qc)::value;
+    lb::Vec<T, V> v;
+#pragma unroll
+    for (int k = 0; k < V; ++k) v.v[k] = out[q][k];
+    lb::st_vec<T, V>(f + q * n + node, v);
+  });
+}
+
 template <class S, typename T>
 int initialize_typed(const lb_desc* d, const Geometry& g, const void* rho, const void* u, int ghost, int with_fneq,
                      void* f, cudaStream_t st) {
   const size_t n = size_t(g.n_nodes);
+  constexpr int V = 16 / int(sizeof(T));
+  static const bool scalar_only = getenv("LB_INIT_SCALAR") != nullptr;   // A/B timing only
+  if (!scalar_only && g.nz % V == 0 && unsigned(ghost) % V == 0 && g.nz / V >= 3u && aligned_to(rho, 16) && aligned_to(u, 16) &&
+      aligned_to(f, 16) && (n * sizeof(T)) % 16 == 0 && (size_t(g.nx) * g.ny * (g.nz + 2 * ghost) * sizeof(T)) % 16 == 0) {
+    const size_t threads = n / V;
+    const unsigned vgrid = unsigned((threads + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK);
+    initialize_vec_kernel<S, T, V><<<vgrid, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(rho), static_cast<const T*>(u),
+                                                                   static_cast<T*>(f), g.nx, g.ny, g.nz, unsigned(ghost),
+                                                                   T(d->tau), with_fneq);
+    LB_CUDA(cudaGetLastError());
+    return LB_OK;
+  }
   const unsigned grid = unsigned((n + lb::STEP_BLOCK - 1) / lb::STEP_BLOCK);
   initialize_kernel<S, T><<<grid, lb::STEP_BLOCK, 0, st>>>(static_cast<const T*>(rho), static_cast<const T*>(u),
                                                         static_cast<T*>(f), g.nx, g.ny, g.nz, unsigned(ghost),
