@@ -558,6 +558,8 @@ template <class S, typename T, int V, int COLL, int MODE = MODE_PLAIN>
 constexpr int step_min_blocks() {
   // masked streaming keeps a few more registers per thread (destination bits): one block less
   if (sizeof(T) == 4 && V >= 2 && MODE == MODE_NCM_SBITS) return (S::Q == 27) ? 2 : 3;
+  // D3Q27 KBC fp32 with four nodes per thread: 255 registers, no spills, two CTAs per SM (see vector_nodes)
+  if (sizeof(T) == 4 && V == 4 && S::Q == 27 && COLL == COLL_KBC && MODE != MODE_NCM_SBITS) return 2;
   if (sizeof(T) == 4 && V >= 2) return (S::Q == 27 || ((COLL == COLL_TRT || COLL >= COLL_REGULARIZED) && V == 4)) ? 3 : 4;
   return 1;
 }
@@ -1149,7 +1151,10 @@ step_pf_kernel(const __grid_constant__ StepParams<T> p) {
   const unsigned tile_end = chunk ? min(n_tiles, tile + chunk) : n_tiles;
   const unsigned stride = chunk ? 1u : gridDim.x;
   if (tile < tile_end) prefetch(tile);
-  double e = 0.0, m2 = 0.0, mass = 0.0;
+  // the thread's running (sum, max, sum) over its tiles live in shared memory, not in six registers across the tile
+  // body: the D3Q27 KBC kernel with four nodes per thread sits at 255 registers
+  __shared__ double s_obs[OBS ? N_OBS_PART : 1][OBS ? STEP_BLOCK : 1];
+  if constexpr (OBS) { s_obs[0][threadIdx.x] = 0.0; s_obs[1][threadIdx.x] = 0.0; s_obs[2][threadIdx.x] = 0.0; }
   for (; tile < tile_end; tile += stride) {
     cp_async_wait_all();
     const uint32_t mword = mword_next;
@@ -1158,9 +1163,14 @@ step_pf_kernel(const __grid_constant__ StepParams<T> p) {
         p, p.f_in, p.f_out, p.u_out, tile, stage, te, tm2, tmass, [&]() {
           if (tile + stride < tile_end) prefetch(tile + stride);
         }, mword);
-    if constexpr (OBS) { e += double(te); m2 = fmax(m2, double(tm2)); mass += double(tmass); }
+    if constexpr (OBS) {
+      s_obs[0][threadIdx.x] += double(te);
+      s_obs[1][threadIdx.x] = fmax(s_obs[1][threadIdx.x], double(tm2));
+      s_obs[2][threadIdx.x] += double(tmass);
+    }
   }
   if constexpr (OBS) {   // one partial per CTA (fixed tiles per CTA); obs_finish_kernel adds them up in a fixed order
+    double e = s_obs[0][threadIdx.x], m2 = s_obs[1][threadIdx.x], mass = s_obs[2][threadIdx.x];
     block_reduce3<STEP_BLOCK>(e, m2, mass);
     if (threadIdx.x == 0) {
       double* bp = p.obs.block_partials + size_t(blockIdx.x) * N_OBS_PART;
@@ -1336,16 +1346,21 @@ cudaError_t launch_step(StepConfig& c, const StepParams<T>& p, cudaStream_t st) 
 // Nodes per thread along the contiguous axis that are COMPILED for (stencil, dtype, collision, mode): one
 // node per thread (any shape, any alignment) and one vector width -- 16 bytes, except where the register
 // budget says otherwise (measured):
-//   D3Q27 KBC / TRT / Smagorinsky hold ~60 values per node beside the populations: fp32 runs two nodes per
-//     thread as packed F2 values (<= 168 registers, three blocks per SM; 0.92 / 0.97 / 0.96 of the HBM
-//     roofline against 0.82 / 0.91 / 0.91 with four nodes), fp64 KBC one node per thread;
+//   D3Q27 TRT / Smagorinsky hold ~60 values per node beside the populations: fp32 runs two nodes per
+//     thread as packed F2 values (<= 168 registers, three blocks per SM; 0.97 / 0.96 of the HBM roofline
+//     against 0.91 / 0.91 with four nodes); D3Q27 KBC fp64 one node per thread;
+//   D3Q27 KBC fp32: FOUR nodes per thread (255 registers without spills, two blocks per SM).  Round 1 had
+//     measured two nodes faster (0.92 vs 0.82); with the packed pair arithmetic of today and the prefetch kernel
+//     hiding the load latency the balance is the other way: the index / edge-store overhead per node halves, and
+//     the kernel is issue- and clock-bound -- config 4 (512^3) 0.955 -> 0.995 in the same run, classic kernel
+//     0.92 -> 0.94 (profiles/r2_bench_kbc_four_nodes_per_thread.jsonl);
 //   D3Q27 with masked streaming: 212 registers (2 blocks per SM) with four nodes, 161 (3 blocks) with two;
 //     0.89 vs 0.92 on the stock obstacle.
 // Lines whose length or alignment does not fit the vector run one node per thread.
 template <class S, typename T>
 __host__ __device__ constexpr int vector_nodes(int coll, int mode) {
   int v = 16 / int(sizeof(T));
-  if (S::Q == 27 && coll == COLL_KBC) v = (sizeof(T) == 4) ? 2 : 1;
+  if (S::Q == 27 && coll == COLL_KBC && sizeof(T) == 8) v = 1;
   if (S::Q == 27 && sizeof(T) == 4 && (coll == COLL_TRT || coll == COLL_SMAGORINSKY)) v = 2;
   if (S::Q == 27 && sizeof(T) == 4 && mode == MODE_NCM_SBITS && v > 2) v = 2;
   return v;
