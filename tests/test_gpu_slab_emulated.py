@@ -35,7 +35,8 @@ def _run_slabs(stencil, dtype, res, R, n_steps, collision, mode, with_mask, with
     flow = gu.FieldFlow(ctx, res, getattr(lt, stencil), f0)
     if with_mask:
         flow.boundaries.append(gu.TaggedBounceBack(solid, nsm=nsm, tag=1))
-    coll = {"none": lt.NoCollision(), "bgk": lt.BGKCollision(0.7), "trt": lt.TRTCollision(0.7, 0.9)}[collision]
+    coll = {"none": lambda: lt.NoCollision(), "bgk": lambda: lt.BGKCollision(0.7), "trt": lambda: lt.TRTCollision(0.7, 0.9),
+            "kbc": lambda: lt.KBCCollision()}[collision]()
     sim = lt.Simulation(flow, coll, [])
     sim(n_steps)
     want = flow.f
@@ -171,3 +172,13 @@ def test_direct_transport_refuses_masked_streaming():
     nat = lt.native
     with pytest.raises(nat.NativeError, match="packed halo transport"):
         _run_slabs("D3Q19", "f32", [4, 4, 16], 2, 1, "none", "direct", with_mask=True, with_nsm=True)
+
+
+@pytest.mark.parametrize("stencil,dtype,res,R", [("D3Q27", "f32", [4, 3, 24], 2), ("D3Q27", "f32", [5, 7, 96], 2),
+                                                 ("D3Q27", "f64", [3, 3, 9], 3), ("D2Q9", "f32", [6, 32], 2)])
+@pytest.mark.parametrize("mode", ["packed", "ll"])
+def test_slab_kbc_equals_undivided(stencil, dtype, res, R, mode):
+    """KBC in slabs: D3Q27 fp32 runs FOUR nodes per thread (255 registers) in the halo variants of the kernel too --
+    slabs of 12 and 48 planes take the vector kernel, the undivided lattice as well; bit for bit"""
+    got, want = _run_slabs(stencil, dtype, res, R, 5, "kbc", mode, with_mask=False)
+    assert torch.equal(got, want)
