@@ -558,8 +558,11 @@ template <class S, typename T, int V, int COLL, int MODE = MODE_PLAIN>
 constexpr int step_min_blocks() {
   // masked streaming keeps a few more registers per thread (destination bits): one block less
   if (sizeof(T) == 4 && V >= 2 && MODE == MODE_NCM_SBITS) return (S::Q == 27) ? 2 : 3;
-  // D3Q27 KBC fp32 with four nodes per thread: 255 registers, no spills, two CTAs per SM (see vector_nodes)
-  if (sizeof(T) == 4 && V == 4 && S::Q == 27 && COLL == COLL_KBC && MODE != MODE_NCM_SBITS) return 2;
+  // D3Q27 KBC / TRT / Smagorinsky fp32 with four nodes per thread: up to 255 registers, no spills, two CTAs per SM
+  // (see vector_nodes)
+  if (sizeof(T) == 4 && V == 4 && S::Q == 27 && (COLL == COLL_KBC || COLL == COLL_TRT || COLL == COLL_SMAGORINSKY) &&
+      MODE != MODE_NCM_SBITS)
+    return 2;
   if (sizeof(T) == 4 && V >= 2) return (S::Q == 27 || ((COLL == COLL_TRT || COLL >= COLL_REGULARIZED) && V == 4)) ? 3 : 4;
   return 1;
 }
@@ -1346,10 +1349,10 @@ cudaError_t launch_step(StepConfig& c, const StepParams<T>& p, cudaStream_t st) 
 // Nodes per thread along the contiguous axis that are COMPILED for (stencil, dtype, collision, mode): one
 // node per thread (any shape, any alignment) and one vector width -- 16 bytes, except where the register
 // budget says otherwise (measured):
-//   D3Q27 TRT / Smagorinsky hold ~60 values per node beside the populations: fp32 runs two nodes per
-//     thread as packed F2 values (<= 168 registers, three blocks per SM; 0.97 / 0.96 of the HBM roofline
-//     against 0.91 / 0.91 with four nodes); D3Q27 KBC fp64 one node per thread;
-//   D3Q27 KBC fp32: FOUR nodes per thread (255 registers without spills, two blocks per SM).  Round 1 had
+//   D3Q27 KBC fp64 one node per thread;
+//   D3Q27 KBC / TRT / Smagorinsky fp32: FOUR nodes per thread like everything else (up to 255 registers without
+//     spills, two blocks per SM) -- TRT 512^3 0.97 -> 1.03 (classic), Smagorinsky 0.98 -> 1.02 (prefetch kernel),
+//     profiles/r2_bench_trt_smagorinsky_four_nodes_per_thread.jsonl.  KBC: round 1 had
 //     measured two nodes faster (0.92 vs 0.82); with the packed pair arithmetic of today and the prefetch kernel
 //     hiding the load latency the balance is the other way: the index / edge-store overhead per node halves, and
 //     the kernel is issue- and clock-bound -- config 4 (512^3) 0.955 -> 0.995 in the same run, classic kernel
@@ -1361,7 +1364,6 @@ template <class S, typename T>
 __host__ __device__ constexpr int vector_nodes(int coll, int mode) {
   int v = 16 / int(sizeof(T));
   if (S::Q == 27 && coll == COLL_KBC && sizeof(T) == 8) v = 1;
-  if (S::Q == 27 && sizeof(T) == 4 && (coll == COLL_TRT || coll == COLL_SMAGORINSKY)) v = 2;
   if (S::Q == 27 && sizeof(T) == 4 && mode == MODE_NCM_SBITS && v > 2) v = 2;
   return v;
 }
@@ -1417,14 +1419,14 @@ cudaError_t launch_tma(StepConfig& c, const StepParams<T>& p, cudaStream_t st) {
 
 // The per-thread prefetch kernel is compiled for the stencil whose collisions are register-bound (D3Q27: three CTAs
 // per SM or fewer) and for D2Q9, and is the default where it was measured to win (profiles/r2_bench_prefetch.jsonl,
-// 256^3 fp32, fraction of the HBM roofline classic -> prefetch: KBC 0.95 -> 1.01, with an every-step energy reporter
-// 0.85 -> 0.96, TRT 0.99 -> 1.015, Smagorinsky 0.965 -> 1.00; BGK 1.03 -> 1.01, regularized 1.00 -> 1.00 and every
-// D3Q27 fp64 variant -- KBC fp64, one node per thread: 0.84 -> 0.81 -- stay with the classic kernel).
+// D3Q27 fp32 with four nodes per thread, fraction of the HBM roofline classic -> prefetch: KBC 512^3 0.94 -> 0.98 -
+// 1.02, Smagorinsky 512^3 0.97 -> 1.02; TRT 1.03 -> 1.01, BGK 1.03 -> 1.01, regularized 1.00 -> 1.00 and every D3Q27
+// fp64 variant -- KBC fp64, one node per thread: 0.84 -> 0.81 -- stay with the classic kernel).
 template <class S, typename T, int COLL>
 constexpr bool pf_compiled() { return (S::Q == 27 && COLL != COLL_NONE) || S::Q == 9; }
 template <class S, typename T, int COLL>
 bool pf_default(size_t n_nodes) {
-  if (S::Q == 27) return sizeof(T) == 4 && (COLL == COLL_KBC || COLL == COLL_TRT || COLL == COLL_SMAGORINSKY);
+  if (S::Q == 27) return sizeof(T) == 4 && (COLL == COLL_KBC || COLL == COLL_SMAGORINSKY);   // TRT: classic 1.03 vs 1.01
   // D2Q9 KBC beyond the L2-sized lattices that the TMA kernel takes (fp32 4096^2: 0.95 -> 1.03, TMA 0.80; fp64
   // 2048 x 1024: 0.84 -> 0.90, TMA 0.89)
   return S::Q == 9 && COLL == COLL_KBC && !tma_default<S, T, COLL>(n_nodes);
