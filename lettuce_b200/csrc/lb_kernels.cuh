@@ -1363,7 +1363,7 @@ cudaError_t launch_step(StepConfig& c, const StepParams<T>& p, cudaStream_t st) 
 template <class S, typename T>
 __host__ __device__ constexpr int vector_nodes(int coll, int mode) {
   int v = 16 / int(sizeof(T));
-  if (S::Q == 27 && coll == COLL_KBC && sizeof(T) == 8) v = 1;
+  if (S::Q == 27 && coll == COLL_KBC && sizeof(T) == 8) v = 1;   // (two nodes: 255 registers, classic 0.77, prefetch 0.84 vs 0.865)
   if (S::Q == 27 && sizeof(T) == 4 && mode == MODE_NCM_SBITS && v > 2) v = 2;
   return v;
 }
